@@ -1,0 +1,250 @@
+// Matrix-factorisation kernels: fused pull-compute-push SGD (N1), streaming ring consumer (N2),
+// prediction.  One sub-warp of LANES lanes owns one rating; each lane owns VPL float4 slices of
+// the two rows.  Item rows come from the owner shard (a peer GPU's HBM through NVLink when the
+// pointer is a peer mapping), the item delta goes back as 16-byte red.add.
+#include "common.cuh"
+#include "flow.cuh"
+#include "mf_core.cuh"
+
+namespace {
+
+template <int LANES, int VPL, bool LAZY, int UNROLL>
+__global__ void __launch_bounds__(MF_THREADS)
+k_mf_sgd(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
+         const int* __restrict__ uid, const int* __restrict__ iid, const float* __restrict__ rating,
+         long long n, const FpsMfParams p, int chunk, FpsFlow* flow) {
+  constexpr int GPB = MF_THREADS / LANES;   // ratings in flight per block pass
+  const int grp = threadIdx.x / LANES;
+  MfCounters c;
+  c.clear();
+  for (long long base = (long long)blockIdx.x * chunk; base < n; base += (long long)gridDim.x * chunk) {
+    const int cnt = (int)min((long long)chunk, n - base);
+    if (p.pull_limit > 0) flow_acquire(flow, cnt, p.pull_limit);
+    for (int k0 = 0; k0 < cnt; k0 += GPB * UNROLL) {   // warp-uniform trip count (shuffles inside)
+      const int k = k0 + grp * UNROLL;
+      MfRec<VPL> rec[UNROLL];
+#pragma unroll
+      for (int q = 0; q < UNROLL; ++q)
+        mf_load<LANES, VPL, LAZY>(rec[q], items, users, uid, iid, rating, base + k + q, k + q < cnt, p.local_shard, c);
+#pragma unroll
+      for (int q = 0; q < UNROLL; ++q) mf_update<LANES, VPL, LAZY>(rec[q], items, p, c);
+    }
+    if (p.pull_limit > 0) flow_release(flow, cnt);
+  }
+  c.flush(flow);
+}
+
+template <int LANES, int VPL, bool LAZY>
+__global__ void __launch_bounds__(MF_THREADS)
+k_mf_predict(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
+             const int* __restrict__ uid, const int* __restrict__ iid, long long n, float* __restrict__ out) {
+  constexpr int GPB = MF_THREADS / LANES;
+  const int lane = threadIdx.x % LANES;
+  MfCounters c;
+  c.clear();
+  for (long long g0 = (long long)blockIdx.x * GPB; g0 < n; g0 += (long long)gridDim.x * GPB) {
+    const long long g = g0 + threadIdx.x / LANES;
+    MfRec<VPL> rec;
+    mf_load<LANES, VPL, LAZY>(rec, items, users, uid, iid, nullptr, g, g < n, -1, c, /*touch=*/false);
+    float dot = 0.f;
+#pragma unroll
+    for (int q = 0; q < VPL; ++q) dot += dot4(rec.u[q], rec.v[q]);
+    dot = group_sum<LANES>(dot);
+    if (lane == 0 && g < n) out[g] = rec.valid ? dot : __int_as_float(0x7fc00000);
+  }
+}
+
+// ---- N2: persistent streaming consumer ------------------------------------------------------
+// The host (or another stream) appends ratings to a ring and advances *tail.  CTAs claim chunks
+// with an atomic on flow->ring_head.  Nothing here waits on another kernel: if the producer
+// stops, every CTA leaves after iteration_wait_ms of idleness (device-side `iterate` timeout,
+// M/FlinkParameterServer.scala:49-52), on *stop, or at the hard lifetime cap.
+template <int LANES, int VPL, bool LAZY>
+__global__ void __launch_bounds__(MF_THREADS)
+k_mf_stream(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
+            const int* ring_u, const int* ring_i, const float* ring_r, unsigned long long capacity,
+            const volatile unsigned long long* tail, const volatile int* stop, const FpsMfParams p,
+            int chunk, unsigned long long wait_ns, unsigned long long life_ns, FpsFlow* flow) {
+  constexpr int GPB = MF_THREADS / LANES;
+  const int grp = threadIdx.x / LANES;
+  __shared__ unsigned long long s_base;
+  __shared__ int s_cnt;
+  MfCounters c;
+  c.clear();
+  const unsigned long long t_start = globaltimer_ns();
+  while (true) {
+    if (threadIdx.x == 0) {
+      int cnt = 0;
+      unsigned long long base = 0;
+      int reason = 0;
+      while (true) {
+        const unsigned long long now = globaltimer_ns();
+        const unsigned long long t = *tail;
+        unsigned long long h = *(volatile unsigned long long*)&flow->ring_head;
+        if (h < t) {
+          const unsigned long long want = min((unsigned long long)chunk, t - h);
+          const unsigned long long got = atomicCAS((unsigned long long*)&flow->ring_head, h, h + want);
+          if (got == h) {
+            base = h;
+            cnt = (int)want;
+            *(volatile unsigned long long*)&flow->last_activity_ns = now;
+            break;
+          }
+          continue;   // lost the race, retry immediately
+        }
+        if (*stop != 0) { reason = 2; break; }
+        if (now - t_start > life_ns) { reason = 3; break; }
+        if (wait_ns != 0) {
+          const unsigned long long last = *(volatile unsigned long long*)&flow->last_activity_ns;
+          const unsigned long long ref = last > t_start ? last : t_start;
+          // idle only counts once everything claimed has retired
+          if (now > ref && now - ref > wait_ns &&
+              *(volatile unsigned long long*)&flow->ring_done == h) { reason = 1; break; }
+        }
+        __nanosleep(2000);
+      }
+      s_base = base;
+      s_cnt = reason ? -reason : cnt;
+    }
+    __syncthreads();
+    const int cnt = s_cnt;
+    const unsigned long long base = s_base;
+    __syncthreads();
+    if (cnt < 0) {
+      if (threadIdx.x == 0) atomicMax(&flow->exit_reason, -cnt);
+      break;
+    }
+    if (p.pull_limit > 0) flow_acquire(flow, cnt, p.pull_limit);
+    for (int k0 = 0; k0 < cnt; k0 += GPB) {
+      const int k = k0 + grp;
+      MfRec<VPL> rec;
+      const long long slot = (long long)((base + k) % capacity);
+      mf_load<LANES, VPL, LAZY>(rec, items, users, ring_u, ring_i, ring_r, slot, k < cnt, p.local_shard, c);
+      mf_update<LANES, VPL, LAZY>(rec, items, p, c);
+    }
+    if (p.pull_limit > 0) flow_release(flow, cnt);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      atomicAdd((unsigned long long*)&flow->ring_done, (unsigned long long)cnt);
+      *(volatile unsigned long long*)&flow->last_activity_ns = globaltimer_ns();
+    }
+  }
+  c.flush(flow);
+}
+
+struct Shape {
+  int lanes, vpl;
+};
+
+Shape shape_for(int stride) {
+  const int nvec = stride / 4;
+  Shape s{1, 1};
+  while (s.lanes < nvec && s.lanes < 32) s.lanes <<= 1;
+  s.vpl = (nvec + s.lanes - 1) / s.lanes;
+  return s;
+}
+
+int check_pair(const FpsTableView* items, const FpsTableView* users, const char* who) {
+  if (int e = fps_check_view(items, who)) return e;
+  if (int e = fps_check_view(users, who)) return e;
+  FPS_REQUIRE(items->stride == users->stride && items->dim == users->dim, FPS_E_INVALID,
+              "%s: item and user tables must have the same dim/stride", who);
+  FPS_REQUIRE(items->stride <= 1024, FPS_E_UNSUPPORTED, "%s: rank above 1024 not supported", who);
+  return 0;
+}
+
+}  // namespace
+
+#define MF_DISPATCH(FN)                                                                      \
+  do {                                                                                       \
+    const Shape s = shape_for(items->stride);                                                \
+    const bool lazy = items->lazy || users->lazy;                                            \
+    if (s.vpl == 1) {                                                                        \
+      switch (s.lanes) {                                                                     \
+        case 1: FN(1, 1, lazy); break;                                                       \
+        case 2: FN(2, 1, lazy); break;                                                       \
+        case 4: FN(4, 1, lazy); break;                                                       \
+        case 8: FN(8, 1, lazy); break;                                                       \
+        case 16: FN(16, 1, lazy); break;                                                     \
+        default: FN(32, 1, lazy); break;                                                     \
+      }                                                                                      \
+    } else if (s.vpl == 2) { FN(32, 2, lazy); }                                              \
+    else if (s.vpl <= 4) { FN(32, 4, lazy); }                                                \
+    else { FN(32, 8, lazy); }                                                                \
+  } while (0)
+
+extern "C" {
+
+int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const int32_t* d_user_ids,
+                    const int32_t* d_item_ids, const float* d_ratings, int64_t n,
+                    const FpsMfParams* params, FpsFlow* d_flow, void* stream) {
+  if (int e = check_pair(items, users, "fps_mf_sgd_step")) return e;
+  FPS_REQUIRE(params != nullptr && d_flow != nullptr, FPS_E_INVALID, "fps_mf_sgd_step: params and flow are required");
+  if (n <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (params->variant == 1) {
+    return fps_mf_sgd_staged(items, users, d_user_ids, d_item_ids, d_ratings, n, params, d_flow, st);
+  }
+  if (params->variant == 2) {
+    return fps_mf_sgd_combine(items, users, d_user_ids, d_item_ids, d_ratings, n, params, d_flow, st);
+  }
+  int chunk = MF_CHUNK;
+  if (params->pull_limit > 0 && params->pull_limit < chunk) chunk = params->pull_limit;
+  long long blocks = (n + chunk - 1) / chunk;
+  const long long cap = (long long)fps_num_sms() * MF_BLOCKS_PER_SM;
+  if (blocks > cap) blocks = cap;
+#define FN(L, V, Z)                                                                                   \
+  if (Z) k_mf_sgd<L, V, true, 1><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow); \
+  else k_mf_sgd<L, V, false, (V <= 2 ? 2 : 1)><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow)
+  MF_DISPATCH(FN);
+#undef FN
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int fps_mf_predict(const FpsTableView* items, const FpsTableView* users, const int32_t* d_user_ids,
+                   const int32_t* d_item_ids, int64_t n, float* d_out, void* stream) {
+  if (int e = check_pair(items, users, "fps_mf_predict")) return e;
+  if (n <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const Shape sh = shape_for(items->stride);
+  const int gpb = MF_THREADS / sh.lanes;
+  long long blocks = (n + gpb - 1) / gpb;
+  const long long cap = (long long)fps_num_sms() * MF_BLOCKS_PER_SM;
+  if (blocks > cap) blocks = cap;
+#define FN(L, V, Z)                                                                                   \
+  if (Z) k_mf_predict<L, V, true><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, n, d_out); \
+  else k_mf_predict<L, V, false><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, n, d_out)
+  MF_DISPATCH(FN);
+#undef FN
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int fps_mf_online_stream(const FpsTableView* items, const FpsTableView* users, const int32_t* ring_users,
+                         const int32_t* ring_items, const float* ring_ratings, uint64_t ring_capacity,
+                         const volatile uint64_t* tail, const volatile int32_t* stop,
+                         const FpsMfParams* params, uint32_t iteration_wait_ms, uint32_t max_lifetime_ms,
+                         FpsFlow* d_flow, void* stream) {
+  if (int e = check_pair(items, users, "fps_mf_online_stream")) return e;
+  FPS_REQUIRE(params && d_flow && tail && stop && ring_capacity > 0, FPS_E_INVALID, "fps_mf_online_stream: bad arguments");
+  FPS_REQUIRE(max_lifetime_ms > 0 && max_lifetime_ms <= 600000u, FPS_E_INVALID,
+              "fps_mf_online_stream: max_lifetime_ms must be in (0, 600000]");
+  cudaStream_t st = (cudaStream_t)stream;
+  int chunk = 64;
+  if (params->pull_limit > 0 && params->pull_limit < chunk) chunk = params->pull_limit;
+  // one resident wave only: every CTA of a polling kernel must be co-resident
+  const int blocks = fps_num_sms() * 2;
+  const unsigned long long wait_ns = (unsigned long long)iteration_wait_ms * 1000000ull;
+  const unsigned long long life_ns = (unsigned long long)max_lifetime_ms * 1000000ull;
+#define FN(L, V, Z)                                                                                   \
+  if (Z) k_mf_stream<L, V, true><<<blocks, MF_THREADS, 0, st>>>(*items, *users, ring_users, ring_items, ring_ratings, ring_capacity, (const volatile unsigned long long*)tail, stop, *params, chunk, wait_ns, life_ns, d_flow); \
+  else k_mf_stream<L, V, false><<<blocks, MF_THREADS, 0, st>>>(*items, *users, ring_users, ring_items, ring_ratings, ring_capacity, (const volatile unsigned long long*)tail, stop, *params, chunk, wait_ns, life_ns, d_flow)
+  MF_DISPATCH(FN);
+#undef FN
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,276 @@
+// Sharded parameter table: eager init (N9), gather = pull without compute, scatter = push /
+// model load (N10), compaction dump (N11).  See include/fps_b200.h for the contracts.
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ long long slot_to_id(const FpsTableView& t, int shard, long long slot) {
+  return t.partition == FPS_PART_HASH ? slot * t.n_shards + shard : (long long)shard * t.div + slot;
+}
+
+__global__ void __launch_bounds__(256)
+k_init_shard(const __grid_constant__ FpsTableView t, int shard, long long n_rows) {
+  const int vec_per_row = t.stride / 4;
+  const long long total = n_rows * vec_per_row;
+  float* base = t.rows[shard];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long slot = i / vec_per_row;
+    const int blk = (int)(i - slot * vec_per_row);
+    const float4 v = init_block(t, slot_to_id(t, shard, slot), blk);
+    *reinterpret_cast<float4*>(base + slot * t.stride + blk * 4) = v;
+  }
+}
+
+// value of float4 `blk` of a row, honouring the lazy life-cycle
+__device__ __forceinline__ float4 row_value4(const FpsTableView& t, const float* row, long long id,
+                                             int blk, int state) {
+  float4 v = ld_row4(row + blk * 4);
+  if (state == FPS_ROW_PULLED) {
+    const float4 b = init_block(t, id, blk);
+    v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+  }
+  return v;
+}
+
+template <int LANES>
+__global__ void __launch_bounds__(256)
+k_gather(const __grid_constant__ FpsTableView t, const long long* __restrict__ ids, long long n,
+         float* __restrict__ out, int out_stride, FpsFlow* flow, int local_shard) {
+  const int lane = threadIdx.x % LANES;
+  const long long groups = (long long)gridDim.x * (blockDim.x / LANES);
+  const int nvec = t.stride / 4;
+  unsigned long long bad = 0, remote = 0, done = 0;
+  for (long long g = (long long)blockIdx.x * (blockDim.x / LANES) + threadIdx.x / LANES; g < n; g += groups) {
+    const long long id = ids[g];
+    const RowRef r = locate(t, id);
+    if (!in_table(t, id, r)) {
+      if (lane == 0) ++bad;
+      continue;
+    }
+    int state = FPS_ROW_PUSHED;
+    if (t.lazy) state = touch_state(t.state[r.owner], r.slot, FPS_ROW_PULLED);
+    const float* row = t.rows[r.owner] + r.slot * t.stride;
+    for (int b = lane; b < nvec; b += LANES) {
+      const float4 v = row_value4(t, row, id, b, state);
+      float* o = out + g * out_stride + b * 4;
+      const int j = b * 4;
+      if (j + 0 < out_stride) o[0] = v.x;
+      if (j + 1 < out_stride) o[1] = v.y;
+      if (j + 2 < out_stride) o[2] = v.z;
+      if (j + 3 < out_stride) o[3] = v.w;
+    }
+    if (lane == 0) {
+      ++done;
+      if (r.owner != local_shard) ++remote;
+    }
+  }
+  if (flow != nullptr && lane == 0) {
+    if (bad) atomicAdd((unsigned long long*)&flow->bad_ids, bad);
+    if (done) atomicAdd((unsigned long long*)&flow->pulls, done);
+    if (remote) atomicAdd((unsigned long long*)&flow->remote_pulls, remote);
+  }
+}
+
+template <int LANES>
+__global__ void __launch_bounds__(256)
+k_scatter(const __grid_constant__ FpsTableView t, const long long* __restrict__ ids, long long n,
+          const float* __restrict__ vals, int val_stride, int mode, FpsFlow* flow, int local_shard) {
+  const int lane = threadIdx.x % LANES;
+  const long long groups = (long long)gridDim.x * (blockDim.x / LANES);
+  const int nvec = t.stride / 4;
+  unsigned long long bad = 0, remote = 0, done = 0;
+  // warp-uniform trip count: mode 2 shuffles inside the loop
+  for (long long g0 = (long long)blockIdx.x * (blockDim.x / LANES); g0 < n; g0 += groups) {
+    const long long g = g0 + threadIdx.x / LANES;
+    const long long id = g < n ? ids[g] : -1;
+    const RowRef r = locate(t, id < 0 ? 0 : id);
+    const bool ok = g < n && in_table(t, id, r);
+    if (g < n && !ok && lane == 0) ++bad;
+    int state = FPS_ROW_PUSHED;
+    if (ok && t.lazy) state = touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
+    float* row = ok ? t.rows[r.owner] + r.slot * t.stride : nullptr;
+    const float* src = vals + (ok ? g : 0) * val_stride;
+    float nrm = 0.f;
+    for (int b = lane; ok && b < nvec; b += LANES) {
+      const int j = b * 4;
+      float4 d;
+      d.x = (j + 0 < val_stride && j + 0 < t.dim) ? src[j + 0] : 0.f;
+      d.y = (j + 1 < val_stride && j + 1 < t.dim) ? src[j + 1] : 0.f;
+      d.z = (j + 2 < val_stride && j + 2 < t.dim) ? src[j + 2] : 0.f;
+      d.w = (j + 3 < val_stride && j + 3 < t.dim) ? src[j + 3] : 0.f;
+      if (mode == 1) {
+        // overwrite: stored := value - base so that base + stored == value
+        if (state == FPS_ROW_PULLED) {
+          const float4 bse = init_block(t, id, b);
+          d.x -= bse.x; d.y -= bse.y; d.z -= bse.z; d.w -= bse.w;
+        }
+        if (t.stride > t.dim) {   // keep aux columns (e.g. the length column) untouched here
+          const float4 old = ld_row4(row + j);
+          if (j + 0 >= t.dim) d.x = old.x;
+          if (j + 1 >= t.dim) d.y = old.y;
+          if (j + 2 >= t.dim) d.z = old.z;
+          if (j + 3 >= t.dim) d.w = old.w;
+        }
+        st_row4(row + j, d);
+      } else {
+        red_add4(row + j, d);
+      }
+    }
+    if (mode == 2 && t.stride > t.dim) {
+      // add-then-renormalise: the aux column `dim` carries ||row|| (attachLength semantics,
+      // PSOnlineMatrixFactorizationAndTopKGenerator.scala:81-84).  Exact when pushes to one row
+      // do not overlap; otherwise it reflects one of the interleavings, like any stale read here.
+      __threadfence_system();
+      for (int b = lane; ok && b < nvec; b += LANES) {
+        const float4 v = row_value4(t, row, id, b, state);
+        const int j = b * 4;
+        if (j + 0 < t.dim) nrm = fmaf(v.x, v.x, nrm);
+        if (j + 1 < t.dim) nrm = fmaf(v.y, v.y, nrm);
+        if (j + 2 < t.dim) nrm = fmaf(v.z, v.z, nrm);
+        if (j + 3 < t.dim) nrm = fmaf(v.w, v.w, nrm);
+      }
+      nrm = group_sum<LANES>(nrm);
+      if (ok && lane == 0) {
+        const float len = sqrtf(nrm);   // aux columns are never part of init()
+        asm volatile("st.global.cg.f32 [%0], %1;" ::"l"(row + t.dim), "f"(len) : "memory");
+      }
+    }
+    if (ok && lane == 0) {
+      ++done;
+      if (r.owner != local_shard) ++remote;
+    }
+  }
+  if (flow != nullptr && lane == 0) {
+    if (bad) atomicAdd((unsigned long long*)&flow->bad_ids, bad);
+    if (done) atomicAdd((unsigned long long*)&flow->pushes, done);
+    if (remote) atomicAdd((unsigned long long*)&flow->remote_pushes, remote);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_dump_shard(const __grid_constant__ FpsTableView t, int shard, long long n_rows, long long n_ids_total,
+             long long* __restrict__ out_ids, float* __restrict__ out_rows, long long capacity,
+             unsigned long long* count) {
+  // one warp per row: lane 0 claims an output slot (warp-aggregated per block would save little:
+  // the dump runs once per job)
+  const int lane = threadIdx.x & 31;
+  const long long warps = (long long)gridDim.x * (blockDim.x / 32);
+  const int nvec = t.stride / 4;
+  const float* base = t.rows[shard];
+  for (long long slot = (long long)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32; slot < n_rows; slot += warps) {
+    const long long id = slot_to_id(t, shard, slot);
+    if (id >= n_ids_total) continue;
+    int state = FPS_ROW_PUSHED;
+    if (t.lazy) {
+      state = t.state[shard][slot];
+      if (state == FPS_ROW_UNTOUCHED) continue;
+    }
+    unsigned long long idx = 0;
+    if (lane == 0) idx = atomicAdd(count, 1ull);
+    idx = __shfl_sync(0xffffffffu, idx, 0);
+    if ((long long)idx >= capacity) continue;
+    if (lane == 0) out_ids[idx] = id;
+    const float* row = base + slot * t.stride;
+    for (int b = lane; b < nvec; b += 32) {
+      const float4 v = row_value4(t, row, id, b, state);
+      *reinterpret_cast<float4*>(out_rows + idx * t.stride + b * 4) = v;
+    }
+  }
+}
+
+int lanes_for(int stride) {
+  const int nvec = stride / 4;
+  int l = 1;
+  while (l < nvec && l < 32) l <<= 1;
+  return l;
+}
+
+int check_view(const FpsTableView* v, const char* who) {
+  FPS_REQUIRE(v != nullptr, FPS_E_INVALID, "%s: null table view", who);
+  FPS_REQUIRE(v->n_shards >= 1 && v->n_shards <= FPS_MAX_SHARDS, FPS_E_INVALID, "%s: n_shards %d out of range", who, v->n_shards);
+  FPS_REQUIRE(v->stride % 4 == 0 && v->stride >= v->dim && v->dim >= 1, FPS_E_INVALID,
+              "%s: stride %d must be a multiple of 4 and >= dim %d", who, v->stride, v->dim);
+  FPS_REQUIRE(v->partition == FPS_PART_HASH || v->div > 0, FPS_E_INVALID, "%s: range partition needs div > 0", who);
+  return 0;
+}
+
+}  // namespace
+
+int fps_check_view(const FpsTableView* v, const char* who) { return check_view(v, who); }
+
+extern "C" {
+
+int fps_table_init_shard(const FpsTableView* view, int shard, int64_t n_rows, void* stream) {
+  if (int e = check_view(view, "fps_table_init_shard")) return e;
+  FPS_REQUIRE(shard >= 0 && shard < view->n_shards && view->rows[shard] != nullptr, FPS_E_INVALID,
+              "fps_table_init_shard: shard %d not mapped", shard);
+  if (n_rows <= 0) return 0;
+  const long long total = (long long)n_rows * (view->stride / 4);
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)fps_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  k_init_shard<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(*view, shard, n_rows);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+#define FPS_DISPATCH_LANES(lanes, KERNEL, ...)                        \
+  switch (lanes) {                                                    \
+    case 1: KERNEL<1> __VA_ARGS__; break;                             \
+    case 2: KERNEL<2> __VA_ARGS__; break;                             \
+    case 4: KERNEL<4> __VA_ARGS__; break;                             \
+    case 8: KERNEL<8> __VA_ARGS__; break;                             \
+    case 16: KERNEL<16> __VA_ARGS__; break;                           \
+    default: KERNEL<32> __VA_ARGS__; break;                           \
+  }
+
+int fps_table_gather(const FpsTableView* view, const int64_t* d_ids, int64_t n, float* d_out,
+                     int out_stride, FpsFlow* d_flow, void* stream) {
+  if (int e = check_view(view, "fps_table_gather")) return e;
+  if (n <= 0) return 0;
+  const int lanes = lanes_for(view->stride);
+  const int gpb = 256 / lanes;
+  long long blocks = (n + gpb - 1) / gpb;
+  const long long cap = (long long)fps_num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t st = (cudaStream_t)stream;
+  FPS_DISPATCH_LANES(lanes, k_gather, <<<(int)blocks, 256, 0, st>>>(*view, (const long long*)d_ids, n, d_out, out_stride, d_flow, -1));
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int fps_table_scatter(const FpsTableView* view, const int64_t* d_ids, int64_t n, const float* d_vals,
+                      int val_stride, int mode, FpsFlow* d_flow, void* stream) {
+  if (int e = check_view(view, "fps_table_scatter")) return e;
+  FPS_REQUIRE(mode >= 0 && mode <= 2, FPS_E_INVALID, "fps_table_scatter: mode %d", mode);
+  if (n <= 0) return 0;
+  const int lanes = lanes_for(view->stride);
+  const int gpb = 256 / lanes;
+  long long blocks = (n + gpb - 1) / gpb;
+  const long long cap = (long long)fps_num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t st = (cudaStream_t)stream;
+  FPS_DISPATCH_LANES(lanes, k_scatter, <<<(int)blocks, 256, 0, st>>>(*view, (const long long*)d_ids, n, d_vals, val_stride, mode, d_flow, -1));
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int fps_table_dump_shard(const FpsTableView* view, int shard, int64_t n_rows, int64_t n_ids_total,
+                         int64_t* d_out_ids, float* d_out_rows, int64_t capacity, int64_t* d_count,
+                         void* stream) {
+  if (int e = check_view(view, "fps_table_dump_shard")) return e;
+  FPS_REQUIRE(shard >= 0 && shard < view->n_shards && view->rows[shard] != nullptr, FPS_E_INVALID,
+              "fps_table_dump_shard: shard %d not mapped", shard);
+  if (n_rows <= 0) return 0;
+  long long blocks = (n_rows + 7) / 8;
+  const long long cap = (long long)fps_num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  k_dump_shard<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
+      *view, shard, n_rows, n_ids_total, (long long*)d_out_ids, d_out_rows, capacity,
+      (unsigned long long*)d_count);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,256 @@
+"""Matrix factorisation on the device engine: HBM-sharded factor tables + the fused
+pull-compute-push kernel (``csrc/mf.cu``).
+
+Layout follows the reference's two-sided split (``PSOfflineMatrixFactorizationWorker.scala:43``):
+user vectors are *worker-resident* (rank ``user % W`` owns a user and receives its ratings, the
+input partitioning of ``PSOfflineMatrixFactorization.scala:71-74``), item vectors live on the
+*parameter server* shards (``item % S``).  Worker ``r`` and shard ``r`` share GPU ``r``.
+
+What one call to ``step`` replaces in the reference: for every rating one Pull message, one
+PullAnswer carrying the item row, the SGD step, one Push carrying the delta and one output
+record - here a P2P row load, registers, and a 16-byte-per-lane ``red.add``.
+
+Semantics kept: asynchronous / stale reads (Hogwild inside a launch, no barrier between
+ranks), ``param_update = add``, lazy ``param_init`` (optional), bounded in-flight pulls
+(``pull_limit`` -> device credit counter), output as ``Left((user, vec))`` / ``Right((item, vec))``.
+Output mode is "on close" (one record per live row, what every reference sink folds to).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Iterable, Optional
+
+import numpy as np
+
+from ...entities import Left, Right
+from ...ops import _native as N
+from ...ops import philox
+from ...ops.table import ShardedTable, new_flow, read_flow
+from .vector import FactorIsNotANumberException
+
+VARIANTS = {"direct": 0, "staged": 1, "combine": 2}
+
+
+class DeviceMF:
+    def __init__(self, n_users: int, n_items: int, num_factors: int = 10, range_min: float = -0.01,
+                 range_max: float = 0.01, learning_rate: float = 0.01, *, lambda_: float = 0.0,
+                 pull_limit: int = 0, seed: int = 0, lazy: bool = False, variant: str = "direct",
+                 ctx=None, n_shards: Optional[int] = None):
+        import torch
+        from ...parallel.device_context import get_context
+        self.ctx = ctx or get_context()
+        self.n_users, self.n_items, self.num_factors = n_users, n_items, num_factors
+        self.items = ShardedTable(n_items, num_factors, n_shards=n_shards, partition="hash",
+                                  init_range=(range_min, range_max), seed=seed,
+                                  stream_tag=philox.STREAM_ITEM, lazy=lazy, ctx=self.ctx)
+        self.users = ShardedTable(n_users, num_factors, n_shards=n_shards, partition="hash",
+                                  init_range=(range_min, range_max), seed=seed,
+                                  stream_tag=philox.STREAM_USER, lazy=lazy, ctx=self.ctx,
+                                  local_only=True)
+        self.params = N.FpsMfParams()
+        self.params.lr, self.params.lambda_ = learning_rate, lambda_
+        self.params.pull_limit = int(pull_limit)
+        self.params.local_shard = self.ctx.rank if self.ctx.distributed else -1
+        self.params.variant = VARIANTS[variant]
+        self.flow = new_flow()
+        self._copy_stream = None
+        self._staging = None
+        self.launches = 0
+
+    # -- training ------------------------------------------------------------------------------
+    def step(self, users, items, ratings) -> None:
+        """One fused pass over a batch already on the device (int32, int32, fp32).  With several
+        ranks every user id in the batch must satisfy ``user % world == rank``."""
+        n = users.numel()
+        N.check(N.lib().fps_mf_sgd_step(self.items.view_ref(), self.users.view_ref(), N.ptr(users),
+                                        N.ptr(items), N.ptr(ratings), n, C.byref(self.params),
+                                        N.ptr(self.flow), N.current_stream()), "fps_mf_sgd_step")
+        self.launches += 1
+
+    def _ensure_staging(self, n: int):
+        import torch
+        if self._staging is None or self._staging[0]["u"].numel() < n:
+            self._staging = [
+                {"u": torch.empty(n, device="cuda", dtype=torch.int32),
+                 "i": torch.empty(n, device="cuda", dtype=torch.int32),
+                 "r": torch.empty(n, device="cuda", dtype=torch.float32),
+                 "copied": torch.cuda.Event(), "done": torch.cuda.Event(), "used": False,
+                 "loss": torch.zeros(2, dtype=torch.float64).pin_memory()}
+                for _ in range(2)]
+            self._copy_stream = torch.cuda.Stream()
+            self._slot = 0
+            self._last_mse = float("nan")
+        return self._staging
+
+    def _read_loss(self, st) -> float:
+        import torch
+        loss_sum = float(st["loss"][0])
+        records = int(st["loss"][1:2].view(torch.int64)[0])
+        return loss_sum / max(records, 1)
+
+    def step_from_host(self, users_h, items_h, ratings_h) -> float:
+        """End-to-end step through the public API.  Every call (a) copies this step's pinned
+        host inputs to the device on a copy stream, (b) runs the fused kernel, (c) copies the
+        running loss (16 bytes of the flow block) back to pinned host memory.  Two staging slots
+        pipeline it: the call only blocks on the step that used this slot two calls ago, so the
+        H2D copy of step k+1 overlaps the kernel of step k.  Returns the mean squared error as of
+        the most recent *retired* step (``flush_host_steps()`` returns the final one)."""
+        import torch
+        n = users_h.numel()
+        stg = self._ensure_staging(n)
+        st = stg[self._slot]
+        self._slot ^= 1
+        if st["used"]:
+            st["done"].synchronize()                 # host waits for step k-2 only
+            self._last_mse = self._read_loss(st)
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(self._copy_stream):
+            st["u"][:n].copy_(users_h, non_blocking=True)
+            st["i"][:n].copy_(items_h, non_blocking=True)
+            st["r"][:n].copy_(ratings_h, non_blocking=True)
+            st["copied"].record(self._copy_stream)
+        main.wait_event(st["copied"])
+        self.step(st["u"][:n], st["i"][:n], st["r"][:n])
+        view = self.flow[N.FLOW_LOSS_OFFSET:N.FLOW_LOSS_OFFSET + 16].view(torch.float64)
+        st["loss"].copy_(view, non_blocking=True)
+        st["done"].record(main)
+        st["used"] = True
+        return self._last_mse
+
+    def flush_host_steps(self) -> float:
+        import torch
+        torch.cuda.current_stream().synchronize()
+        if self._staging:
+            last = self._staging[self._slot ^ 1]
+            if last["used"]:
+                self._last_mse = self._read_loss(last)
+        return self._last_mse
+
+    H2D_BYTES_PER_RATING = 12
+    D2H_BYTES_PER_STEP = 16
+
+    # -- evaluation / output ---------------------------------------------------------------------
+    def predict(self, users, items):
+        import torch
+        out = torch.empty(users.numel(), device="cuda", dtype=torch.float32)
+        N.check(N.lib().fps_mf_predict(self.items.view_ref(), self.users.view_ref(), N.ptr(users),
+                                       N.ptr(items), users.numel(), N.ptr(out), N.current_stream()),
+                "fps_mf_predict")
+        return out
+
+    def rmse(self, users, items, ratings) -> float:
+        import torch
+        p = self.predict(users, items)
+        return float(torch.sqrt(torch.mean((p - ratings) ** 2)))
+
+    def stats(self, check_nan: bool = True) -> dict:
+        s = read_flow(self.flow)
+        if check_nan and s["nan_count"]:
+            raise FactorIsNotANumberException(f"{s['nan_count']} ratings produced a non-finite error")
+        return s
+
+    def reset_stats(self) -> None:
+        self.flow.zero_()
+
+    def dump(self) -> list:
+        """The job's output stream in on-close mode: ``Left((user, vec))`` for every live local
+        user row and ``Right((item, vec))`` for every live row of the local item shard."""
+        out = []
+        uid, urows = self.users.dump()
+        for k, v in zip(uid.tolist(), urows.cpu().numpy().astype(np.float64)):
+            out.append(Left((k, v)))
+        iid, irows = self.items.dump()
+        for k, v in zip(iid.tolist(), irows.cpu().numpy().astype(np.float64)):
+            out.append(Right((k, v)))
+        return out
+
+    def load(self, model: Iterable) -> None:
+        """Warm start from a previous output stream (``transform_with_double_model_load``):
+        ``Left((user, vec))`` -> user table, ``Right((item, vec))`` -> item table.  Rows owned by
+        another rank are skipped for the worker-resident half."""
+        import torch
+        us, uv, its, iv = [], [], [], []
+        for e in model:
+            k, v = e.value
+            (us if e.is_left else its).append(k)
+            (uv if e.is_left else iv).append(np.asarray(v, dtype=np.float32))
+        W = self.ctx.world_size
+        if us:
+            ids = torch.tensor(us, dtype=torch.int64)
+            vals = torch.from_numpy(np.stack(uv))
+            if W > 1:
+                keep = (ids % W) == self.ctx.rank
+                ids, vals = ids[keep], vals[keep]
+            if ids.numel():
+                self.users.load(ids, vals)
+        if its:
+            self.items.load(torch.tensor(its, dtype=torch.int64), torch.from_numpy(np.stack(iv)))
+        torch.cuda.synchronize()
+        self.ctx.barrier()
+
+
+def _ratings_to_tensors(ratings, rank: int, world: int):
+    import torch
+    u = np.fromiter((r.user for r in ratings), dtype=np.int32)
+    i = np.fromiter((r.item for r in ratings), dtype=np.int32)
+    v = np.fromiter((r.rating for r in ratings), dtype=np.float32)
+    if world > 1:
+        keep = (u % world) == rank        # input partitioning by user (X4)
+        u, i, v = u[keep], i[keep], v[keep]
+    return (torch.from_numpy(u).cuda(), torch.from_numpy(i).cuda(), torch.from_numpy(v).cuda())
+
+
+def ps_offline_mf_device(src, num_factors: int = 10, range_min: float = -0.01, range_max: float = 0.01,
+                         learning_rate: float = 0.01, iterations: int = 1, pull_limit: int = 1600,
+                         *, n_users: Optional[int] = None, n_items: Optional[int] = None, seed: int = 0,
+                         shuffle: bool = True, lambda_: float = 0.0, lazy: bool = True,
+                         conflict_free: bool = False, n_shards: Optional[int] = None,
+                         variant: str = "direct", return_model: bool = False):
+    """Device twin of ``ps_offline_mf`` (same arguments where they apply): multi-epoch SGD MF,
+    returns the ``Left((user, vec))`` / ``Right((item, vec))`` stream.
+
+    ``conflict_free=True`` splits every epoch into waves in which no user and no item repeats,
+    which makes the asynchronous result equal to a serial schedule (used to check the kernel
+    against the fp64 oracle); the default is one Hogwild launch per epoch."""
+    import torch
+    from ...parallel.device_context import get_context
+    ctx = get_context()
+    ratings = list(src)
+    n_users = n_users or (max(r.user for r in ratings) + 1)
+    n_items = n_items or (max(r.item for r in ratings) + 1)
+    mf = DeviceMF(n_users, n_items, num_factors, range_min, range_max, learning_rate, lambda_=lambda_,
+                  pull_limit=pull_limit, seed=seed, lazy=lazy, variant=variant, ctx=ctx, n_shards=n_shards)
+    u, i, v = _ratings_to_tensors(ratings, ctx.rank, ctx.world_size)
+    gen = torch.Generator(device="cpu").manual_seed(seed)
+    for _ in range(iterations):
+        if shuffle and u.numel():
+            perm = torch.randperm(u.numel(), generator=gen).cuda()
+            u, i, v = u[perm], i[perm], v[perm]
+        if conflict_free:
+            for wu, wi, wv in conflict_free_waves(u, i, v):
+                mf.step(wu, wi, wv)
+        else:
+            mf.step(u, i, v)
+    torch.cuda.synchronize()
+    ctx.barrier()
+    mf.stats()
+    out = mf.dump()
+    return (out, mf) if return_model else out
+
+
+def conflict_free_waves(u, i, v):
+    """Greedy split of a batch into waves with pairwise distinct users and items, preserving the
+    batch order across waves (wave k holds, for every record, the k-th occurrence rank)."""
+    import torch
+    uu, ii = u.cpu().numpy(), i.cpu().numpy()
+    wave_of = np.zeros(len(uu), dtype=np.int64)
+    next_u, next_i = {}, {}
+    for k in range(len(uu)):
+        w = max(next_u.get(int(uu[k]), 0), next_i.get(int(ii[k]), 0))
+        wave_of[k] = w
+        next_u[int(uu[k])] = w + 1
+        next_i[int(ii[k])] = w + 1
+    for w in range(int(wave_of.max()) + 1 if len(uu) else 0):
+        idx = torch.from_numpy(np.nonzero(wave_of == w)[0]).cuda()
+        yield u[idx], i[idx], v[idx]

@@ -1,0 +1,196 @@
+"""HBM-resident sharded parameter table (the device replacement of the PS shards' hash maps).
+
+Parity: the store inside ``M/server/SimplePSLogic.scala:7-26`` / ``RangePSLogicWithClose.scala:7-63``
+and the two partitioners (hash ``M/FlinkParameterServer.scala:126-134``; range
+``M/passive/aggressive/PassiveAggressiveParameterServer.scala:372-384``), laid out for HBM:
+
+  * shard ``s`` is one contiguous ``[rows_per_shard, stride]`` fp32 array (stride = dim rounded up
+    to 4 floats, optionally + aux columns such as the vector length);
+  * ids map to (owner, slot) with the reference's formulas, evaluated on the device;
+  * ``lazy=True`` keeps the reference's life-cycle (untouched / first-pulled / first-pushed) in
+    one state byte per row; ``lazy=False`` materialises ``init(id)`` eagerly (the benchmark mode);
+  * with ``world_size > 1`` shard ``r`` lives on rank ``r`` and every rank maps all shards
+    through CUDA IPC, so kernels dereference peer rows directly over NVLink.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import List, Optional, Tuple
+
+from . import _native as N
+from . import philox
+
+
+def padded_stride(dim: int, aux_cols: int = 0) -> int:
+    return ((dim + aux_cols + 3) // 4) * 4
+
+
+class ShardedTable:
+    def __init__(self, n_ids: int, dim: int, *, n_shards: Optional[int] = None, partition: str = "hash",
+                 init_range: Tuple[float, float] = (0.0, 0.0), seed: int = 0,
+                 stream_tag: int = philox.STREAM_ITEM, lazy: bool = False, aux_cols: int = 0,
+                 ctx=None, local_only: bool = False):
+        """``local_only`` = a worker-resident table (MF user factors): sharded by the same formula
+        but a rank only ever touches its own shard, so no peer mapping is made."""
+        import torch
+        from ..parallel.device_context import get_context
+        self.ctx = ctx or get_context()
+        world = self.ctx.world_size
+        self.n_ids, self.dim = int(n_ids), int(dim)
+        self.stride = padded_stride(dim, aux_cols)
+        self.aux_cols = aux_cols
+        self.n_shards = int(n_shards or world)
+        if world > 1 and self.n_shards != world:
+            raise ValueError("with several ranks the table has exactly one shard per rank")
+        if not 1 <= self.n_shards <= N.FPS_MAX_SHARDS:
+            raise ValueError(f"n_shards must be in [1, {N.FPS_MAX_SHARDS}]")
+        self.partition = {"hash": N.PART_HASH, "range": N.PART_RANGE}[partition]
+        self.div = int(math.ceil(self.n_ids / self.n_shards))
+        self.rows_per_shard = max(self.div, 1)
+        self.init_range = (float(init_range[0]), float(init_range[1]))
+        self.seed, self.stream_tag, self.lazy = int(seed), int(stream_tag), bool(lazy)
+        self.local_only = local_only
+        self.local_shards = [self.ctx.rank] if world > 1 else list(range(self.n_shards))
+
+        self._bufs: dict = {}
+        self._state_bufs: dict = {}
+        self._peer_ptrs: List[int] = []
+        self.rows: dict = {}
+        self.state: dict = {}
+        for s in self.local_shards:
+            b = N.DeviceBuffer(self.rows_per_shard * self.stride * 4)
+            self._bufs[s] = b
+            self.rows[s] = b.tensor((self.rows_per_shard, self.stride), "<f4")
+            if self.lazy:
+                sb = N.DeviceBuffer(((self.rows_per_shard + 3) // 4) * 4)
+                self._state_bufs[s] = sb
+                self.state[s] = sb.tensor((((self.rows_per_shard + 3) // 4) * 4,), "|u1")
+        self._view = N.FpsTableView()
+        v = self._view
+        v.n_shards, v.dim, v.stride, v.partition = self.n_shards, self.dim, self.stride, self.partition
+        v.div, v.rows_per_shard = self.div, self.rows_per_shard
+        v.init_lo, v.init_hi = self.init_range
+        v.seed, v.stream_tag, v.lazy = self.seed, self.stream_tag, int(self.lazy)
+        for s in self.local_shards:
+            v.rows[s] = self._bufs[s].ptr
+            v.state[s] = self._state_bufs[s].ptr if self.lazy else None
+        if world > 1 and not local_only:
+            self._map_peers()
+        if self.lazy:
+            for s in self.local_shards:
+                self.rows[s].zero_()
+                self.state[s].zero_()
+        else:
+            self.init_eager()
+        torch.cuda.synchronize()
+        self.ctx.barrier()
+
+    # -- peer mapping ------------------------------------------------------------------------
+    def _map_peers(self) -> None:
+        me = self.ctx.rank
+        mine = (self._bufs[me].ipc_handle(), self._state_bufs[me].ipc_handle() if self.lazy else None)
+        handles = self.ctx.all_gather_object(mine)
+        for r, (hrows, hstate) in enumerate(handles):
+            if r == me:
+                continue
+            p = N.open_ipc(hrows)
+            self._peer_ptrs.append(p)
+            self._view.rows[r] = p
+            if hstate is not None:
+                ps = N.open_ipc(hstate)
+                self._peer_ptrs.append(ps)
+                self._view.state[r] = ps
+
+    # -- basic ops -----------------------------------------------------------------------------
+    def view(self) -> N.FpsTableView:
+        return self._view
+
+    def view_ref(self):
+        return C.byref(self._view)
+
+    def init_eager(self) -> None:
+        for s in self.local_shards:
+            N.check(N.lib().fps_table_init_shard(C.byref(self._view), s, self.rows_per_shard,
+                                                 N.current_stream()), "fps_table_init_shard")
+
+    def owner_of(self, ids):
+        """Vectorised torch twin of the device ``locate`` (tests / host routing)."""
+        if self.partition == N.PART_HASH:
+            return ids % self.n_shards, ids // self.n_shards
+        owner = ids // self.div
+        return owner, ids - owner * self.div
+
+    def gather(self, ids, flow=None):
+        """Pull without compute: ``[len(ids), dim]`` values (remote rows come over NVLink)."""
+        import torch
+        ids = ids.to(device="cuda", dtype=torch.int64).contiguous()
+        out = torch.empty((ids.numel(), self.stride), device="cuda", dtype=torch.float32)
+        N.check(N.lib().fps_table_gather(C.byref(self._view), N.ptr(ids), ids.numel(), N.ptr(out),
+                                         self.stride, N.ptr(flow), N.current_stream()), "fps_table_gather")
+        return out[:, : self.dim + self.aux_cols]
+
+    def scatter(self, ids, vals, mode: str = "add", flow=None) -> None:
+        """Push: ``add`` (vectorSum), ``overwrite`` (model load / top-K users) or ``add_norm``
+        (add, then refresh the length column)."""
+        import torch
+        ids = ids.to(device="cuda", dtype=torch.int64).contiguous()
+        vals = vals.to(device="cuda", dtype=torch.float32).contiguous()
+        if vals.dim() == 1:
+            vals = vals[:, None]
+        m = {"add": 0, "overwrite": 1, "add_norm": 2}[mode]
+        N.check(N.lib().fps_table_scatter(C.byref(self._view), N.ptr(ids), ids.numel(), N.ptr(vals),
+                                          vals.shape[1], m, N.ptr(flow), N.current_stream()),
+                "fps_table_scatter")
+
+    def load(self, ids, vals) -> None:
+        """Model load (``transform_with_model_load``): store the given values; rows become
+        first-pushed, i.e. exactly the loaded value with no init added."""
+        self.scatter(ids, vals, "overwrite")
+
+    def dump(self):
+        """``(ids, rows[:, :dim+aux])`` of the live rows of the local shard(s), sorted by id -
+        the on-close model dump (``Right((id, value))`` records)."""
+        import torch
+        ids_out, rows_out = [], []
+        for s in self.local_shards:
+            cap = self.rows_per_shard
+            d_ids = torch.empty(cap, device="cuda", dtype=torch.int64)
+            d_rows = torch.empty((cap, self.stride), device="cuda", dtype=torch.float32)
+            cnt = torch.zeros(1, device="cuda", dtype=torch.int64)
+            N.check(N.lib().fps_table_dump_shard(C.byref(self._view), s, self.rows_per_shard, self.n_ids,
+                                                 N.ptr(d_ids), N.ptr(d_rows), cap, N.ptr(cnt),
+                                                 N.current_stream()), "fps_table_dump_shard")
+            k = int(cnt.item())
+            ids_out.append(d_ids[:k])
+            rows_out.append(d_rows[:k, : self.dim + self.aux_cols])
+        ids = torch.cat(ids_out)
+        rows = torch.cat(rows_out)
+        order = torch.argsort(ids)
+        return ids[order], rows[order]
+
+    def expected_init(self, ids):
+        """Host oracle of ``init(id)`` (numpy, fp32)."""
+        return philox.ranged_uniform(ids, self.dim, self.init_range[0], self.init_range[1], self.seed,
+                                     self.stream_tag)
+
+    def close(self) -> None:
+        for p in self._peer_ptrs:
+            try:
+                N.lib().fps_ipc_close_handle(p)
+            except Exception:
+                pass
+        self._peer_ptrs = []
+
+
+def new_flow():
+    """A zeroed device FpsFlow block (256 bytes) as a uint8 tensor."""
+    import torch
+    return torch.zeros(N.FLOW_BYTES, device="cuda", dtype=torch.uint8)
+
+
+def read_flow(flow) -> dict:
+    """Copy the flow block to the host and decode it."""
+    raw = bytes(flow.cpu().numpy().tobytes())
+    f = N.FpsFlow.from_buffer_copy(raw)
+    return {name: getattr(f, name) for name, _ in N.FpsFlow._fields_ if name != "reserved"}

@@ -1,0 +1,203 @@
+/* fps_b200 - C ABI of the B200-native parameter-server kernels (sm_100a).
+ *
+ * Every entry point returns 0 on success or a non-zero code (a cudaError_t value, or one of the
+ * FPS_E_* codes below); fps_last_error() returns a human-readable description of the last
+ * failure on the calling thread.  All pointers named d_* are device pointers.  `stream` is a
+ * cudaStream_t passed as void* (NULL = legacy default stream).  Nothing here synchronises the
+ * stream unless stated.
+ *
+ * "Reference" citations (file:line) point at the JVM code whose behaviour the entry point
+ * provides; M/ = src/main/scala/hu/sztaki/ilab/ps/ of flink-parameter-server.
+ */
+#ifndef FPS_B200_H
+#define FPS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FPS_MAX_SHARDS 16
+
+#define FPS_E_INVALID   10001   /* bad argument                                   */
+#define FPS_E_TOO_LARGE 10002   /* size beyond a documented fixed maximum          */
+#define FPS_E_UNSUPPORTED 10003 /* shape not supported by this build               */
+
+/* How parameter ids map to (owner shard, slot).  Same formulas as the reference:
+ *   HASH : owner = id % n_shards, slot = id / n_shards            (M/FlinkParameterServer.scala:126-134)
+ *   RANGE: owner = id / div,      slot = id - owner * div         (M/passive/aggressive/PassiveAggressiveParameterServer.scala:372-375,
+ *                                                                  M/server/RangePSLogicWithClose.scala:53-61)            */
+enum { FPS_PART_HASH = 0, FPS_PART_RANGE = 1 };
+
+/* Row life-cycle in lazy mode (state byte per row; SURVEY 2.9 "Parameter life-cycle"):
+ *   0 untouched; 1 first touch was a pull -> value = init(id) + stored; 2 first touch was a push
+ *   (or a model load) -> value = stored.  In eager mode `state` pointers are NULL and every row
+ *   already holds init(id).                                                                      */
+enum { FPS_ROW_UNTOUCHED = 0, FPS_ROW_PULLED = 1, FPS_ROW_PUSHED = 2 };
+
+/* A sharded fp32 table as seen from one GPU: rows[s] is shard s' base pointer mapped into this
+ * process (its own cudaMalloc for the local shard, a cudaIpc mapping for a peer's).            */
+typedef struct FpsTableView {
+  float*    rows[FPS_MAX_SHARDS];
+  uint8_t*  state[FPS_MAX_SHARDS];   /* NULL everywhere = eager table                            */
+  int32_t   n_shards;
+  int32_t   dim;                     /* logical row length                                       */
+  int32_t   stride;                  /* allocated row length in floats, multiple of 4            */
+  int32_t   partition;               /* FPS_PART_*                                               */
+  int64_t   div;                     /* RANGE divisor = ceil(n_ids / n_shards)                   */
+  int64_t   rows_per_shard;          /* capacity of every shard (bounds checks)                  */
+  float     init_lo, init_hi;        /* lazy init: value = lo + (hi-lo)*U(seed, stream, id, j)   */
+  uint64_t  seed;
+  int32_t   stream_tag;              /* Philox stream: 0 = PS-side table, 1 = worker-side table  */
+  int32_t   lazy;                    /* 1 = use the state bytes                                  */
+} FpsTableView;
+
+/* Device-side flow control + observability block (one per worker; 256 B, zero it before use).
+ * The pull limiter of M/WorkerLogic.scala:176-225 and the idle timeout of
+ * M/FlinkParameterServer.scala:49-52 live here, in device memory, not on the host.              */
+typedef struct FpsFlow {
+  int32_t   in_flight;               /* unanswered pulls right now                               */
+  int32_t   max_in_flight;           /* high-water mark (must stay <= pull_limit)                */
+  uint64_t  limiter_stalls;          /* times a CTA had to wait for credits                      */
+  uint64_t  pulls;                   /* rows pulled                                              */
+  uint64_t  pushes;                  /* rows pushed                                              */
+  uint64_t  remote_pulls;            /* of which from another shard than `local_shard`           */
+  uint64_t  remote_pushes;
+  uint64_t  nan_count;               /* non-finite factors seen (FactorIsNotANumberException)    */
+  uint64_t  bad_ids;                 /* ids outside the table                                    */
+  double    loss_sum;                /* sum of squared errors / hinge losses                     */
+  uint64_t  records;                 /* records processed                                        */
+  uint64_t  last_activity_ns;        /* globaltimer stamp of the last processed chunk            */
+  uint64_t  ring_head;               /* streaming kernel: next record index to claim             */
+  uint64_t  ring_done;               /* streaming kernel: records fully retired                  */
+  int32_t   exit_reason;             /* 1 idle timeout, 2 stop flag, 3 lifetime cap              */
+  int32_t   combined_groups;         /* hot-key groups pre-combined in shared memory             */
+  uint64_t  reserved[18];
+} FpsFlow;
+
+const char* fps_last_error(void);
+int fps_version(void);
+
+/* ---- runtime: memory, peer mapping, probes --------------------------------------------------- */
+int fps_malloc(void** d_ptr, size_t bytes);                  /* cudaMalloc (IPC-exportable)      */
+int fps_free(void* d_ptr);
+int fps_memset(void* d_ptr, int value, size_t bytes, void* stream);
+int fps_ipc_get_handle(void* d_ptr, unsigned char handle[64]);
+int fps_ipc_open_handle(const unsigned char handle[64], void** d_ptr);
+int fps_ipc_close_handle(void* d_ptr);
+int fps_enable_peer_access(int peer_device);                 /* single-process multi-GPU         */
+int fps_host_alloc_mapped(void** h_ptr, void** d_ptr, size_t bytes);  /* pinned + device alias   */
+int fps_host_free(void* h_ptr);
+/* P2P probe: moves `bytes` between local and (possibly peer-mapped) buffers with the three access
+ * types the PS uses; mode 0 = 128-bit loads from src, 1 = 128-bit stores to dst, 2 = red.add.v4.f32
+ * into dst.  Returns elapsed ms of `iters` launches via *ms.                                       */
+int fps_p2p_probe(float* d_dst, const float* d_src, size_t bytes, int mode, int iters, float* ms,
+                  void* stream);
+
+/* ---- table: init (N9), load (N10), dump (N11) ------------------------------------------------ */
+/* Fill local shard `shard` with init(id) for every slot (eager tables) - RangedRandomFactorInitializer
+ * (M/matrix/factorization/factors/RangedRandomFactorInitializer.scala:7-9), made counter-based.  */
+int fps_table_init_shard(const FpsTableView* view, int shard, int64_t n_rows, void* stream);
+/* Gather rows by id (pull without compute): out[i, :dim] = value(ids[i]).  ids may be remote.    */
+int fps_table_gather(const FpsTableView* view, const int64_t* d_ids, int64_t n, float* d_out,
+                     int out_stride, FpsFlow* d_flow, void* stream);
+/* Push rows: mode 0 = add (vectorSum), 1 = overwrite, 2 = add then store the new L2 norm in
+ * column `dim` (LengthAndVector tables, stride > dim).  value semantics of SimplePSLogic
+ * (M/server/SimplePSLogic.scala:16-25): an untouched row becomes exactly the pushed value.       */
+int fps_table_scatter(const FpsTableView* view, const int64_t* d_ids, int64_t n, const float* d_vals,
+                      int val_stride, int mode, FpsFlow* d_flow, void* stream);
+/* Dump the live rows of local shard `shard` (close() of the ...WithClose logics,
+ * M/server/SimplePSLogicWithClose.scala:29-31): compacts (id, row) pairs into d_out_ids /
+ * d_out_rows, count in *d_count (device int64, zero it first).  Eager tables dump every row.     */
+int fps_table_dump_shard(const FpsTableView* view, int shard, int64_t n_rows, int64_t n_ids_total,
+                         int64_t* d_out_ids, float* d_out_rows, int64_t capacity, int64_t* d_count,
+                         void* stream);
+
+/* ---- matrix factorisation (N1, N2) ----------------------------------------------------------- */
+typedef struct FpsMfParams {
+  float   lr;
+  float   lambda;          /* L2 regularisation, reference = 0                                    */
+  int32_t pull_limit;      /* 0 = unlimited; else max unanswered pulls per worker                 */
+  int32_t local_shard;     /* this worker's index (its user rows, and "remote" accounting)        */
+  int32_t variant;         /* 0 = direct (warp-per-rating, register path)
+                              1 = staged (TMA bulk copies of rows into shared memory + mbarrier)
+                              2 = direct + hot-key pre-combine in shared memory                   */
+  int32_t write_user_out;  /* reserved                                                            */
+} FpsMfParams;
+
+/* One fused pull-compute-push pass over n ratings: for each (user, item, r): v = pull(item) from
+ * its owner shard (P2P load if remote), u = local user row; e = r - u.v; u += lr*(e*v - lambda*u);
+ * push(item, lr*(e*u - lambda*v)) as a vector red.add on the owner.  SGDUpdater.scala:5-11 +
+ * PSOfflineMatrixFactorizationWorker.scala:131-146 + SimplePSLogic.scala:16-25 in one kernel.    */
+int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users,
+                    const int32_t* d_user_ids, const int32_t* d_item_ids, const float* d_ratings,
+                    int64_t n, const FpsMfParams* params, FpsFlow* d_flow, void* stream);
+
+/* Streaming worker (PSOnlineMatrixFactorizationWorker.scala:22-90 on device): a persistent kernel
+ * that consumes a ring of ratings written by the host, exits by itself after the ring has been
+ * idle for iteration_wait_ms (0 = until *stop != 0), never lives longer than max_lifetime_ms.
+ * ring_* are device-visible (mapped pinned or device memory); `tail` is advanced by the producer.*/
+int fps_mf_online_stream(const FpsTableView* items, const FpsTableView* users,
+                         const int32_t* ring_users, const int32_t* ring_items, const float* ring_ratings,
+                         uint64_t ring_capacity, const volatile uint64_t* tail,
+                         const volatile int32_t* stop, const FpsMfParams* params,
+                         uint32_t iteration_wait_ms, uint32_t max_lifetime_ms, FpsFlow* d_flow,
+                         void* stream);
+
+/* Predict r_hat = u.v for n (user, item) pairs (RMSE evaluation).                                */
+int fps_mf_predict(const FpsTableView* items, const FpsTableView* users, const int32_t* d_user_ids,
+                   const int32_t* d_item_ids, int64_t n, float* d_out, void* stream);
+
+/* ---- passive-aggressive (N3, N4, N5) --------------------------------------------------------- */
+typedef struct FpsPaParams {
+  int32_t variant;        /* 0 = PA, 1 = PA-I, 2 = PA-II  (PassiveAggressiveBinaryAlgorithm.scala:95-112) */
+  float   C;              /* aggressiveness                                                       */
+  int32_t multiclass;     /* 0 binary, 1 one-vs-all, 2 cost-based PB, 3 cost-based ML             */
+  int32_t n_classes;
+  int32_t pull_limit;     /* counted in features (rows), like the reference limiter               */
+  int32_t local_shard;
+  int32_t predict_only;   /* 1 = unlabelled: write predictions, push nothing                      */
+  int32_t reserved;
+} FpsPaParams;
+
+/* CSR mini-batch: example e has features d_indices[d_indptr[e] .. d_indptr[e+1]) with values
+ * d_values; label d_labels[e] (+1/-1 binary, class index multiclass).  Fused gather (pull of every
+ * active feature), margin / tau, and scatter red.add (push of tau*y*x_i).  d_pred (may be NULL)
+ * receives the prediction made with the pulled (pre-update) weights.
+ * PassiveAggressiveParameterServer.scala:283-338 + algorithm/*.scala.                            */
+int fps_pa_step(const FpsTableView* weights, const int64_t* d_indptr, const int32_t* d_indices,
+                const float* d_values, const int32_t* d_labels, int64_t n_examples,
+                const FpsPaParams* params, int32_t* d_pred, FpsFlow* d_flow, void* stream);
+
+/* ---- LEMP top-K (N6, N7) ---------------------------------------------------------------------- */
+/* Scores n_q queries against n_items local item rows on the tensor cores (tcgen05.mma kind::tf32,
+ * 3xTF32 split for fp32 fidelity, accumulators in TMEM), prunes tiles by the length bound
+ * ||q||*max||p|| <= theta (LEMP LENGTH test, PSTopKGeneratorWorker.scala:72-76) and keeps a
+ * per-query top-k.  Items must be sorted by length descending (d_item_len) for the bound to bite.
+ * Partial top-k lists per (query, item-split) go to caller-provided scratch, then are merged.
+ * Outputs: d_out_scores/d_out_ids [n_q, k] sorted descending, ids are d_item_ids[slot] or the
+ * slot itself when d_item_ids is NULL; unused entries have id -1.
+ * scratch_bytes must be >= fps_topk_scratch_bytes(n_q, k, n_items).                               */
+size_t fps_topk_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items);
+int fps_lemp_topk(const float* d_queries, int32_t q_stride, int64_t n_q,
+                  const float* d_items, int32_t item_stride, const float* d_item_len,
+                  const int32_t* d_item_ids, int64_t n_items, int32_t dim, int32_t k,
+                  int32_t use_pruning, void* d_scratch, size_t scratch_bytes,
+                  float* d_out_scores, int32_t* d_out_ids, uint64_t* d_stats, void* stream);
+/* CUDA-core fp32 reference scorer with the same interface (baseline + oracle on device).          */
+int fps_topk_simt(const float* d_queries, int32_t q_stride, int64_t n_q,
+                  const float* d_items, int32_t item_stride, const int32_t* d_item_ids,
+                  int64_t n_items, int32_t dim, int32_t k, void* d_scratch, size_t scratch_bytes,
+                  float* d_out_scores, int32_t* d_out_ids, void* stream);
+/* Merge n_parts partial top-k lists per query (X8: CollectTopKFromEachWorker.scala:40-48) with an
+ * optional per-query seen-set filter (d_seen: [n_q, seen_stride] item ids, -1 padded).            */
+int fps_topk_merge(const float* d_part_scores, const int32_t* d_part_ids, int32_t n_parts,
+                   int64_t n_q, int32_t k_in, int32_t k_out, const int32_t* d_seen,
+                   int32_t seen_stride, float* d_out_scores, int32_t* d_out_ids, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FPS_B200_H */

@@ -1,0 +1,200 @@
+"""GPU tests of the device substrate and the fused MF kernel against plain fp32/fp64 references."""
+import math
+import random
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def native():
+    from fps_b200.ops import _native
+    if not _native.available():
+        import build_native
+        build_native.build()
+    return _native
+
+
+def test_table_eager_init_matches_philox(native):
+    from fps_b200.ops.table import ShardedTable
+    for dim, shards, part in [(10, 1, "hash"), (15, 3, "hash"), (64, 4, "range"), (128, 2, "hash"), (1, 3, "range")]:
+        t = ShardedTable(1000, dim, n_shards=shards, partition=part, init_range=(-0.01, 0.01), seed=11)
+        ids = torch.arange(1000)
+        got = t.gather(ids).cpu().numpy()
+        want = t.expected_init(np.arange(1000))
+        np.testing.assert_allclose(got, want, rtol=0, atol=2e-9)
+        did, drows = t.dump()
+        assert did.tolist() == list(range(1000))
+        np.testing.assert_allclose(drows.cpu().numpy(), want, rtol=0, atol=2e-9)
+
+
+def test_table_lazy_life_cycle(native):
+    """untouched rows are not dumped; first pull -> init(id); push before pull -> value = delta;
+    push after pull -> init + delta; overwrite wins over both."""
+    from fps_b200.ops.table import ShardedTable, new_flow, read_flow
+    t = ShardedTable(100, 6, n_shards=3, partition="hash", init_range=(1.0, 2.0), seed=3, lazy=True)
+    flow = new_flow()
+    init = t.expected_init(np.arange(100))
+    pulled = t.gather(torch.tensor([5, 7]), flow).cpu().numpy()
+    np.testing.assert_allclose(pulled, init[[5, 7]], atol=1e-7)
+    t.scatter(torch.tensor([7, 9]), torch.ones(2, 6) * 0.5, "add", flow)
+    got = t.gather(torch.tensor([7, 9])).cpu().numpy()
+    np.testing.assert_allclose(got[0], init[7] + 0.5, atol=1e-6)
+    np.testing.assert_allclose(got[1], np.full(6, 0.5), atol=1e-7)       # delta became the value
+    t.scatter(torch.tensor([5, 11]), torch.full((2, 6), 3.0), "overwrite")
+    got = t.gather(torch.tensor([5, 11])).cpu().numpy()
+    np.testing.assert_allclose(got, np.full((2, 6), 3.0), atol=1e-6)
+    ids, rows = t.dump()
+    assert ids.tolist() == [5, 7, 9, 11]
+    s = read_flow(flow)
+    assert s["pulls"] == 2 and s["pushes"] == 2 and s["bad_ids"] == 0
+    t.gather(torch.tensor([1000, -1]), flow)
+    assert read_flow(flow)["bad_ids"] == 2
+
+
+def test_table_add_norm_column(native):
+    from fps_b200.ops.table import ShardedTable
+    t = ShardedTable(50, 10, n_shards=2, init_range=(0.0, 0.0), aux_cols=1)
+    v = torch.arange(10, dtype=torch.float32)[None, :].repeat(3, 1)
+    t.scatter(torch.tensor([3, 4, 40]), v, "add_norm")
+    got = t.gather(torch.tensor([3, 40])).cpu().numpy()
+    np.testing.assert_allclose(got[:, :10], v[:2].numpy(), atol=1e-6)
+    np.testing.assert_allclose(got[:, 10], math.sqrt(float((v[0] ** 2).sum())), rtol=1e-6)
+
+
+def serial_sgd_oracle(u, i, r, U, V, lr, lam=0.0):
+    U, V = U.astype(np.float64).copy(), V.astype(np.float64).copy()
+    for a, b, y in zip(u, i, r):
+        e = y - U[a] @ V[b]
+        du = lr * (e * V[b] - lam * U[a])
+        dv = lr * (e * U[a] - lam * V[b])
+        U[a] += du
+        V[b] += dv
+    return U, V
+
+
+@pytest.mark.parametrize("dim,shards,lazy", [(10, 1, False), (15, 4, True), (64, 3, False), (128, 2, True), (200, 1, False)])
+def test_mf_step_matches_serial_oracle_on_conflict_free_schedule(native, dim, shards, lazy):
+    from fps_b200.models.mf.device import DeviceMF, conflict_free_waves
+    rng = np.random.default_rng(dim)
+    nu, ni, n = 300, 200, 3000
+    u = rng.integers(0, nu, n).astype(np.int32)
+    i = rng.integers(0, ni, n).astype(np.int32)
+    r = rng.random(n).astype(np.float32)
+    mf = DeviceMF(nu, ni, dim, 0.0, 0.3, 0.05, lambda_=0.01, lazy=lazy, n_shards=shards, seed=5)
+    U0 = mf.users.expected_init(np.arange(nu))
+    V0 = mf.items.expected_init(np.arange(ni))
+    du, di, dr = (torch.from_numpy(x).cuda() for x in (u, i, r))
+    order_u, order_i, order_r = [], [], []
+    for wu, wi, wv in conflict_free_waves(du, di, dr):
+        mf.step(wu, wi, wv)
+        order_u += wu.tolist(); order_i += wi.tolist(); order_r += wv.tolist()
+    torch.cuda.synchronize()
+    U, V = serial_sgd_oracle(order_u, order_i, order_r, U0, V0, 0.05, 0.01)
+    s = mf.stats()
+    assert s["records"] == n and s["bad_ids"] == 0
+    got_v = mf.items.gather(torch.arange(ni)).cpu().numpy()
+    got_u = mf.users.gather(torch.arange(nu)).cpu().numpy()
+    np.testing.assert_allclose(got_v, V, rtol=2e-4, atol=2e-5)
+    np.testing.assert_allclose(got_u, U, rtol=2e-4, atol=2e-5)
+    # predict == fp64 dot of the trained factors
+    p = mf.predict(du[:100], di[:100]).cpu().numpy()
+    np.testing.assert_allclose(p, np.einsum("ij,ij->i", U[u[:100]], V[i[:100]]), rtol=1e-3, atol=1e-4)
+
+
+def test_offline_mf_device_reference_acceptance(native):
+    """Same tiny config as the reference's own test: RMSE < 0.5, Hogwild mode."""
+    from fps_b200.models.mf import Rating
+    from fps_b200.models.mf.device import ps_offline_mf_device
+    from fps_b200 import last_write_wins, lefts, rights
+    rnd = random.Random(47)
+    seen, ratings = set(), []
+    for _ in range(100):
+        a, b = rnd.randrange(20), rnd.randrange(15)
+        if (a, b) not in seen:
+            seen.add((a, b)); ratings.append(Rating(a, b, rnd.random()))
+    out = ps_offline_mf_device(ratings, num_factors=15, range_min=0.0, range_max=1.0, learning_rate=0.01,
+                               iterations=10, pull_limit=10, n_shards=4, seed=1)
+    users, items = last_write_wins(lefts(out)), last_write_wins(rights(out))
+    se = sum((r.rating - float(users[r.user] @ items[r.item])) ** 2 for r in ratings)
+    assert math.sqrt(se / len(ratings)) < 0.5
+
+
+def test_device_agrees_with_host_engine_oracle(native):
+    """The same job on the host engine (fp64, serial schedule) and on the device
+    (conflict-free waves) ends in the same factors."""
+    from fps_b200.models.mf import Rating, ps_offline_mf
+    from fps_b200.models.mf.device import ps_offline_mf_device
+    from fps_b200 import last_write_wins, lefts, rights
+    rnd = random.Random(9)
+    ratings = [Rating(rnd.randrange(30), rnd.randrange(25), rnd.random()) for _ in range(400)]
+    kw = dict(num_factors=12, range_min=0.0, range_max=0.5, learning_rate=0.02, iterations=2, seed=4)
+    host = ps_offline_mf(ratings, worker_parallelism=1, ps_parallelism=1, iteration_wait_time=10,
+                         pull_limit=1, shuffle=False, schedule="feedback_first", **kw)
+    dev = ps_offline_mf_device(ratings, shuffle=False, conflict_free=True, pull_limit=0, n_shards=1, **kw)
+    hu, hi = last_write_wins(lefts(host)), last_write_wins(rights(host))
+    du, di = last_write_wins(lefts(dev)), last_write_wins(rights(dev))
+    assert set(hu) == set(du) and set(hi) == set(di)
+    for k in hu:
+        np.testing.assert_allclose(du[k], hu[k], rtol=5e-4, atol=5e-5)
+    for k in hi:
+        np.testing.assert_allclose(di[k], hi[k], rtol=5e-4, atol=5e-5)
+
+
+def test_pull_limiter_is_a_device_credit_counter(native):
+    from fps_b200.models.mf.device import DeviceMF
+    g = torch.Generator().manual_seed(1)
+    n = 200_000
+    u = torch.randint(0, 5000, (n,), generator=g, dtype=torch.int32).cuda()
+    i = torch.randint(0, 3000, (n,), generator=g, dtype=torch.int32).cuda()
+    r = torch.rand(n, generator=g).cuda()
+    for limit in (10, 500, 1600):
+        mf = DeviceMF(5000, 3000, 32, 0.0, 0.1, 0.01, pull_limit=limit)
+        mf.step(u, i, r)
+        torch.cuda.synchronize()
+        s = mf.stats()
+        assert s["records"] == n and s["in_flight"] == 0
+        assert 0 < s["max_in_flight"] <= limit, s
+        assert s["limiter_stalls"] > 0
+    mf = DeviceMF(5000, 3000, 32, 0.0, 0.1, 0.01, pull_limit=0)
+    mf.step(u, i, r)
+    assert mf.stats()["max_in_flight"] == 0       # unlimited: limiter not engaged
+
+
+def test_nan_guard_counts_instead_of_poisoning(native):
+    from fps_b200.models.mf import FactorIsNotANumberException
+    from fps_b200.models.mf.device import DeviceMF
+    mf = DeviceMF(10, 10, 8, 0.0, 0.1, 0.01)
+    u = torch.tensor([1, 2], dtype=torch.int32).cuda()
+    i = torch.tensor([3, 4], dtype=torch.int32).cuda()
+    r = torch.tensor([float("nan"), 1.0]).cuda()
+    mf.step(u, i, r)
+    with pytest.raises(FactorIsNotANumberException):
+        mf.stats()
+    assert torch.isfinite(mf.items.gather(torch.arange(10))).all()
+
+
+def test_streaming_kernel_idle_timeout_and_results(native):
+    """N2: persistent ring consumer exits by itself after iteration_wait_ms of idleness."""
+    from fps_b200.models.mf.device import DeviceMF
+    from fps_b200.models.mf.stream import OnlineStream
+    mf = DeviceMF(2000, 1000, 16, 0.0, 0.2, 0.05, pull_limit=1600)
+    g = torch.Generator().manual_seed(2)
+    n = 50_000
+    u = torch.randint(0, 2000, (n,), generator=g, dtype=torch.int32)
+    i = torch.randint(0, 1000, (n,), generator=g, dtype=torch.int32)
+    r = torch.rand(n, generator=g)
+    before = mf.rmse(u.cuda(), i.cuda(), r.cuda())
+    st = OnlineStream(mf, capacity=1 << 14, iteration_wait_ms=300, max_lifetime_ms=20_000)
+    st.start()
+    for k in range(0, n, 5000):
+        st.feed(u[k:k + 5000], i[k:k + 5000], r[k:k + 5000])
+    reason = st.join()
+    s = mf.stats()
+    assert reason == 1, reason                      # idle timeout, not the lifetime cap
+    assert s["records"] == n and s["ring_done"] == n
+    assert s["max_in_flight"] <= 1600
+    assert mf.rmse(u.cuda(), i.cuda(), r.cuda()) < before
