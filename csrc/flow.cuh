@@ -10,15 +10,22 @@
 __device__ __forceinline__ void flow_acquire(FpsFlow* flow, int n, int limit) {
   if (threadIdx.x == 0) {
     unsigned long long stalls = 0;
+    // CAS, not add-then-undo: speculative adds from hundreds of waiting CTAs would keep the
+    // counter above the limit forever (livelock) when the limit is small.
+    int cur = *(volatile int*)&flow->in_flight;
     while (true) {
-      const int old = atomicAdd(&flow->in_flight, n);
-      if (old + n <= limit) {
-        atomicMax(&flow->max_in_flight, old + n);
-        break;
+      if (cur + n <= limit) {
+        const int seen = atomicCAS(&flow->in_flight, cur, cur + n);
+        if (seen == cur) {
+          atomicMax(&flow->max_in_flight, cur + n);
+          break;
+        }
+        cur = seen;
+        continue;
       }
-      atomicSub(&flow->in_flight, n);
       ++stalls;
-      __nanosleep(200 + (blockIdx.x & 63) * 8);
+      __nanosleep(100 + (blockIdx.x & 63) * 4);
+      cur = *(volatile int*)&flow->in_flight;
     }
     if (stalls) atomicAdd((unsigned long long*)&flow->limiter_stalls, stalls);
   }

@@ -1,0 +1,329 @@
+// Passive-aggressive kernels (N3 binary, N4 multiclass OVA / cost-based, N5 predict).
+// One CSR mini-batch per launch; per example: gather (pull) every active feature from its
+// owner shard, margin / tau, scatter red.add (push) of tau*y*x_i.  The reference does this with
+// nnz Pull messages, nnz PullAnswers, a HashMap assembly and nnz Push messages per example
+// (PassiveAggressiveParameterServer.scala:289-336).
+#include "common.cuh"
+#include "flow.cuh"
+
+namespace {
+
+constexpr int PA_THREADS = 256;
+
+__device__ __forceinline__ float scalar_init(const FpsTableView& t, long long id) {
+  if (t.init_lo == 0.f && t.init_hi == 0.f) return 0.f;
+  return init_block(t, id, 0).x;
+}
+
+// value of a scalar-row (dim == 1) parameter; registers the pull in lazy mode
+__device__ __forceinline__ float pull_scalar(const FpsTableView& t, long long id, const RowRef& r) {
+  float w = ld_row1(t.rows[r.owner] + r.slot * t.stride);
+  if (t.lazy) {
+    const int s = touch_state(t.state[r.owner], r.slot, FPS_ROW_PULLED);
+    if (s == FPS_ROW_PULLED) w += scalar_init(t, id);
+  }
+  return w;
+}
+
+__device__ __forceinline__ float tau_of(int variant, float C, float loss, float n2) {
+  if (n2 <= 0.f) return 0.f;
+  if (variant == 0) return loss / n2;
+  if (variant == 1) return fminf(C, loss / n2);
+  return loss / (n2 + 1.f / (2.f * C));
+}
+
+struct PaCounters {
+  float loss;
+  unsigned int records, pulls, pushes, remote, bad;
+};
+
+__device__ __forceinline__ void pa_flush(PaCounters c, FpsFlow* flow) {
+  __shared__ float s_loss[PA_THREADS / 32];
+  __shared__ unsigned int s_cnt[PA_THREADS / 32][5];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    c.loss += __shfl_xor_sync(0xffffffffu, c.loss, o);
+    c.records += __shfl_xor_sync(0xffffffffu, c.records, o);
+    c.pulls += __shfl_xor_sync(0xffffffffu, c.pulls, o);
+    c.pushes += __shfl_xor_sync(0xffffffffu, c.pushes, o);
+    c.remote += __shfl_xor_sync(0xffffffffu, c.remote, o);
+    c.bad += __shfl_xor_sync(0xffffffffu, c.bad, o);
+  }
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) {
+    s_loss[w] = c.loss;
+    s_cnt[w][0] = c.records; s_cnt[w][1] = c.pulls; s_cnt[w][2] = c.pushes; s_cnt[w][3] = c.remote; s_cnt[w][4] = c.bad;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double L = 0.0;
+    unsigned long long a[5] = {0, 0, 0, 0, 0};
+    for (int i = 0; i < PA_THREADS / 32; ++i) {
+      L += s_loss[i];
+      for (int k = 0; k < 5; ++k) a[k] += s_cnt[i][k];
+    }
+    if (a[0]) {
+      atomicAdd(&flow->loss_sum, L);
+      atomicAdd((unsigned long long*)&flow->records, a[0]);
+    }
+    if (a[1]) atomicAdd((unsigned long long*)&flow->pulls, a[1]);
+    if (a[2]) atomicAdd((unsigned long long*)&flow->pushes, a[2]);
+    if (a[3]) atomicAdd((unsigned long long*)&flow->remote_pulls, a[3]);
+    if (a[4]) atomicAdd((unsigned long long*)&flow->bad_ids, a[4]);
+  }
+}
+
+// ---- N3 / N5 binary: one warp per example -----------------------------------------------------
+__global__ void __launch_bounds__(PA_THREADS)
+k_pa_binary(const __grid_constant__ FpsTableView t, const long long* __restrict__ indptr,
+            const int* __restrict__ indices, const float* __restrict__ values,
+            const int* __restrict__ labels, long long n, const FpsPaParams p, int* __restrict__ pred,
+            FpsFlow* flow) {
+  constexpr int WPB = PA_THREADS / 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  PaCounters c = {0.f, 0, 0, 0, 0, 0};
+  for (long long e0 = (long long)blockIdx.x * WPB; e0 < n; e0 += (long long)gridDim.x * WPB) {
+    const long long e1 = min(e0 + WPB, n);
+    int credits = 0;
+    if (p.pull_limit > 0) {   // limiter counts features (rows), like the reference's limiter
+      credits = (int)min((long long)p.pull_limit, indptr[e1] - indptr[e0]);
+      if (credits > 0) flow_acquire(flow, credits, p.pull_limit);
+    }
+    const long long e = e0 + warp;
+    if (e < n) {
+      const long long b = indptr[e], end = indptr[e + 1];
+      float m = 0.f, n2 = 0.f;
+      for (long long k = b + lane; k < end; k += 32) {
+        const long long id = indices[k];
+        const float x = values[k];
+        const RowRef r = locate(t, id);
+        if (!in_table(t, id, r)) { ++c.bad; continue; }
+        m = fmaf(x, pull_scalar(t, id, r), m);
+        n2 = fmaf(x, x, n2);
+        ++c.pulls;
+        if (r.owner != p.local_shard) ++c.remote;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        m += __shfl_xor_sync(0xffffffffu, m, o);
+        n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+      }
+      if (lane == 0) {
+        ++c.records;
+        if (pred != nullptr) pred[e] = m > 0.f ? 1 : -1;
+      }
+      if (!p.predict_only) {
+        const float y = labels[e] > 0 ? 1.f : -1.f;
+        const float loss = fmaxf(0.f, 1.f - y * m);
+        const float mult = tau_of(p.variant, p.C, loss, n2) * y;
+        if (lane == 0) c.loss += loss;
+        if (mult != 0.f) {
+          for (long long k = b + lane; k < end; k += 32) {
+            const long long id = indices[k];
+            const RowRef r = locate(t, id);
+            if (!in_table(t, id, r)) continue;
+            if (t.lazy) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
+            red_add1(t.rows[r.owner] + r.slot * t.stride, mult * values[k]);
+            ++c.pushes;
+          }
+        }
+      }
+    }
+    if (p.pull_limit > 0 && credits > 0) flow_release(flow, credits);
+  }
+  pa_flush(c, flow);
+}
+
+// ---- N4 / N5 multiclass: one CTA per example ---------------------------------------------------
+// Warps split the active features, lanes split the class columns (float4 each); the decision
+// vector d = W^T x is reduced across warps in shared memory, tau/y per class is computed once,
+// then every warp scatters its features' row deltas.
+__global__ void __launch_bounds__(PA_THREADS)
+k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__ indptr,
+           const int* __restrict__ indices, const float* __restrict__ values,
+           const int* __restrict__ labels, long long n, const FpsPaParams p,
+           const float* __restrict__ cost, int* __restrict__ pred, FpsFlow* flow) {
+  constexpr int WPB = PA_THREADS / 32;
+  extern __shared__ __align__(16) float smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nvec = t.stride >> 2, L = p.n_classes;
+  float* s_part = smem;                       // [WPB][stride]
+  float* s_d = smem + WPB * t.stride;         // [stride] decision, then multiplier vector
+  __shared__ float s_n2[WPB];
+  __shared__ int s_q;
+  __shared__ float s_tau;
+  PaCounters c = {0.f, 0, 0, 0, 0, 0};
+  for (long long e = blockIdx.x; e < n; e += gridDim.x) {
+    const long long b = indptr[e], end = indptr[e + 1];
+    int credits = 0;
+    if (p.pull_limit > 0) {
+      credits = (int)min((long long)p.pull_limit, end - b);
+      if (credits > 0) flow_acquire(flow, credits, p.pull_limit);
+    }
+    // ---- pull + decision vector
+    float n2 = 0.f;
+    for (int v0 = 0; v0 < nvec; v0 += 32) {
+      const int vb = v0 + lane;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (long long k = b + warp; k < end; k += WPB) {
+        const long long id = indices[k];
+        const float x = values[k];
+        const RowRef r = locate(t, id);
+        if (!in_table(t, id, r)) { if (lane == 0 && v0 == 0) ++c.bad; continue; }
+        if (v0 == 0 && lane == 0) {
+          n2 = fmaf(x, x, n2);
+          ++c.pulls;
+          if (r.owner != p.local_shard) ++c.remote;
+        }
+        if (vb < nvec) {
+          float4 w = ld_row4(t.rows[r.owner] + r.slot * t.stride + vb * 4);
+          if (t.lazy) {
+            const int s = touch_state(t.state[r.owner], r.slot, FPS_ROW_PULLED);
+            if (s == FPS_ROW_PULLED && !(t.init_lo == 0.f && t.init_hi == 0.f)) {
+              const float4 i4 = init_block(t, id, vb);
+              w.x += i4.x; w.y += i4.y; w.z += i4.z; w.w += i4.w;
+            }
+          }
+          acc.x = fmaf(x, w.x, acc.x); acc.y = fmaf(x, w.y, acc.y);
+          acc.z = fmaf(x, w.z, acc.z); acc.w = fmaf(x, w.w, acc.w);
+        }
+      }
+      if (vb < nvec) *reinterpret_cast<float4*>(s_part + warp * t.stride + vb * 4) = acc;
+    }
+    if (lane == 0) s_n2[warp] = n2;
+    __syncthreads();
+    for (int j = threadIdx.x; j < t.stride; j += PA_THREADS) {
+      float d = 0.f;
+#pragma unroll
+      for (int w = 0; w < WPB; ++w) d += s_part[w * t.stride + j];
+      s_d[j] = d;
+    }
+    __syncthreads();
+    float norm2 = 0.f;
+#pragma unroll
+    for (int w = 0; w < WPB; ++w) norm2 += s_n2[w];
+    const int y = p.predict_only ? 0 : labels[e];
+    // ---- argmax family (thread 0; L is ~100: cheaper than a tree for this size)
+    if (threadIdx.x == 0) {
+      int am = 0;
+      float best = s_d[0];
+      for (int j = 1; j < L; ++j)
+        if (s_d[j] > best) { best = s_d[j]; am = j; }
+      if (pred != nullptr) pred[e] = am;
+      int q = am;
+      float tau = 0.f;
+      if (!p.predict_only && p.multiclass >= 2) {
+        if (p.multiclass == 3) {   // ML: argmax_i d_i - d_y + sqrt(cost(y, i))
+          float bestv = -INFINITY;
+          for (int j = 0; j < L; ++j) {
+            const float cj = cost ? sqrtf(cost[y * L + j]) : (j == y ? 0.f : 1.f);
+            const float v = s_d[j] - s_d[y] + cj;
+            if (v > bestv) { bestv = v; q = j; }
+          }
+        }
+        if (q != y) {
+          const float cq = cost ? sqrtf(cost[y * L + q]) : 1.f;
+          const float loss = s_d[q] - s_d[y] + cq;
+          tau = norm2 > 0.f ? loss / (2.f * norm2) : 0.f;
+          c.loss += fmaxf(loss, 0.f);
+        }
+      }
+      s_q = q;
+      s_tau = tau;
+      ++c.records;
+    }
+    __syncthreads();
+    if (!p.predict_only) {
+      bool any = false;
+      if (p.multiclass == 1) {
+        // one-vs-all: per-class multiplier tau_c * y_c, written over s_d
+        float lsum = 0.f;
+        for (int j = threadIdx.x; j < t.stride; j += PA_THREADS) {
+          float mult = 0.f;
+          if (j < L) {
+            const float yc = (j == y) ? 1.f : -1.f;
+            const float loss = fmaxf(0.f, 1.f - s_d[j] * yc);
+            mult = tau_of(p.variant, p.C, loss, norm2) * yc;
+            lsum += loss;
+          }
+          s_d[j] = mult;
+        }
+        c.loss += lsum;
+        __syncthreads();
+        any = true;   // rows of all-zero multipliers are rare (every class already separated)
+      }
+      if (p.multiclass == 1 && any) {
+        for (long long k = b + warp; k < end; k += WPB) {
+          const long long id = indices[k];
+          const float x = values[k];
+          const RowRef r = locate(t, id);
+          if (!in_table(t, id, r)) continue;
+          float* row = t.rows[r.owner] + r.slot * t.stride;
+          if (t.lazy && lane == 0) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
+          for (int vb = lane; vb < nvec; vb += 32) {
+            const float4 m4 = *reinterpret_cast<const float4*>(s_d + vb * 4);
+            red_add4(row + vb * 4, make_float4(x * m4.x, x * m4.y, x * m4.z, x * m4.w));
+          }
+          if (lane == 0) ++c.pushes;
+        }
+      } else if (p.multiclass >= 2 && s_q != y) {
+        const float tau = s_tau;
+        const int q = s_q;
+        for (long long k = b + threadIdx.x; k < end; k += PA_THREADS) {
+          const long long id = indices[k];
+          const float x = values[k];
+          const RowRef r = locate(t, id);
+          if (!in_table(t, id, r)) continue;
+          float* row = t.rows[r.owner] + r.slot * t.stride;
+          if (t.lazy) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
+          red_add1(row + y, tau * x);
+          red_add1(row + q, -tau * x);
+          ++c.pushes;
+        }
+      }
+    }
+    if (p.pull_limit > 0 && credits > 0) flow_release(flow, credits);
+    __syncthreads();
+  }
+  pa_flush(c, flow);
+}
+
+}  // namespace
+
+extern "C" int fps_pa_step(const FpsTableView* weights, const int64_t* d_indptr, const int32_t* d_indices,
+                           const float* d_values, const int32_t* d_labels, int64_t n_examples,
+                           const FpsPaParams* params, int32_t* d_pred, FpsFlow* d_flow, void* stream) {
+  return fps_pa_step_cost(weights, d_indptr, d_indices, d_values, d_labels, n_examples, params, nullptr,
+                          d_pred, d_flow, stream);
+}
+
+extern "C" int fps_pa_step_cost(const FpsTableView* weights, const int64_t* d_indptr, const int32_t* d_indices,
+                                const float* d_values, const int32_t* d_labels, int64_t n_examples,
+                                const FpsPaParams* params, const float* d_cost, int32_t* d_pred,
+                                FpsFlow* d_flow, void* stream) {
+  FPS_REQUIRE(weights && params && d_flow, FPS_E_INVALID, "fps_pa_step: null argument");
+  FPS_REQUIRE(weights->n_shards >= 1 && weights->n_shards <= FPS_MAX_SHARDS, FPS_E_INVALID, "fps_pa_step: n_shards");
+  FPS_REQUIRE(params->predict_only || d_labels != nullptr, FPS_E_INVALID, "fps_pa_step: labels required for training");
+  if (n_examples <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int sms = fps_num_sms();
+  if (params->multiclass == 0) {
+    FPS_REQUIRE(weights->dim == 1, FPS_E_INVALID, "fps_pa_step: binary PA needs a dim-1 table");
+    long long blocks = (n_examples + 7) / 8;
+    if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
+    k_pa_binary<<<(int)blocks, PA_THREADS, 0, st>>>(*weights, (const long long*)d_indptr, d_indices, d_values,
+                                                    d_labels, n_examples, *params, d_pred, d_flow);
+  } else {
+    FPS_REQUIRE(weights->stride % 4 == 0 && weights->dim == params->n_classes, FPS_E_INVALID,
+                "fps_pa_step: multiclass table must have dim == n_classes (%d vs %d)", weights->dim, params->n_classes);
+    const size_t smem = (size_t)(PA_THREADS / 32 + 1) * weights->stride * sizeof(float);
+    FPS_REQUIRE(smem <= 200 * 1024, FPS_E_UNSUPPORTED, "fps_pa_step: too many classes (%d)", params->n_classes);
+    if (smem > 48 * 1024) FPS_CUDA(cudaFuncSetAttribute(k_pa_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    long long blocks = n_examples;
+    if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
+    k_pa_multi<<<(int)blocks, PA_THREADS, smem, st>>>(*weights, (const long long*)d_indptr, d_indices, d_values,
+                                                      d_labels, n_examples, *params, d_cost, d_pred, d_flow);
+  }
+  FPS_LAUNCH_CHECK();
+  return 0;
+}

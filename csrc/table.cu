@@ -179,6 +179,87 @@ k_dump_shard(const __grid_constant__ FpsTableView t, int shard, long long n_rows
   }
 }
 
+// ---- scalar tables (dim == stride == 1: binary PA weights) --------------------------------------
+__device__ __forceinline__ float scalar_init_value(const FpsTableView& t, long long id) {
+  if (t.init_lo == 0.f && t.init_hi == 0.f) return 0.f;
+  return init_block(t, id, 0).x;
+}
+
+__global__ void __launch_bounds__(256)
+k_init_shard_scalar(const __grid_constant__ FpsTableView t, int shard, long long n_rows) {
+  float* base = t.rows[shard];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows;
+       i += (long long)gridDim.x * blockDim.x)
+    base[i] = scalar_init_value(t, slot_to_id(t, shard, i));
+}
+
+__global__ void __launch_bounds__(256)
+k_gather_scalar(const __grid_constant__ FpsTableView t, const long long* __restrict__ ids, long long n,
+                float* __restrict__ out, int out_stride, FpsFlow* flow) {
+  unsigned long long bad = 0, done = 0;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < n; g += (long long)gridDim.x * blockDim.x) {
+    const long long id = ids[g];
+    const RowRef r = locate(t, id);
+    if (!in_table(t, id, r)) { ++bad; continue; }
+    float v = ld_row1(t.rows[r.owner] + r.slot);
+    if (t.lazy && touch_state(t.state[r.owner], r.slot, FPS_ROW_PULLED) == FPS_ROW_PULLED)
+      v += scalar_init_value(t, id);
+    out[g * out_stride] = v;
+    ++done;
+  }
+  if (flow != nullptr) {
+    if (bad) atomicAdd((unsigned long long*)&flow->bad_ids, bad);
+    if (done) atomicAdd((unsigned long long*)&flow->pulls, done);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_scatter_scalar(const __grid_constant__ FpsTableView t, const long long* __restrict__ ids, long long n,
+                 const float* __restrict__ vals, int val_stride, int mode, FpsFlow* flow) {
+  unsigned long long bad = 0, done = 0;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < n; g += (long long)gridDim.x * blockDim.x) {
+    const long long id = ids[g];
+    const RowRef r = locate(t, id);
+    if (!in_table(t, id, r)) { ++bad; continue; }
+    int state = FPS_ROW_PUSHED;
+    if (t.lazy) state = touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
+    float* row = t.rows[r.owner] + r.slot;
+    float d = vals[g * val_stride];
+    if (mode == 1) {
+      if (state == FPS_ROW_PULLED) d -= scalar_init_value(t, id);
+      asm volatile("st.global.cg.f32 [%0], %1;" ::"l"(row), "f"(d) : "memory");
+    } else {
+      red_add1(row, d);
+    }
+    ++done;
+  }
+  if (flow != nullptr) {
+    if (bad) atomicAdd((unsigned long long*)&flow->bad_ids, bad);
+    if (done) atomicAdd((unsigned long long*)&flow->pushes, done);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_dump_shard_scalar(const __grid_constant__ FpsTableView t, int shard, long long n_rows, long long n_ids_total,
+                    long long* __restrict__ out_ids, float* __restrict__ out_rows, long long capacity,
+                    unsigned long long* count) {
+  const float* base = t.rows[shard];
+  for (long long slot = (long long)blockIdx.x * blockDim.x + threadIdx.x; slot < n_rows;
+       slot += (long long)gridDim.x * blockDim.x) {
+    const long long id = slot_to_id(t, shard, slot);
+    if (id >= n_ids_total) continue;
+    int state = FPS_ROW_PUSHED;
+    if (t.lazy) {
+      state = t.state[shard][slot];
+      if (state == FPS_ROW_UNTOUCHED) continue;
+    }
+    const unsigned long long idx = atomicAdd(count, 1ull);
+    if ((long long)idx >= capacity) continue;
+    out_ids[idx] = id;
+    out_rows[idx] = ld_row1(base + slot) + (state == FPS_ROW_PULLED ? scalar_init_value(t, id) : 0.f);
+  }
+}
+
 int lanes_for(int stride) {
   const int nvec = stride / 4;
   int l = 1;
@@ -189,8 +270,9 @@ int lanes_for(int stride) {
 int check_view(const FpsTableView* v, const char* who) {
   FPS_REQUIRE(v != nullptr, FPS_E_INVALID, "%s: null table view", who);
   FPS_REQUIRE(v->n_shards >= 1 && v->n_shards <= FPS_MAX_SHARDS, FPS_E_INVALID, "%s: n_shards %d out of range", who, v->n_shards);
-  FPS_REQUIRE(v->stride % 4 == 0 && v->stride >= v->dim && v->dim >= 1, FPS_E_INVALID,
-              "%s: stride %d must be a multiple of 4 and >= dim %d", who, v->stride, v->dim);
+  FPS_REQUIRE((v->stride % 4 == 0 || (v->stride == 1 && v->dim == 1)) && v->stride >= v->dim && v->dim >= 1,
+              FPS_E_INVALID, "%s: stride %d must be a multiple of 4 (or 1 for scalar tables) and >= dim %d",
+              who, v->stride, v->dim);
   FPS_REQUIRE(v->partition == FPS_PART_HASH || v->div > 0, FPS_E_INVALID, "%s: range partition needs div > 0", who);
   return 0;
 }
@@ -206,6 +288,13 @@ int fps_table_init_shard(const FpsTableView* view, int shard, int64_t n_rows, vo
   FPS_REQUIRE(shard >= 0 && shard < view->n_shards && view->rows[shard] != nullptr, FPS_E_INVALID,
               "fps_table_init_shard: shard %d not mapped", shard);
   if (n_rows <= 0) return 0;
+  if (view->stride == 1) {
+    long long b = (n_rows + 255) / 256;
+    if (b > (long long)fps_num_sms() * 16) b = (long long)fps_num_sms() * 16;
+    k_init_shard_scalar<<<(int)b, 256, 0, (cudaStream_t)stream>>>(*view, shard, n_rows);
+    FPS_LAUNCH_CHECK();
+    return 0;
+  }
   const long long total = (long long)n_rows * (view->stride / 4);
   long long blocks = (total + 255) / 256;
   const long long cap = (long long)fps_num_sms() * 16;
@@ -229,6 +318,13 @@ int fps_table_gather(const FpsTableView* view, const int64_t* d_ids, int64_t n, 
                      int out_stride, FpsFlow* d_flow, void* stream) {
   if (int e = check_view(view, "fps_table_gather")) return e;
   if (n <= 0) return 0;
+  if (view->stride == 1) {
+    long long b = (n + 255) / 256;
+    if (b > (long long)fps_num_sms() * 8) b = (long long)fps_num_sms() * 8;
+    k_gather_scalar<<<(int)b, 256, 0, (cudaStream_t)stream>>>(*view, (const long long*)d_ids, n, d_out, out_stride, d_flow);
+    FPS_LAUNCH_CHECK();
+    return 0;
+  }
   const int lanes = lanes_for(view->stride);
   const int gpb = 256 / lanes;
   long long blocks = (n + gpb - 1) / gpb;
@@ -245,6 +341,14 @@ int fps_table_scatter(const FpsTableView* view, const int64_t* d_ids, int64_t n,
   if (int e = check_view(view, "fps_table_scatter")) return e;
   FPS_REQUIRE(mode >= 0 && mode <= 2, FPS_E_INVALID, "fps_table_scatter: mode %d", mode);
   if (n <= 0) return 0;
+  if (view->stride == 1) {
+    FPS_REQUIRE(mode != 2, FPS_E_INVALID, "fps_table_scatter: add_norm needs a vector table");
+    long long b = (n + 255) / 256;
+    if (b > (long long)fps_num_sms() * 8) b = (long long)fps_num_sms() * 8;
+    k_scatter_scalar<<<(int)b, 256, 0, (cudaStream_t)stream>>>(*view, (const long long*)d_ids, n, d_vals, val_stride, mode, d_flow);
+    FPS_LAUNCH_CHECK();
+    return 0;
+  }
   const int lanes = lanes_for(view->stride);
   const int gpb = 256 / lanes;
   long long blocks = (n + gpb - 1) / gpb;
@@ -263,6 +367,14 @@ int fps_table_dump_shard(const FpsTableView* view, int shard, int64_t n_rows, in
   FPS_REQUIRE(shard >= 0 && shard < view->n_shards && view->rows[shard] != nullptr, FPS_E_INVALID,
               "fps_table_dump_shard: shard %d not mapped", shard);
   if (n_rows <= 0) return 0;
+  if (view->stride == 1) {
+    long long b = (n_rows + 255) / 256;
+    if (b > (long long)fps_num_sms() * 8) b = (long long)fps_num_sms() * 8;
+    k_dump_shard_scalar<<<(int)b, 256, 0, (cudaStream_t)stream>>>(*view, shard, n_rows, n_ids_total, (long long*)d_out_ids,
+                                                                  d_out_rows, capacity, (unsigned long long*)d_count);
+    FPS_LAUNCH_CHECK();
+    return 0;
+  }
   long long blocks = (n_rows + 7) / 8;
   const long long cap = (long long)fps_num_sms() * 8;
   if (blocks > cap) blocks = cap;

@@ -1,0 +1,533 @@
+// LEMP top-K retrieval on the 5th-gen tensor cores (N6) + partial-list merge (N7).
+//
+// Reference behaviour: PSTopKGeneratorWorker.scala:49-111 walks items in buckets of decreasing
+// length, stops when ||q|| * bucketMaxLen <= theta (theta = current k-th best score), scores the
+// surviving items with scalar dot products and keeps a min-heap of workerK entries - per query.
+//
+// Here a CTA owns a tile of 128 queries and walks 64-item tiles (= buckets) of the length-sorted
+// item matrix.  Scores S = Q * P^T are tcgen05.mma tiles (M=128, N=64, kind::tf32) with the
+// accumulator in TMEM.  The tables are fp32 and must stay fp32, so both operands are split
+// x = hi + lo (hi = tf32(x), lo = tf32(x - hi)) and three MMAs accumulate hi*hi + hi*lo + lo*hi
+// (3xTF32, error ~2^-21 relative to the operand magnitudes).  Operands are staged in shared memory
+// in the K-major SWIZZLE_128B layout the UMMA descriptors expect.  The LEMP LENGTH test is applied
+// per tile: when ||q|| * tileMaxLen <= theta holds for every query of the CTA the walk stops
+// (exact, because lengths are sorted).  Selection: thread t owns query t (TMEM lane t); scores
+// above its running theta are appended to a per-query candidate buffer in scratch memory; when a
+// buffer fills it is pruned back to the k best by a bitwise selection of the k-th largest key,
+// which also raises theta.  Item tiles are dealt round-robin to `n_splits` CTAs per query tile;
+// their partial lists are merged by fps_topk_merge (X8: CollectTopKFromEachWorker.scala:40-48).
+#include "common.cuh"
+
+namespace {
+
+constexpr int TK_M = 128;          // queries per CTA (UMMA M, TMEM lanes)
+constexpr int TK_N = 64;           // items per tile (UMMA N)
+constexpr int TK_KB = 32;          // fp32 elements per K block = one 128-byte swizzle row
+constexpr int TK_THREADS = 128;
+constexpr int TK_CAP = 256;        // candidate slots per (query, split)
+constexpr int TK_MAX_K = 128;      // k <= CAP - N must hold: 128 <= 256 - 64
+
+// ------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  }
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, tf32 inputs, fp32 accumulate, issued by one thread
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 32 consecutive accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor layout):
+//   [0,14) start >> 4 | [16,30) LBO >> 4 (unused for swizzled K-major, 1) | [32,46) SBO >> 4 = 1024 B
+//   between 8-row groups | [46,48) version = 1 | [61,64) layout = 2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// instruction descriptor: D fp32 (1<<4), A/B tf32 (2<<7, 2<<10), both K-major, N>>3 at 17, M>>4 at 24
+constexpr uint32_t TK_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TK_N >> 3) << 17) | ((uint32_t)(TK_M >> 4) << 24);
+
+__device__ __forceinline__ float to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+// order-preserving float <-> uint key
+__device__ __forceinline__ uint32_t f2key(float f) {
+  const uint32_t b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float key2f(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// Stage `rows` x (KBLKS*32) fp32 values (row-major, `stride` floats apart, rows >= valid are zero,
+// columns >= dim are zero) into the swizzled K-major layout: K block kb is a [rows x 128 B] slab;
+// inside it row r sits at r*128 and its 16-byte chunk c at ((c ^ (r & 7)) * 16).
+template <bool SPLIT>
+__device__ __forceinline__ void stage_tile(float* __restrict__ s_hi, float* __restrict__ s_lo,
+                                           const float* __restrict__ src, int stride, int rows, int valid,
+                                           int dim, int kblks) {
+  const int chunks_per_row = kblks * 8;
+  for (int i = threadIdx.x; i < rows * chunks_per_row; i += TK_THREADS) {
+    const int r = i / chunks_per_row, cc = i - r * chunks_per_row;
+    const int kb = cc >> 3, c = cc & 7;
+    const int col = kb * TK_KB + c * 4;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < valid && col < dim) {
+      const float* p = src + (size_t)r * stride + col;
+      if (col + 3 < dim) x = *reinterpret_cast<const float4*>(p);
+      else {
+        x.x = p[0];
+        if (col + 1 < dim) x.y = p[1];
+        if (col + 2 < dim) x.z = p[2];
+      }
+    }
+    const int off = kb * rows * TK_KB + r * TK_KB + ((c ^ (r & 7)) << 2);   // in floats
+    if (SPLIT) {
+      float4 h, l;
+      h.x = to_tf32(x.x); h.y = to_tf32(x.y); h.z = to_tf32(x.z); h.w = to_tf32(x.w);
+      l.x = to_tf32(x.x - h.x); l.y = to_tf32(x.y - h.y); l.z = to_tf32(x.z - h.z); l.w = to_tf32(x.w - h.w);
+      *reinterpret_cast<float4*>(s_hi + off) = h;
+      *reinterpret_cast<float4*>(s_lo + off) = l;
+    } else {
+      *reinterpret_cast<float4*>(s_hi + off) = x;
+    }
+  }
+}
+
+struct TopkScratch {
+  float* cand_s;          // [n_ctas][CAP][128]
+  int* cand_i;            // [n_ctas][CAP][128]
+  uint32_t* theta;        // [n_q_tiles*128] shared k-th-best lower bound per query (ordered key)
+  float* part_s;          // [n_q_pad][n_splits][k]
+  int* part_i;
+};
+
+// prune the candidate list of this thread's query back to its k best; returns new count and theta
+__device__ __forceinline__ int prune_candidates(float* cs, int* ci, int cnt, int k, float& theta) {
+  if (cnt <= k) {
+    if (cnt == k) {   // theta = min of the list
+      float m = INFINITY;
+      for (int j = 0; j < cnt; ++j) m = fminf(m, cs[j * TK_M]);
+      theta = fmaxf(theta, m);
+    }
+    return cnt;
+  }
+  uint32_t T = 0;
+  for (int b = 31; b >= 0; --b) {
+    const uint32_t trial = T | (1u << b);
+    int n = 0;
+    for (int j = 0; j < cnt; ++j) n += (f2key(cs[j * TK_M]) >= trial);
+    if (n >= k) T = trial;
+  }
+  // keep everything above T, then fill with keys equal to T up to k
+  int w = 0, above = 0;
+  for (int j = 0; j < cnt; ++j) above += (f2key(cs[j * TK_M]) > T);
+  int ties_left = k - above;
+  for (int j = 0; j < cnt; ++j) {
+    const float s = cs[j * TK_M];
+    const int id = ci[j * TK_M];
+    const uint32_t key = f2key(s);
+    bool keep = key > T;
+    if (!keep && key == T && ties_left > 0) { keep = true; --ties_left; }
+    if (keep) { cs[w * TK_M] = s; ci[w * TK_M] = id; ++w; }
+  }
+  theta = fmaxf(theta, key2f(T));
+  return w;
+}
+
+template <bool TC>
+__global__ void __launch_bounds__(TK_THREADS, 1)
+k_lemp_topk(const float* __restrict__ queries, int q_stride, long long n_q,
+            const float* __restrict__ items, int item_stride, const float* __restrict__ item_len,
+            const int* __restrict__ item_ids, long long n_items, int dim, int kblks, int k, int n_splits,
+            int use_pruning, TopkScratch sc, unsigned long long* __restrict__ stats) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment is required by SWIZZLE_128B; dynamic smem base is only 16-byte aligned
+  uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int a_floats = TK_M * kblks * TK_KB, b_floats = TK_N * kblks * TK_KB;
+  float* sA_hi = (float*)base;
+  float* sA_lo = sA_hi + a_floats;
+  float* sB_hi = sA_lo + (TC ? a_floats : 0);
+  float* sB_lo = sB_hi + b_floats;
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ uint32_t s_tmem;
+
+  const int t = threadIdx.x, warp = t >> 5;
+  const int qt = blockIdx.x / n_splits, split = blockIdx.x - qt * n_splits;
+  const long long q0 = (long long)qt * TK_M;
+  const int q_valid = (int)min((long long)TK_M, n_q - q0);
+
+  if (TC) {
+    if (warp == 0) tmem_alloc(&s_tmem, 64);
+    if (t == 0) {
+      mbar_init(&s_bar, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+  }
+  stage_tile<TC>(sA_hi, sA_lo, queries + q0 * q_stride, q_stride, TK_M, q_valid, dim, kblks);
+
+  // ||q|| for the LENGTH bound
+  float qlen = 0.f;
+  if (t < q_valid) {
+    const float* qp = queries + (q0 + t) * q_stride;
+    float s = 0.f;
+    for (int j = 0; j < dim; ++j) s = fmaf(qp[j], qp[j], s);
+    qlen = sqrtf(s);
+  }
+  if (TC) {
+    tc_fence_before();
+    fence_async_smem();
+  }
+  __syncthreads();
+  uint32_t tmem_base = 0;
+  if (TC) {
+    tc_fence_after();
+    tmem_base = s_tmem;
+  }
+
+  float* cs = sc.cand_s + (size_t)blockIdx.x * TK_CAP * TK_M + t;
+  int* ci = sc.cand_i + (size_t)blockIdx.x * TK_CAP * TK_M + t;
+  volatile uint32_t* theta_g = sc.theta + q0 + t;
+  int cnt = 0;
+  float theta = -INFINITY;
+  uint32_t phase = 0;
+  unsigned long long tiles_done = 0, accepted = 0, prunes = 0;
+
+  const long long n_tiles = (n_items + TK_N - 1) / TK_N;
+  for (long long tile = split; tile < n_tiles; tile += n_splits) {
+    const long long i0 = tile * TK_N;
+    const int i_valid = (int)min((long long)TK_N, n_items - i0);
+    // ---- LEMP LENGTH test for the whole bucket (exact early exit: lengths are descending)
+    if (use_pruning) {
+      theta = fmaxf(theta, key2f(*theta_g));
+      const float bound = qlen * item_len[i0];
+      const int can_skip = (t >= q_valid) || (theta > -INFINITY && bound <= theta);
+      if (__syncthreads_and(can_skip)) break;
+    }
+    // ---- stage the item tile
+    stage_tile<TC>(sB_hi, sB_lo, items + i0 * item_stride, item_stride, TK_N, i_valid, dim, kblks);
+    float sc_row[TK_N];
+    if (TC) {
+      fence_async_smem();
+      __syncthreads();
+      if (t == 0) {
+        tc_fence_after();
+        uint32_t acc = 0;
+        for (int kb = 0; kb < kblks; ++kb) {
+#pragma unroll
+          for (int ks = 0; ks < TK_KB / 8; ++ks) {
+            const uint32_t a_off = (uint32_t)(kb * TK_M * TK_KB + ks * 8) * 4, b_off = (uint32_t)(kb * TK_N * TK_KB + ks * 8) * 4;
+            const uint64_t ah = make_desc(smem_u32(sA_hi) + a_off), al = make_desc(smem_u32(sA_lo) + a_off);
+            const uint64_t bh = make_desc(smem_u32(sB_hi) + b_off), bl = make_desc(smem_u32(sB_lo) + b_off);
+            umma_tf32(tmem_base, al, bh, TK_IDESC, acc);   // small terms first
+            umma_tf32(tmem_base, ah, bl, TK_IDESC, 1);
+            umma_tf32(tmem_base, ah, bh, TK_IDESC, 1);
+            acc = 1;
+          }
+        }
+        umma_commit(&s_bar);
+      }
+      mbar_wait(&s_bar, phase);
+      phase ^= 1;
+      tc_fence_after();
+      const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+      float v0[32], v1[32];
+      tmem_ld32(lane_addr, v0);
+      tmem_ld32(lane_addr + 32, v1);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) { sc_row[j] = v0[j]; sc_row[32 + j] = v1[j]; }
+      tc_fence_before();
+    } else {
+      __syncthreads();
+      // CUDA-core fp32 scoring of the same staged tile (baseline / oracle)
+#pragma unroll
+      for (int j = 0; j < TK_N; ++j) sc_row[j] = 0.f;
+      for (int kb = 0; kb < kblks; ++kb) {
+        for (int c = 0; c < 8; ++c) {
+          const float4 a = *reinterpret_cast<const float4*>(sA_hi + kb * TK_M * TK_KB + t * TK_KB + ((c ^ (t & 7)) << 2));
+#pragma unroll
+          for (int j = 0; j < TK_N; ++j) {
+            const float4 b = *reinterpret_cast<const float4*>(sB_hi + kb * TK_N * TK_KB + j * TK_KB + ((c ^ (j & 7)) << 2));
+            sc_row[j] = fmaf(a.x, b.x, fmaf(a.y, b.y, fmaf(a.z, b.z, fmaf(a.w, b.w, sc_row[j]))));
+          }
+        }
+      }
+    }
+    // ---- selection: append everything that beats the running theta
+    if (t < q_valid) {
+#pragma unroll
+      for (int j = 0; j < TK_N; ++j) {
+        if (j < i_valid && sc_row[j] > theta) {
+          cs[cnt * TK_M] = sc_row[j];
+          ci[cnt * TK_M] = (int)(i0 + j);
+          ++cnt;
+          ++accepted;
+        }
+      }
+    }
+    ++tiles_done;
+    if (__syncthreads_or(cnt > TK_CAP - TK_N)) {
+      if (cnt > k) {
+        cnt = prune_candidates(cs, ci, cnt, k, theta);
+        ++prunes;
+        if (use_pruning) atomicMax((uint32_t*)theta_g, f2key(theta));
+      }
+    }
+    __syncthreads();   // the next stage_tile overwrites sB; every thread is done with this tile
+  }
+
+  // ---- final: k best of this (query, split), unsorted, padded with (-inf, -1)
+  if (t < q_valid) {
+    cnt = prune_candidates(cs, ci, cnt, k, theta);
+    float* ps = sc.part_s + ((size_t)(q0 + t) * n_splits + split) * k;
+    int* pi = sc.part_i + ((size_t)(q0 + t) * n_splits + split) * k;
+    for (int j = 0; j < k; ++j) {
+      if (j < cnt) {
+        const int slot = ci[j * TK_M];
+        ps[j] = cs[j * TK_M];
+        pi[j] = item_ids ? item_ids[slot] : slot;
+      } else {
+        ps[j] = -INFINITY;
+        pi[j] = -1;
+      }
+    }
+  }
+  if (stats != nullptr && t == 0) {
+    atomicAdd(&stats[0], tiles_done);
+    atomicAdd(&stats[1], (unsigned long long)((n_tiles - split + n_splits - 1) / n_splits));
+  }
+  if (stats != nullptr) {
+    atomicAdd(&stats[2], accepted);
+    if (prunes) atomicAdd(&stats[3], prunes);
+  }
+  if (TC) {
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, 64);
+  }
+}
+
+// ---- N7: merge partial lists (one CTA per query, bitonic sort in shared memory) ------------------
+__global__ void __launch_bounds__(256)
+k_topk_merge(const float* __restrict__ part_s, const int* __restrict__ part_i, int n_parts, long long n_q,
+             int k_in, int k_out, const int* __restrict__ seen, int seen_stride,
+             float* __restrict__ out_s, int* __restrict__ out_i, int pow2) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  float* s = (float*)smem_raw;
+  int* id = (int*)(s + pow2);
+  const long long q = blockIdx.x;
+  const int n = n_parts * k_in;
+  for (int j = threadIdx.x; j < pow2; j += blockDim.x) {
+    float v = -INFINITY;
+    int ii = -1;
+    if (j < n) {
+      v = part_s[q * n + j];
+      ii = part_i[q * n + j];
+      if (ii >= 0 && seen != nullptr) {
+        for (int m = 0; m < seen_stride; ++m) {
+          const int sv = seen[q * seen_stride + m];
+          if (sv < 0) break;
+          if (sv == ii) { v = -INFINITY; ii = -1; break; }
+        }
+      }
+      if (ii < 0) v = -INFINITY;
+    }
+    s[j] = v;
+    id[j] = ii;
+  }
+  __syncthreads();
+  // bitonic sort, descending by (score, then smaller id first for determinism)
+  for (int size = 2; size <= pow2; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int j = threadIdx.x; j < pow2; j += blockDim.x) {
+        const int p = j ^ stride;
+        if (p > j) {
+          const bool desc = ((j & size) == 0);
+          const float a = s[j], b = s[p];
+          const int ia = id[j], ib = id[p];
+          const bool a_first = (a > b) || (a == b && (unsigned)ia <= (unsigned)ib);
+          if (desc ? !a_first : a_first) {
+            s[j] = b; s[p] = a; id[j] = ib; id[p] = ia;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int j = threadIdx.x; j < k_out; j += blockDim.x) {
+    out_s[q * k_out + j] = j < pow2 ? s[j] : -INFINITY;
+    out_i[q * k_out + j] = j < pow2 ? id[j] : -1;
+  }
+}
+
+struct Plan {
+  int n_q_tiles, n_splits, n_ctas, kblks;
+  size_t off_cand_i, off_theta, off_part_s, off_part_i, total;
+};
+
+Plan make_plan(long long n_q, int k, long long n_items, int dim) {
+  Plan p;
+  p.n_q_tiles = (int)((n_q + TK_M - 1) / TK_M);
+  const long long n_tiles = (n_items + TK_N - 1) / TK_N;
+  const int sms = fps_num_sms();
+  long long splits = sms / (p.n_q_tiles > 0 ? p.n_q_tiles : 1);
+  if (splits < 1) splits = 1;
+  if (splits > 16) splits = 16;
+  if (splits > n_tiles) splits = n_tiles > 0 ? n_tiles : 1;
+  p.n_splits = (int)splits;
+  p.n_ctas = p.n_q_tiles * p.n_splits;
+  p.kblks = (dim + TK_KB - 1) / TK_KB;
+  auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  size_t o = 0;
+  o = align(o + (size_t)p.n_ctas * TK_CAP * TK_M * sizeof(float));
+  p.off_cand_i = o;
+  o = align(o + (size_t)p.n_ctas * TK_CAP * TK_M * sizeof(int));
+  p.off_theta = o;
+  o = align(o + (size_t)p.n_q_tiles * TK_M * sizeof(uint32_t));
+  p.off_part_s = o;
+  o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * k * sizeof(float));
+  p.off_part_i = o;
+  o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * k * sizeof(int));
+  p.total = o;
+  return p;
+}
+
+int launch_merge(const float* part_s, const int* part_i, int n_parts, long long n_q, int k_in, int k_out,
+                 const int* seen, int seen_stride, float* out_s, int* out_i, cudaStream_t st) {
+  int pow2 = 1;
+  while (pow2 < n_parts * k_in) pow2 <<= 1;
+  FPS_REQUIRE(pow2 <= 8192, FPS_E_TOO_LARGE, "fps_topk_merge: %d candidates per query exceed 8192", n_parts * k_in);
+  FPS_REQUIRE(k_out <= pow2, FPS_E_INVALID, "fps_topk_merge: k_out %d > candidates %d", k_out, pow2);
+  const size_t smem = (size_t)pow2 * 8;
+  if (smem > 48 * 1024) FPS_CUDA(cudaFuncSetAttribute(k_topk_merge, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_topk_merge<<<(unsigned)n_q, 256, smem, st>>>(part_s, part_i, n_parts, n_q, k_in, k_out, seen, seen_stride, out_s, out_i, pow2);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+template <bool TC>
+int run_topk(const float* d_queries, int q_stride, long long n_q, const float* d_items, int item_stride,
+             const float* d_item_len, const int* d_item_ids, long long n_items, int dim, int k,
+             int use_pruning, void* d_scratch, size_t scratch_bytes, float* d_out_scores, int* d_out_ids,
+             unsigned long long* d_stats, cudaStream_t st) {
+  FPS_REQUIRE(n_q > 0 && n_items > 0 && dim > 0, FPS_E_INVALID, "topk: empty problem");
+  FPS_REQUIRE(k >= 1 && k <= TK_MAX_K, FPS_E_TOO_LARGE, "topk: k = %d outside [1, %d]", k, TK_MAX_K);
+  FPS_REQUIRE(dim <= 128, FPS_E_UNSUPPORTED, "topk: rank %d > 128 not supported by the tile kernel", dim);
+  FPS_REQUIRE(q_stride % 4 == 0 && item_stride % 4 == 0, FPS_E_INVALID, "topk: strides must be multiples of 4 floats");
+  FPS_REQUIRE(!use_pruning || d_item_len != nullptr, FPS_E_INVALID, "topk: pruning needs item lengths");
+  const Plan p = make_plan(n_q, k, n_items, dim);
+  FPS_REQUIRE(scratch_bytes >= p.total, FPS_E_INVALID, "topk: scratch too small (%zu < %zu)", scratch_bytes, p.total);
+  uint8_t* sb = (uint8_t*)d_scratch;
+  TopkScratch sc;
+  sc.cand_s = (float*)sb;
+  sc.cand_i = (int*)(sb + p.off_cand_i);
+  sc.theta = (uint32_t*)(sb + p.off_theta);
+  sc.part_s = (float*)(sb + p.off_part_s);
+  sc.part_i = (int*)(sb + p.off_part_i);
+  // theta keys start at 0 == "below every float"
+  FPS_CUDA(cudaMemsetAsync(sc.theta, 0, (size_t)p.n_q_tiles * TK_M * sizeof(uint32_t), st));
+  const size_t a_bytes = (size_t)TK_M * p.kblks * TK_KB * 4, b_bytes = (size_t)TK_N * p.kblks * TK_KB * 4;
+  const size_t smem = 1024 + (TC ? 2 : 1) * a_bytes + 2 * b_bytes;
+  FPS_CUDA(cudaFuncSetAttribute(k_lemp_topk<TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_lemp_topk<TC><<<p.n_ctas, TK_THREADS, smem, st>>>(d_queries, q_stride, n_q, d_items, item_stride, d_item_len,
+                                                      d_item_ids, n_items, dim, p.kblks, k, p.n_splits,
+                                                      use_pruning, sc, d_stats);
+  FPS_LAUNCH_CHECK();
+  return launch_merge(sc.part_s, sc.part_i, p.n_splits, n_q, k, k, nullptr, 0, d_out_scores, d_out_ids, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t fps_topk_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items) {
+  if (n_q <= 0 || n_items <= 0 || k <= 0) return 0;
+  return make_plan(n_q, k, n_items, 128).total;
+}
+
+int fps_lemp_topk(const float* d_queries, int32_t q_stride, int64_t n_q, const float* d_items,
+                  int32_t item_stride, const float* d_item_len, const int32_t* d_item_ids, int64_t n_items,
+                  int32_t dim, int32_t k, int32_t use_pruning, void* d_scratch, size_t scratch_bytes,
+                  float* d_out_scores, int32_t* d_out_ids, uint64_t* d_stats, void* stream) {
+  return run_topk<true>(d_queries, q_stride, n_q, d_items, item_stride, d_item_len, d_item_ids, n_items, dim, k,
+                        use_pruning, d_scratch, scratch_bytes, d_out_scores, d_out_ids,
+                        (unsigned long long*)d_stats, (cudaStream_t)stream);
+}
+
+int fps_topk_simt(const float* d_queries, int32_t q_stride, int64_t n_q, const float* d_items,
+                  int32_t item_stride, const int32_t* d_item_ids, int64_t n_items, int32_t dim, int32_t k,
+                  void* d_scratch, size_t scratch_bytes, float* d_out_scores, int32_t* d_out_ids, void* stream) {
+  return run_topk<false>(d_queries, q_stride, n_q, d_items, item_stride, nullptr, d_item_ids, n_items, dim, k, 0,
+                         d_scratch, scratch_bytes, d_out_scores, d_out_ids, nullptr, (cudaStream_t)stream);
+}
+
+int fps_topk_merge(const float* d_part_scores, const int32_t* d_part_ids, int32_t n_parts, int64_t n_q,
+                   int32_t k_in, int32_t k_out, const int32_t* d_seen, int32_t seen_stride,
+                   float* d_out_scores, int32_t* d_out_ids, void* stream) {
+  FPS_REQUIRE(n_parts >= 1 && k_in >= 1 && k_out >= 1 && n_q >= 0, FPS_E_INVALID, "fps_topk_merge: bad arguments");
+  if (n_q == 0) return 0;
+  return launch_merge(d_part_scores, d_part_ids, n_parts, n_q, k_in, k_out, d_seen, seen_stride, d_out_scores,
+                      d_out_ids, (cudaStream_t)stream);
+}
+
+}  // extern "C"

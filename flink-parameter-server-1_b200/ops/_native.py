@@ -134,6 +134,7 @@ def lib() -> C.CDLL:
         "fps_mf_online_stream": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, vp, u64, vp, vp,
                                            P(FpsMfParams), C.c_uint32, C.c_uint32, vp, vp]),
         "fps_pa_step": (C.c_int, [P(FpsTableView), vp, vp, vp, vp, i64, P(FpsPaParams), vp, vp, vp]),
+        "fps_pa_step_cost": (C.c_int, [P(FpsTableView), vp, vp, vp, vp, i64, P(FpsPaParams), vp, vp, vp, vp]),
         "fps_topk_scratch_bytes": (C.c_size_t, [i64, i32, i64]),
         "fps_lemp_topk": (C.c_int, [vp, i32, i64, vp, i32, vp, vp, i64, i32, i32, i32, vp, C.c_size_t,
                                     vp, vp, vp, vp]),

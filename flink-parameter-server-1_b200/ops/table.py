@@ -30,15 +30,18 @@ class ShardedTable:
     def __init__(self, n_ids: int, dim: int, *, n_shards: Optional[int] = None, partition: str = "hash",
                  init_range: Tuple[float, float] = (0.0, 0.0), seed: int = 0,
                  stream_tag: int = philox.STREAM_ITEM, lazy: bool = False, aux_cols: int = 0,
-                 ctx=None, local_only: bool = False):
+                 ctx=None, local_only: bool = False, scalar: bool = False):
         """``local_only`` = a worker-resident table (MF user factors): sharded by the same formula
-        but a rank only ever touches its own shard, so no peer mapping is made."""
+        but a rank only ever touches its own shard, so no peer mapping is made.
+        ``scalar`` = one float per id with no padding (binary PA weights)."""
         import torch
         from ..parallel.device_context import get_context
         self.ctx = ctx or get_context()
         world = self.ctx.world_size
         self.n_ids, self.dim = int(n_ids), int(dim)
-        self.stride = padded_stride(dim, aux_cols)
+        if scalar and (dim != 1 or aux_cols):
+            raise ValueError("a scalar table has dim 1 and no aux columns")
+        self.stride = 1 if scalar else padded_stride(dim, aux_cols)
         self.aux_cols = aux_cols
         self.n_shards = int(n_shards or world)
         if world > 1 and self.n_shards != world:

@@ -1,0 +1,92 @@
+"""Python front-end of the LEMP top-K kernels (``csrc/topk.cu``).
+
+``lemp_topk`` = tensor-core path (tcgen05 / TMEM, 3xTF32), ``topk_simt`` = CUDA-core fp32 path with
+the same tiling and selection (baseline + on-device oracle), ``topk_merge`` = merge of partial
+lists with an optional seen-set filter (``CollectTopKFromEachWorker.scala:40-48``).
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+from . import _native as N
+
+
+def sort_items_by_length(items, ids=None):
+    """Length-descending order (the LEMP bucket order, ``PSTopKGeneratorWorker.scala:19``).
+    Returns ``(items_sorted, lengths_sorted, ids_sorted int32)``."""
+    import torch
+    lens = torch.linalg.vector_norm(items.float(), dim=1)
+    order = torch.argsort(lens, descending=True)
+    ids = torch.arange(items.shape[0], device=items.device, dtype=torch.int32) if ids is None else ids.int()
+    return items[order].contiguous(), lens[order].contiguous(), ids[order].contiguous()
+
+
+def _pad4(t):
+    import torch
+    if t.shape[1] % 4 == 0 and t.is_contiguous():
+        return t
+    pad = (-t.shape[1]) % 4
+    return torch.nn.functional.pad(t, (0, pad)).contiguous()
+
+
+def scratch_bytes(n_q: int, k: int, n_items: int) -> int:
+    return int(N.lib().fps_topk_scratch_bytes(n_q, k, n_items))
+
+
+def _run(fn_name: str, queries, items, k: int, item_len, item_ids, use_pruning: bool, scratch, stats):
+    import torch
+    dim = queries.shape[1]
+    assert items.shape[1] == dim, "queries and items must have the same rank"
+    q = _pad4(queries.float())
+    it = _pad4(items.float())
+    n_q, n_items = q.shape[0], it.shape[0]
+    need = scratch_bytes(n_q, k, n_items)
+    if scratch is None:
+        scratch = torch.empty(need, device="cuda", dtype=torch.uint8)
+    assert scratch.numel() >= need
+    out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
+    out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
+    L = N.lib()
+    if fn_name == "tc":
+        N.check(L.fps_lemp_topk(N.ptr(q), q.shape[1], n_q, N.ptr(it), it.shape[1], N.ptr(item_len),
+                                N.ptr(item_ids), n_items, dim, k, int(use_pruning), N.ptr(scratch),
+                                scratch.numel(), N.ptr(out_s), N.ptr(out_i), N.ptr(stats), N.current_stream()),
+                "fps_lemp_topk")
+    else:
+        N.check(L.fps_topk_simt(N.ptr(q), q.shape[1], n_q, N.ptr(it), it.shape[1], N.ptr(item_ids), n_items,
+                                dim, k, N.ptr(scratch), scratch.numel(), N.ptr(out_s), N.ptr(out_i),
+                                N.current_stream()), "fps_topk_simt")
+    return out_s, out_i
+
+
+def lemp_topk(queries, items, k: int, *, item_len=None, item_ids=None, use_pruning: bool = True,
+              scratch=None, stats=None):
+    """Top-``k`` inner products of every query against ``items`` (already sorted by length
+    descending if ``use_pruning``).  ``stats`` (uint64[4], optional): tiles scored, tiles total,
+    candidates accepted, prunes."""
+    import torch
+    if use_pruning and item_len is None:
+        item_len = torch.linalg.vector_norm(items.float(), dim=1).contiguous()
+    return _run("tc", queries, items, k, item_len, item_ids, use_pruning, scratch, stats)
+
+
+def topk_simt(queries, items, k: int, *, item_ids=None, scratch=None):
+    return _run("simt", queries, items, k, None, item_ids, False, scratch, None)
+
+
+def topk_merge(part_scores, part_ids, k_out: int, seen=None):
+    """``part_scores`` / ``part_ids``: ``[n_q, n_parts, k_in]``.  ``seen``: ``[n_q, m]`` int32 item ids
+    to drop (-1 padded)."""
+    import torch
+    n_q, n_parts, k_in = part_scores.shape
+    ps = part_scores.float().contiguous()
+    pi = part_ids.int().contiguous()
+    out_s = torch.empty((n_q, k_out), device="cuda", dtype=torch.float32)
+    out_i = torch.empty((n_q, k_out), device="cuda", dtype=torch.int32)
+    seen_stride = 0
+    if seen is not None:
+        seen = seen.int().contiguous()
+        seen_stride = seen.shape[1]
+    N.check(N.lib().fps_topk_merge(N.ptr(ps), N.ptr(pi), n_parts, n_q, k_in, k_out, N.ptr(seen), seen_stride,
+                                   N.ptr(out_s), N.ptr(out_i), N.current_stream()), "fps_topk_merge")
+    return out_s, out_i

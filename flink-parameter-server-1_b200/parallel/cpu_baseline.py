@@ -1,0 +1,82 @@
+"""BL2 front-end: the multi-threaded C++ CPU parameter server (``csrc/cpu/ps_cpu.cpp``).
+
+This is the *timed CPU baseline* that stands in for the reference's Flink mini-cluster run
+(unavailable on this box) and a second oracle for the MF maths.  Always
+report its numbers as "CPU restatement, not Flink".
+"""
+from __future__ import annotations
+
+import ctypes as C
+import pathlib
+
+import numpy as np
+
+_LIB = pathlib.Path(__file__).resolve().parent.parent / "ops" / "_lib" / "libfps_cpu.so"
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not _LIB.exists():
+            import importlib.util
+            import sys
+            root = pathlib.Path(__file__).resolve().parents[2]
+            spec = importlib.util.spec_from_file_location("build_native", root / "build_native.py")
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            mod.build()
+        L = C.CDLL(str(_LIB))
+        L.fps_cpu_mf_run.restype = C.c_double
+        L.fps_cpu_mf_run.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_double, C.c_int,
+                                     C.POINTER(C.c_double)]
+        L.fps_cpu_fill_uniform.restype = None
+        L.fps_cpu_fill_uniform.argtypes = [C.c_void_p, C.c_int64, C.c_double, C.c_double, C.c_uint64]
+        _lib = L
+    return _lib
+
+
+def run_mf(users, items, ratings, user_table, item_table, lr: float, pull_limit: int = 1600):
+    """``users`` / ``items`` / ``ratings``: ``[W, n]`` arrays (worker-local user slots, global item
+    ids); ``user_table`` ``[W, U, dim]`` and ``item_table`` ``[S, I, dim]`` fp64, updated in place.
+    Returns ``(seconds, sum of squared errors)``."""
+    users = np.ascontiguousarray(users, dtype=np.int32)
+    items = np.ascontiguousarray(items, dtype=np.int32)
+    ratings = np.ascontiguousarray(ratings, dtype=np.float32)
+    W, n = users.shape
+    S, I, dim = item_table.shape
+    assert user_table.shape[0] == W and user_table.shape[2] == dim
+    assert user_table.flags.c_contiguous and item_table.flags.c_contiguous
+    sse = C.c_double(0.0)
+    secs = lib().fps_cpu_mf_run(W, S, dim, n, users.ctypes.data, items.ctypes.data, ratings.ctypes.data,
+                                user_table.ctypes.data, user_table.shape[1], item_table.ctypes.data, I,
+                                float(lr), int(pull_limit), C.byref(sse))
+    return secs, sse.value
+
+
+def bench_mf(n_users: int, n_items: int, dim: int, batch: int, steps: int, warmup: int, workers: int,
+             shards: int, lr: float = 0.01, pull_limit: int = 1600, seed: int = 0) -> dict:
+    rng = np.random.default_rng(seed)
+    upw = (n_users + workers - 1) // workers
+    ips = (n_items + shards - 1) // shards
+    ut = np.empty((workers, upw, dim), dtype=np.float64)
+    it = np.empty((shards, ips, dim), dtype=np.float64)
+    lib().fps_cpu_fill_uniform(ut.ctypes.data, ut.size, -0.01, 0.01, 1)
+    lib().fps_cpu_fill_uniform(it.ctypes.data, it.size, -0.01, 0.01, 2)
+    n = batch // workers
+
+    def batch_arrays(k):
+        u = rng.integers(0, upw, size=(workers, n), dtype=np.int32)
+        i = (rng.random((workers, n)) ** 3 * n_items).astype(np.int32)
+        r = rng.random((workers, n), dtype=np.float32)
+        return u, i, r
+
+    for k in range(warmup):
+        run_mf(*batch_arrays(k), ut, it, lr, pull_limit)
+    total = 0.0
+    for k in range(steps):
+        secs, _ = run_mf(*batch_arrays(k), ut, it, lr, pull_limit)
+        total += secs
+    return {"ratings_per_sec": n * workers * steps / total, "ms_per_step": total / steps * 1e3,
+            "workers": workers, "shards": shards}

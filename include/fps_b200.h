@@ -171,6 +171,13 @@ int fps_pa_step(const FpsTableView* weights, const int64_t* d_indptr, const int3
                 const float* d_values, const int32_t* d_labels, int64_t n_examples,
                 const FpsPaParams* params, int32_t* d_pred, FpsFlow* d_flow, void* stream);
 
+/* Same, with an optional class-cost matrix d_cost[n_classes * n_classes] (row = true label) for
+ * the cost-based variants (PassiveAggressiveCostBased.scala:54-64); NULL = 0/1 cost.             */
+int fps_pa_step_cost(const FpsTableView* weights, const int64_t* d_indptr, const int32_t* d_indices,
+                     const float* d_values, const int32_t* d_labels, int64_t n_examples,
+                     const FpsPaParams* params, const float* d_cost, int32_t* d_pred, FpsFlow* d_flow,
+                     void* stream);
+
 /* ---- LEMP top-K (N6, N7) ---------------------------------------------------------------------- */
 /* Scores n_q queries against n_items local item rows on the tensor cores (tcgen05.mma kind::tf32,
  * 3xTF32 split for fp32 fidelity, accumulators in TMEM), prunes tiles by the length bound

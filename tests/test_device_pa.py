@@ -1,0 +1,124 @@
+"""GPU tests of the passive-aggressive kernels against the fp64 host rules."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+from fps_b200 import Left, Right, last_write_wins, lefts, rights  # noqa: E402
+from fps_b200.models.pa import (PassiveAggressiveBinaryAlgorithm, PassiveAggressiveCostBased,  # noqa: E402
+                                PassiveAggressiveOneVersusAll, SparseVector, zero_one_cost)
+from fps_b200.utils.evaluation import binary_accuracy  # noqa: E402
+
+
+def make_binary(n=80, features=5000, nnz=120, seed=50):
+    rnd = np.random.default_rng(seed)
+    w_true = rnd.normal(size=features)
+    data = []
+    for _ in range(n):
+        idx = rnd.choice(features, nnz, replace=False)
+        val = rnd.normal(size=nnz).astype(np.float32).astype(np.float64)
+        x = SparseVector(idx, val, features)
+        data.append((x, bool(x.dot(w_true) > 0)))
+    return data
+
+
+def make_multi(n=60, features=300, nnz=25, classes=7, seed=3):
+    rnd = np.random.default_rng(seed)
+    W = rnd.normal(size=(features, classes))
+    data = []
+    for _ in range(n):
+        idx = rnd.choice(features, nnz, replace=False)
+        val = rnd.normal(size=nnz).astype(np.float32).astype(np.float64)
+        x = SparseVector(idx, val, features)
+        data.append((x, int(np.argmax(W[x.indices].T @ x.values))))
+    return data
+
+
+@pytest.mark.parametrize("variant,range_part,shards", [("pa", True, 3), ("pa_i", False, 2), ("pa_ii", True, 1)])
+def test_binary_kernel_equals_serial_host_rule(variant, range_part, shards):
+    from fps_b200.models.pa.device import DevicePA
+    data = make_binary(n=40, features=3000, nnz=50)
+    algo = {"pa": PassiveAggressiveBinaryAlgorithm.build_pa(),
+            "pa_i": PassiveAggressiveBinaryAlgorithm.build_pa_i(0.05),
+            "pa_ii": PassiveAggressiveBinaryAlgorithm.build_pa_ii(0.5)}[variant]
+    C = {"pa": 1.0, "pa_i": 0.05, "pa_ii": 0.5}[variant]
+    pa = DevicePA(3000, algorithm="binary", variant=variant, aggressiveness=C,
+                  range_partitioning=range_part, n_shards=shards)
+    w = {}
+    for x, y in data:                         # one example per launch == the serial schedule
+        want_pred = algo.predict(x, w)
+        got = pa.step_vectors([x], [y]).item()
+        assert (got > 0) == want_pred or abs(sum(v * w.get(i, 0.0) for i, v in x.active_iterator())) < 1e-4
+        for i, d in algo.delta(x, w, y):
+            w[i] = w.get(i, 0.0) + d
+    dumped = dict(r.value for r in pa.dump())
+    touched = {i for x, _ in data for i in x.indices.tolist()}
+    assert set(dumped) == touched                # untouched features are not dumped
+    for i in touched:
+        assert dumped[i] == pytest.approx(w.get(i, 0.0), rel=2e-3, abs=2e-5)
+    s = pa.stats()
+    assert s["records"] == 40 and s["pulls"] == 40 * 50 and s["bad_ids"] == 0
+
+
+def test_binary_minibatch_acceptance_and_predict_stream():
+    """Reference acceptance (accuracy >= 80 % on the first 20 training vectors) with
+    asynchronous mini-batches, then unlabelled records through the same entry point."""
+    from fps_b200.models.pa.device import transform_binary_device
+    data = make_binary()
+    stream = [Left(d) for d in data] * 3 + [Right((100 + k, x)) for k, (x, _y) in enumerate(data[:20])]
+    out, pa = transform_binary_device(stream, "pa", feature_count=5000, range_partitioning=True,
+                                      batch_size=8, pull_limit=10000, n_shards=3)
+    model = last_write_wins(rights(out))
+    assert binary_accuracy(model, data[:20], PassiveAggressiveBinaryAlgorithm.build_pa()) >= 80.0
+    preds = lefts(out)
+    assert len(preds) == 20
+    agree = sum(1 for (vec, p), (_x, y) in zip(preds, data[:20]) if p == y)
+    assert agree >= 16
+    s = pa.stats()
+    assert 0 < s["max_in_flight"] <= 10000
+
+
+@pytest.mark.parametrize("algorithm", ["ova", "pb", "ml"])
+def test_multiclass_kernel_equals_serial_host_rule(algorithm):
+    from fps_b200.models.pa.device import DevicePA
+    L, F = 7, 300
+    data = make_multi(classes=L, features=F)
+    algo = {"ova": PassiveAggressiveOneVersusAll.build_pa_i(L, 0.3),
+            "pb": PassiveAggressiveCostBased.build_pb(zero_one_cost, L),
+            "ml": PassiveAggressiveCostBased.build_ml(zero_one_cost, L)}[algorithm]
+    pa = DevicePA(F, label_count=L, algorithm=algorithm, variant="pa_i", aggressiveness=0.3,
+                  range_partitioning=False, n_shards=2)
+    W = {}
+    for x, y in data:
+        pa.step_vectors([x], [y])
+        for i, d in algo.delta(x, {k: W[k] for k in x.indices.tolist() if k in W}, y):
+            W[i] = W.get(i, np.zeros(L)) + d
+    dumped = dict(r.value for r in pa.dump())
+    for i, row in W.items():
+        np.testing.assert_allclose(dumped[i], row, rtol=5e-3, atol=5e-5)
+    # prediction path uses the same decision vector
+    x0 = data[0][0]
+    pred = pa.step_vectors([x0], None).item()
+    assert pred == algo.predict(x0, {k: W[k] for k in x0.indices.tolist() if k in W})
+
+
+def test_cost_matrix_and_wide_rows():
+    """100 classes (BASELINE config 4 shape) with an explicit cost matrix; compares one update."""
+    from fps_b200.models.pa.device import DevicePA
+    L, F = 100, 2000
+    rnd = np.random.default_rng(1)
+    cost = rnd.uniform(0.5, 2.0, size=(L, L))
+    np.fill_diagonal(cost, 0.0)
+    algo = PassiveAggressiveCostBased.build_ml(lambda y, q: float(cost[y, q]), L)
+    pa = DevicePA(F, label_count=L, algorithm="ml", cost=cost, n_shards=4)
+    model0 = [(i, rnd.normal(size=L)) for i in range(0, F, 3)]
+    pa.load(model0)
+    W = {i: v.astype(np.float32).astype(np.float64) for i, v in model0}
+    x = SparseVector(rnd.choice(F, 40, replace=False), rnd.normal(size=40).astype(np.float32), F)
+    pa.step_vectors([x], [5])
+    for i, d in algo.delta(x, {k: W[k] for k in x.indices.tolist() if k in W}, 5):
+        W[i] = W.get(i, np.zeros(L)) + d
+    dumped = dict(r.value for r in pa.dump())
+    for i in x.indices.tolist():
+        np.testing.assert_allclose(dumped[i], W.get(i, np.zeros(L)), rtol=2e-3, atol=2e-4)

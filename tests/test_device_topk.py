@@ -1,0 +1,107 @@
+"""GPU tests of the tcgen05 LEMP top-K kernel, its CUDA-core twin and the merge kernel against a
+plain fp32 / fp64 PyTorch reference."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+def reference_topk(q, items, k):
+    s = q.double() @ items.double().T
+    v, i = torch.topk(s, k, dim=1)
+    return v, i
+
+
+def check_against_reference(out_s, out_i, q, items, k, ids=None, rtol=2e-5, atol=2e-5):
+    ref_v, ref_i = reference_topk(q, items, k)
+    got_s = out_s.double()
+    # scores: sorted descending and equal to the reference's
+    assert torch.all(got_s[:, :-1] >= got_s[:, 1:])
+    torch.testing.assert_close(got_s, ref_v, rtol=rtol, atol=atol)
+    # ids: every returned id really has the returned score (robust to ties / near-ties)
+    idx = out_i.long()
+    if ids is not None:
+        inv = torch.empty(int(ids.max()) + 1, dtype=torch.long, device=ids.device)
+        inv[ids.long()] = torch.arange(ids.numel(), device=ids.device)
+        idx = inv[idx]
+    true_scores = torch.gather(q.double() @ items.double().T, 1, idx)
+    torch.testing.assert_close(true_scores, got_s, rtol=rtol, atol=atol)
+    # and (almost) all of them are in the reference set
+    same = (idx.sort(dim=1).values == ref_i.sort(dim=1).values).float().mean().item()
+    assert same > 0.98, same
+
+
+@pytest.mark.parametrize("dim,n_q,n_items,k", [(10, 37, 1000, 10), (64, 200, 5000, 75), (128, 128, 4096, 100),
+                                                (128, 300, 20011, 50), (32, 1, 70, 5)])
+def test_tensor_core_topk_matches_reference(dim, n_q, n_items, k):
+    from fps_b200.ops.topk import lemp_topk, sort_items_by_length
+    g = torch.Generator(device="cuda").manual_seed(dim + n_q)
+    q = torch.randn(n_q, dim, device="cuda", generator=g)
+    items = torch.randn(n_items, dim, device="cuda", generator=g) * (0.2 + 2.0 * torch.rand(n_items, 1, device="cuda", generator=g))
+    it_s, len_s, ids_s = sort_items_by_length(items)
+    stats = torch.zeros(4, device="cuda", dtype=torch.int64)
+    out_s, out_i = lemp_topk(q, it_s, k, item_len=len_s, item_ids=ids_s, use_pruning=True, stats=stats)
+    torch.cuda.synchronize()
+    check_against_reference(out_s, out_i, q, items, k)
+    st = stats.tolist()
+    assert 0 < st[0] <= st[1]
+    # without pruning: same answer, every tile scored
+    stats.zero_()
+    out_s2, out_i2 = lemp_topk(q, it_s, k, item_ids=ids_s, use_pruning=False, stats=stats)
+    check_against_reference(out_s2, out_i2, q, items, k)
+    assert stats[0].item() == stats[1].item()
+
+
+def test_length_pruning_skips_tiles_on_skewed_lengths():
+    """LEMP's point: with a long-tailed length distribution most buckets are never scored."""
+    from fps_b200.ops.topk import lemp_topk, sort_items_by_length
+    g = torch.Generator(device="cuda").manual_seed(0)
+    dim, n_items = 64, 200_000
+    lens = torch.rand(n_items, 1, device="cuda", generator=g) ** 8 * 10 + 0.01
+    items = torch.nn.functional.normalize(torch.randn(n_items, dim, device="cuda", generator=g), dim=1) * lens
+    q = torch.randn(256, dim, device="cuda", generator=g)
+    it_s, len_s, ids_s = sort_items_by_length(items)
+    stats = torch.zeros(4, device="cuda", dtype=torch.int64)
+    out_s, out_i = lemp_topk(q, it_s, 20, item_len=len_s, item_ids=ids_s, stats=stats)
+    check_against_reference(out_s, out_i, q, items, 20)
+    scored, total = stats[0].item(), stats[1].item()
+    assert scored < 0.5 * total, (scored, total)
+
+
+def test_3xtf32_keeps_fp32_fidelity():
+    """Plain TF32 would err at ~1e-3 relative; the split keeps scores at fp32 level."""
+    from fps_b200.ops.topk import lemp_topk
+    g = torch.Generator(device="cuda").manual_seed(5)
+    q = torch.randn(128, 128, device="cuda", generator=g)
+    items = torch.randn(2048, 128, device="cuda", generator=g)
+    out_s, _ = lemp_topk(q, items, 16, use_pruning=False)
+    ref_v, _ = reference_topk(q, items, 16)
+    err = ((out_s.double() - ref_v).abs() / ref_v.abs().clamp_min(1.0)).max().item()
+    assert err < 5e-6, err
+
+
+def test_simt_twin_matches_reference():
+    from fps_b200.ops.topk import topk_simt
+    g = torch.Generator(device="cuda").manual_seed(9)
+    q = torch.randn(150, 48, device="cuda", generator=g)
+    items = torch.randn(3000, 48, device="cuda", generator=g)
+    out_s, out_i = topk_simt(q, items, 30)
+    check_against_reference(out_s, out_i, q, items, 30)
+
+
+def test_merge_with_seen_filter():
+    from fps_b200.ops.topk import topk_merge
+    g = torch.Generator(device="cuda").manual_seed(2)
+    n_q, parts, k_in = 9, 4, 75
+    ids = torch.stack([torch.randperm(100000, device="cuda", generator=g)[: parts * k_in] for _ in range(n_q)]).int()
+    scores = torch.randn(n_q, parts * k_in, device="cuda", generator=g)
+    seen = torch.full((n_q, 8), -1, device="cuda", dtype=torch.int32)
+    seen[:, 0] = ids[torch.arange(n_q), scores.argmax(dim=1)]       # hide every query's best item
+    out_s, out_i = topk_merge(scores.view(n_q, parts, k_in), ids.view(n_q, parts, k_in), 100, seen)
+    masked = scores.clone()
+    masked[torch.arange(n_q), scores.argmax(dim=1)] = -float("inf")
+    ref_v, ref_idx = torch.topk(masked, 100, dim=1)
+    torch.testing.assert_close(out_s, ref_v)
+    assert torch.equal(out_i.long(), torch.gather(ids.long(), 1, ref_idx))
+    assert not (out_i == seen[:, :1]).any()
