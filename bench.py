@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--lr", type=float, default=0.01)
     ap.add_argument("--pool", type=int, default=4, help="distinct pre-generated batches rotated through")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--unroll", type=int, default=0, help="kernel tuning: ratings in flight per sub-warp")
+    ap.add_argument("--blocks-per-sm", type=int, default=0, help="kernel tuning: persistent CTAs per SM")
     return ap.parse_args()
 
 
@@ -143,6 +145,7 @@ def main():
         from fps_b200.models.mf.device import DeviceMF
         model = DeviceMF(a.users, a.items, a.rank, -0.01, 0.01, a.lr, pull_limit=a.pull_limit, seed=7,
                          lazy=False, variant=a.variant, ctx=ctx)
+        model.params.unroll, model.params.blocks_per_sm = a.unroll, a.blocks_per_sm
         step = lambda b: model.step(*b)                      # noqa: E731
         e2e_step = lambda b: model.step_from_host(*b)        # noqa: E731
         launches_per_step = 1

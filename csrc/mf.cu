@@ -13,23 +13,44 @@ __global__ void __launch_bounds__(MF_THREADS)
 k_mf_sgd(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
          const int* __restrict__ uid, const int* __restrict__ iid, const float* __restrict__ rating,
          long long n, const FpsMfParams p, int chunk, FpsFlow* flow) {
-  constexpr int GPB = MF_THREADS / LANES;   // ratings in flight per block pass
+  constexpr int GPB = MF_THREADS / LANES;   // sub-warps per CTA
+  constexpr int STEP = GPB * UNROLL;        // ratings a CTA retires per iteration
   const int grp = threadIdx.x / LANES;
   MfCounters c;
   c.clear();
-  for (long long base = (long long)blockIdx.x * chunk; base < n; base += (long long)gridDim.x * chunk) {
-    const int cnt = (int)min((long long)chunk, n - base);
-    if (p.pull_limit > 0) flow_acquire(flow, cnt, p.pull_limit);
-    for (int k0 = 0; k0 < cnt; k0 += GPB * UNROLL) {   // warp-uniform trip count (shuffles inside)
-      const int k = k0 + grp * UNROLL;
-      MfRec<VPL> rec[UNROLL];
+  // The CTA's work is chunk c = blockIdx.x, +gridDim.x, ... ; iterations are flattened over its
+  // chunks so the ids of iteration it+1 can be fetched while the rows of iteration it are in flight.
+  const int ipc = (chunk + STEP - 1) / STEP;                          // iterations per chunk
+  const long long n_chunks = (n + chunk - 1) / chunk;
+  const long long my_chunks = n_chunks > blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const long long iters = my_chunks * ipc;
+  auto index_of = [&](long long it, int q) -> long long {
+    const long long ci = it / ipc;
+    const int k = (int)(it - ci * ipc) * STEP + grp * UNROLL + q;
+    const long long idx = ((long long)blockIdx.x + ci * gridDim.x) * chunk + k;
+    return (it < iters && k < chunk && idx < n) ? idx : -1;
+  };
+  MfIds cur[UNROLL], nxt[UNROLL];
 #pragma unroll
-      for (int q = 0; q < UNROLL; ++q)
-        mf_load<LANES, VPL, LAZY>(rec[q], items, users, uid, iid, rating, base + k + q, k + q < cnt, p.local_shard, c);
-#pragma unroll
-      for (int q = 0; q < UNROLL; ++q) mf_update<LANES, VPL, LAZY>(rec[q], items, p, c);
+  for (int q = 0; q < UNROLL; ++q) cur[q] = mf_fetch_ids(uid, iid, rating, index_of(0, q));
+  for (long long it = 0; it < iters; ++it) {
+    const int phase = (int)(it % ipc);
+    int cnt = 0;
+    if (p.pull_limit > 0) {
+      const long long base = ((long long)blockIdx.x + (it / ipc) * gridDim.x) * chunk;
+      cnt = (int)min((long long)chunk, n - base);
+      if (phase == 0) flow_acquire(flow, cnt, p.pull_limit);
     }
-    if (p.pull_limit > 0) flow_release(flow, cnt);
+#pragma unroll
+    for (int q = 0; q < UNROLL; ++q) nxt[q] = mf_fetch_ids(uid, iid, rating, index_of(it + 1, q));
+    MfRec<VPL> rec[UNROLL];
+#pragma unroll
+    for (int q = 0; q < UNROLL; ++q) mf_load_ids<LANES, VPL, LAZY>(rec[q], items, users, cur[q], p.local_shard, c);
+#pragma unroll
+    for (int q = 0; q < UNROLL; ++q) mf_update<LANES, VPL, LAZY>(rec[q], items, p, c);
+    if (p.pull_limit > 0 && phase == ipc - 1) flow_release(flow, cnt);
+#pragma unroll
+    for (int q = 0; q < UNROLL; ++q) cur[q] = nxt[q];
   }
   c.flush(flow);
 }
@@ -192,10 +213,14 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
   int chunk = MF_CHUNK;
   if (params->pull_limit > 0 && params->pull_limit < chunk) chunk = params->pull_limit;
   long long blocks = (n + chunk - 1) / chunk;
-  const long long cap = (long long)fps_num_sms() * MF_BLOCKS_PER_SM;
+  const int bps = params->blocks_per_sm > 0 ? params->blocks_per_sm : MF_BLOCKS_PER_SM;
+  const long long cap = (long long)fps_num_sms() * bps;
   if (blocks > cap) blocks = cap;
+  const int unroll = params->unroll;   // 0 = default (2)
 #define FN(L, V, Z)                                                                                   \
   if (Z) k_mf_sgd<L, V, true, 1><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow); \
+  else if (unroll == 1) k_mf_sgd<L, V, false, 1><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow); \
+  else if (unroll == 4 && V == 1) k_mf_sgd<L, V, false, (V == 1 ? 4 : 1)><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow); \
   else k_mf_sgd<L, V, false, (V <= 2 ? 2 : 1)><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow)
   MF_DISPATCH(FN);
 #undef FN

@@ -62,20 +62,40 @@ struct MfRec {
   bool valid;
 };
 
+// The (user, item, rating) triple of one record; fetched one iteration ahead of its row loads so
+// the index-load latency is off the critical path (ncu: 14 % of stall samples sat on it).
+struct MfIds {
+  int u, i;
+  float r;
+  bool active;
+};
+
+__device__ __forceinline__ MfIds mf_fetch_ids(const int* __restrict__ uid, const int* __restrict__ iid,
+                                              const float* __restrict__ rating, long long idx) {
+  MfIds d;
+  d.active = idx >= 0;
+  d.u = d.i = 0;
+  d.r = 0.f;
+  if (d.active) {
+    d.u = uid[idx];
+    d.i = iid[idx];
+    d.r = rating ? rating[idx] : 0.f;
+  }
+  return d;
+}
+
 // Pull: issue the row loads of one rating.  `touch` = register the access in the lazy life-cycle.
 template <int LANES, int VPL, bool LAZY>
-__device__ __forceinline__ void mf_load(MfRec<VPL>& rec, const FpsTableView& items, const FpsTableView& users,
-                                        const int* __restrict__ uid, const int* __restrict__ iid,
-                                        const float* __restrict__ rating, long long idx, bool active,
-                                        int local_shard, MfCounters& c, bool touch = true) {
+__device__ __forceinline__ void mf_load_ids(MfRec<VPL>& rec, const FpsTableView& items, const FpsTableView& users,
+                                            const MfIds& ids, int local_shard, MfCounters& c, bool touch = true) {
   const int lane = threadIdx.x % LANES;
   const int nvec = items.stride >> 2;
   rec.valid = false;
 #pragma unroll
   for (int q = 0; q < VPL; ++q) rec.v[q] = rec.u[q] = rec.us[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (!active) return;
-  const long long u_id = uid[idx], i_id = iid[idx];
-  rec.r = rating ? rating[idx] : 0.f;
+  if (!ids.active) return;
+  const long long u_id = ids.u, i_id = ids.i;
+  rec.r = ids.r;
   const RowRef ir = locate(items, i_id), ur = locate(users, u_id);
   if (!in_table(items, i_id, ir) || !in_table(users, u_id, ur) || users.rows[ur.owner] == nullptr) {
     if (lane == 0) ++c.bad;
@@ -128,6 +148,15 @@ __device__ __forceinline__ void mf_load(MfRec<VPL>& rec, const FpsTableView& ite
     ++c.records;
     if (ir.owner != local_shard) ++c.remote;
   }
+}
+
+template <int LANES, int VPL, bool LAZY>
+__device__ __forceinline__ void mf_load(MfRec<VPL>& rec, const FpsTableView& items, const FpsTableView& users,
+                                        const int* __restrict__ uid, const int* __restrict__ iid,
+                                        const float* __restrict__ rating, long long idx, bool active,
+                                        int local_shard, MfCounters& c, bool touch = true) {
+  const MfIds ids = mf_fetch_ids(uid, iid, rating, active ? idx : -1);
+  mf_load_ids<LANES, VPL, LAZY>(rec, items, users, ids, local_shard, c, touch);
 }
 
 // Compute + push: e = r - u.v; user row updated in place (worker-resident half), item delta

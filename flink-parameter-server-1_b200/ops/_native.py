@@ -72,7 +72,9 @@ class FpsMfParams(C.Structure):
         ("pull_limit", C.c_int32),
         ("local_shard", C.c_int32),
         ("variant", C.c_int32),
-        ("write_user_out", C.c_int32),
+        ("unroll", C.c_int32),
+        ("blocks_per_sm", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 

@@ -124,7 +124,9 @@ typedef struct FpsMfParams {
   int32_t variant;         /* 0 = direct (warp-per-rating, register path)
                               1 = staged (TMA bulk copies of rows into shared memory + mbarrier)
                               2 = direct + hot-key pre-combine in shared memory                   */
-  int32_t write_user_out;  /* reserved                                                            */
+  int32_t unroll;          /* ratings a sub-warp keeps in flight: 0 = default (2), 1, 2 or 4       */
+  int32_t blocks_per_sm;   /* persistent grid = SMs * this; 0 = default (6)                       */
+  int32_t reserved;
 } FpsMfParams;
 
 /* One fused pull-compute-push pass over n ratings: for each (user, item, r): v = pull(item) from
