@@ -157,3 +157,70 @@ extern "C" int fps_p2p_probe(float* d_dst, const float* d_src, size_t bytes, int
   cudaEventDestroy(e1);
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Random-row probe: the PS access pattern (one warp per 512-byte-ish row at a random slot inside
+// `span_rows`), to separate link bandwidth from address-translation / request-size effects.
+//   mode 0 = pull only (row load), 1 = push only (red.add.v4), 2 = pull then push on the same row
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+template <int UNROLL>
+__global__ void __launch_bounds__(256)
+probe_random_rows(float* table, long long span_rows, int row_floats, long long n_rows, int mode,
+                  unsigned long long seed, float* sink) {
+  const int lane = threadIdx.x & 31;
+  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const int nvec = row_floats >> 2;
+  float acc = 0.f;
+  for (long long r0 = warp * UNROLL; r0 < n_rows; r0 += n_warps * UNROLL) {
+    float4 v[UNROLL];
+    float* row[UNROLL];
+#pragma unroll
+    for (int q = 0; q < UNROLL; ++q) {
+      const long long slot = (long long)(mix64(seed + (unsigned long long)(r0 + q)) % (unsigned long long)span_rows);
+      row[q] = table + slot * row_floats;
+      v[q] = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (mode != 1 && lane < nvec) v[q] = ld_row4(row[q] + lane * 4);
+    }
+#pragma unroll
+    for (int q = 0; q < UNROLL; ++q) {
+      acc += v[q].x;
+      if (mode != 0 && lane < nvec) red_add4(row[q] + lane * 4, make_float4(1e-9f * v[q].x, 0.f, 0.f, 0.f));
+    }
+  }
+  if (acc == 123.456f) sink[0] = acc;
+}
+
+extern "C" int fps_p2p_probe_random(float* d_table, int64_t span_rows, int row_floats, int64_t n_rows,
+                                    int mode, int unroll, int blocks_per_sm, int iters, float* ms, void* stream) {
+  FPS_REQUIRE(row_floats % 4 == 0 && row_floats <= 128 && span_rows > 0 && iters > 0, FPS_E_INVALID,
+              "fps_p2p_probe_random: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int grid = fps_num_sms() * (blocks_per_sm > 0 ? blocks_per_sm : 8);
+  float* sink = nullptr;
+  FPS_CUDA(cudaMalloc(&sink, 256));
+  cudaEvent_t e0, e1;
+  FPS_CUDA(cudaEventCreate(&e0));
+  FPS_CUDA(cudaEventCreate(&e1));
+  for (int it = -1; it < iters; ++it) {
+    if (it == 0) FPS_CUDA(cudaEventRecord(e0, st));
+    const unsigned long long seed = 0x1234567ull * (unsigned long long)(it + 2);
+    if (unroll >= 4) probe_random_rows<4><<<grid, 256, 0, st>>>(d_table, span_rows, row_floats, n_rows, mode, seed, sink);
+    else if (unroll >= 2) probe_random_rows<2><<<grid, 256, 0, st>>>(d_table, span_rows, row_floats, n_rows, mode, seed, sink);
+    else probe_random_rows<1><<<grid, 256, 0, st>>>(d_table, span_rows, row_floats, n_rows, mode, seed, sink);
+  }
+  FPS_LAUNCH_CHECK();
+  FPS_CUDA(cudaEventRecord(e1, st));
+  FPS_CUDA(cudaEventSynchronize(e1));
+  FPS_CUDA(cudaEventElapsedTime(ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(sink);
+  return 0;
+}
