@@ -6,6 +6,11 @@
 #include "flow.cuh"
 #include "mf_core.cuh"
 
+extern "C" int fps_debug_set(int flags) {
+  FPS_CUDA(cudaMemcpyToSymbol(g_mf_dbg, &flags, sizeof(int)));
+  return 0;
+}
+
 namespace {
 
 template <int LANES, int VPL, bool LAZY, int UNROLL>

@@ -224,3 +224,61 @@ extern "C" int fps_p2p_probe_random(float* d_table, int64_t span_rows, int row_f
   cudaFree(sink);
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Mixed probe: per row, any combination of {remote load, remote red, local load, local store,
+// local red} selected by `flags`, to find which mix of apertures inside one warp is slow.
+//   bit0 remote load | bit1 remote red.add | bit2 local load | bit3 local store | bit4 local red
+//   bit5: use weak (non-.cg) local stores / loads    bit6: remote red issued BEFORE the local store
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+probe_mixed_rows(float* remote, float* local, long long span_rows, long long n_rows, int flags,
+                 unsigned long long seed, float* sink) {
+  const int lane = threadIdx.x & 31;
+  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+  float acc = 0.f;
+  for (long long r = warp; r < n_rows; r += n_warps) {
+    const unsigned long long h = mix64(seed + (unsigned long long)r);
+    float* rr = remote + (long long)(h % (unsigned long long)span_rows) * 128 + lane * 4;
+    float* lr = local + (long long)((h >> 20) % (unsigned long long)span_rows) * 128 + lane * 4;
+    float4 a = make_float4(1.f, 1.f, 1.f, 1.f), b = a;
+    if (flags & 1) a = ld_row4(rr);
+    if (flags & 4) b = (flags & 32) ? *reinterpret_cast<const float4*>(lr) : ld_row4(lr);
+    const float4 d = make_float4(1e-6f * (a.x + b.x), 1e-6f, 0.f, 0.f);
+    acc += a.x + b.x;
+    if (flags & 128) acc += a.y + a.z + a.w + b.y + b.z + b.w;   // keeps the loads 128-bit wide
+    if ((flags & 2) && (flags & 64)) red_add4(rr, d);
+    if (flags & 8) {
+      if (flags & 32) *reinterpret_cast<float4*>(lr) = d; else st_row4(lr, d);
+    }
+    if (flags & 16) red_add4(lr, d);
+    if ((flags & 2) && !(flags & 64)) red_add4(rr, d);
+  }
+  if (acc == 123.456f) sink[0] = acc;
+}
+
+extern "C" int fps_p2p_probe_mixed(float* d_remote, float* d_local, int64_t span_rows, int64_t n_rows,
+                                   int flags, int iters, float* ms, void* stream) {
+  FPS_REQUIRE(span_rows > 0 && iters > 0 && ms != nullptr, FPS_E_INVALID, "fps_p2p_probe_mixed: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int grid = fps_num_sms() * 8;
+  float* sink = nullptr;
+  FPS_CUDA(cudaMalloc(&sink, 256));
+  cudaEvent_t e0, e1;
+  FPS_CUDA(cudaEventCreate(&e0));
+  FPS_CUDA(cudaEventCreate(&e1));
+  for (int it = -1; it < iters; ++it) {
+    if (it == 0) FPS_CUDA(cudaEventRecord(e0, st));
+    probe_mixed_rows<<<grid, 256, 0, st>>>(d_remote, d_local, span_rows, n_rows, flags,
+                                           0x9876543ull * (unsigned long long)(it + 2), sink);
+  }
+  FPS_LAUNCH_CHECK();
+  FPS_CUDA(cudaEventRecord(e1, st));
+  FPS_CUDA(cudaEventSynchronize(e1));
+  FPS_CUDA(cudaEventElapsedTime(ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(sink);
+  return 0;
+}

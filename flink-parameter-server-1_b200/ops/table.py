@@ -16,10 +16,22 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from typing import List, Optional, Tuple
 
 from . import _native as N
 from . import philox
+
+
+def _symm_alloc(shape, dtype, ctx, keep: list):
+    """Allocate a symmetric (same shape on every rank) VMM buffer and return
+    ``(local tensor, [base pointer on rank 0, 1, ...])``."""
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm
+    t = symm.empty(shape, dtype=dtype, device=ctx.device)
+    hdl = symm.rendezvous(t, ctx.group if ctx.group is not None else dist.group.WORLD)
+    keep.append((t, hdl))
+    return t, [int(p) for p in hdl.buffer_ptrs]
 
 
 def padded_stride(dim: int, aux_cols: int = 0) -> int:
@@ -30,7 +42,8 @@ class ShardedTable:
     def __init__(self, n_ids: int, dim: int, *, n_shards: Optional[int] = None, partition: str = "hash",
                  init_range: Tuple[float, float] = (0.0, 0.0), seed: int = 0,
                  stream_tag: int = philox.STREAM_ITEM, lazy: bool = False, aux_cols: int = 0,
-                 ctx=None, local_only: bool = False, scalar: bool = False):
+                 ctx=None, local_only: bool = False, scalar: bool = False,
+                 peer_mapping: Optional[str] = None):
         """``local_only`` = a worker-resident table (MF user factors): sharded by the same formula
         but a rank only ever touches its own shard, so no peer mapping is made.
         ``scalar`` = one float per id with no padding (binary PA weights)."""
@@ -59,27 +72,44 @@ class ShardedTable:
         self._bufs: dict = {}
         self._state_bufs: dict = {}
         self._peer_ptrs: List[int] = []
+        self._symm = []               # keeps symmetric-memory handles alive
         self.rows: dict = {}
         self.state: dict = {}
-        for s in self.local_shards:
-            b = N.DeviceBuffer(self.rows_per_shard * self.stride * 4)
-            self._bufs[s] = b
-            self.rows[s] = b.tensor((self.rows_per_shard, self.stride), "<f4")
-            if self.lazy:
-                sb = N.DeviceBuffer(((self.rows_per_shard + 3) // 4) * 4)
-                self._state_bufs[s] = sb
-                self.state[s] = sb.tensor((((self.rows_per_shard + 3) // 4) * 4,), "|u1")
         self._view = N.FpsTableView()
         v = self._view
         v.n_shards, v.dim, v.stride, v.partition = self.n_shards, self.dim, self.stride, self.partition
         v.div, v.rows_per_shard = self.div, self.rows_per_shard
         v.init_lo, v.init_hi = self.init_range
         v.seed, v.stream_tag, v.lazy = self.seed, self.stream_tag, int(self.lazy)
-        for s in self.local_shards:
-            v.rows[s] = self._bufs[s].ptr
-            v.state[s] = self._state_bufs[s].ptr if self.lazy else None
-        if world > 1 and not local_only:
-            self._map_peers()
+        n_state = ((self.rows_per_shard + 3) // 4) * 4
+        shared = world > 1 and not local_only
+        self.peer_mapping = (peer_mapping or os.environ.get("FPS_PEER_MAPPING", "vmm")) if shared else "none"
+        if shared and self.peer_mapping == "vmm":
+            # cuMem (VMM) allocations exchanged through torch symmetric memory.  Measured on 2xB200:
+            # random 512-byte rows over a 2.4 GB peer shard run at the NVLink rate (2.2 ms / 2M rows)
+            # through this mapping but 8x slower (17 ms) through cudaIpcOpenMemHandle mappings, which
+            # collapse once the randomly accessed span exceeds ~1 GB (profiles/r1_2gpu/ipc_vs_vmm.md).
+            me = self.ctx.rank
+            self.rows[me], ptrs = _symm_alloc((self.rows_per_shard, self.stride), torch.float32, self.ctx, self._symm)
+            for r in range(world):
+                v.rows[r] = ptrs[r]
+            if self.lazy:
+                self.state[me], sptrs = _symm_alloc((n_state,), torch.uint8, self.ctx, self._symm)
+                for r in range(world):
+                    v.state[r] = sptrs[r]
+        else:
+            for s in self.local_shards:
+                b = N.DeviceBuffer(self.rows_per_shard * self.stride * 4)
+                self._bufs[s] = b
+                self.rows[s] = b.tensor((self.rows_per_shard, self.stride), "<f4")
+                v.rows[s] = b.ptr
+                if self.lazy:
+                    sb = N.DeviceBuffer(n_state)
+                    self._state_bufs[s] = sb
+                    self.state[s] = sb.tensor((n_state,), "|u1")
+                    v.state[s] = sb.ptr
+            if shared:
+                self._map_peers_ipc()
         if self.lazy:
             for s in self.local_shards:
                 self.rows[s].zero_()
@@ -90,7 +120,9 @@ class ShardedTable:
         self.ctx.barrier()
 
     # -- peer mapping ------------------------------------------------------------------------
-    def _map_peers(self) -> None:
+    def _map_peers_ipc(self) -> None:
+        """Legacy path (``peer_mapping="ipc"``): cudaMalloc + cudaIpc handles.  Correct, but slow
+        for random access over large shards - kept for comparison and for small tables."""
         me = self.ctx.rank
         mine = (self._bufs[me].ipc_handle(), self._state_bufs[me].ipc_handle() if self.lazy else None)
         handles = self.ctx.all_gather_object(mine)

@@ -1,0 +1,92 @@
+"""GPU tests of the device job front-ends that compose kernels: top-K generator, prequential
+learner+generator, model dump / load round trip (checkpoint-resume), P2P probes on one GPU."""
+import random
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+from fps_b200 import Left, Right, last_write_wins, lefts, rights  # noqa: E402
+from fps_b200.models.mf import Rating, attach_length  # noqa: E402
+
+
+def test_topk_generator_device_matches_brute_force():
+    from fps_b200.models.mf.device_topk import ps_top_k_generator_device
+    rng = np.random.default_rng(5)
+    k, n_items, n_users = 16, 3000, 40
+    items = rng.normal(size=(n_items, k)).astype(np.float32)
+    users = rng.normal(size=(n_users, k)).astype(np.float32)
+    model = [Left((u, attach_length(users[u]))) for u in range(n_users)] + \
+            [Right((i, attach_length(items[i]))) for i in range(n_items)]
+    queries = [Rating(u, 0, 1.0, 100 + u) for u in range(n_users)] + [Rating(n_users + 5, 0, 1.0, 7)]
+    res = ps_top_k_generator_device(queries, model, num_factors=k, K=10, worker_k=10, user_memory=-1,
+                                    n_users=n_users + 10)
+    by_ts = {ts: topk for (_item, ts, topk) in res}
+    for u in range(n_users):
+        want = np.argsort(-(items.astype(np.float64) @ users[u].astype(np.float64)))[:10]
+        got = [i for _s, i in by_ts[100 + u]]
+        assert len(set(got) & set(want.tolist())) >= 9
+        assert got[0] == want[0]
+    assert by_ts[7] == []                       # unknown user -> empty recommendation
+
+
+def test_learner_generator_device_prequential():
+    from fps_b200.models.mf.device_topk import ps_online_learner_and_generator_device
+    from fps_b200.utils.evaluation import NDCGSink
+    rnd = random.Random(2)
+    # users have a favourite group of items; the model should learn to rank them
+    stream = []
+    for t in range(3000):
+        u = rnd.randrange(50)
+        item = (u % 5) * 20 + rnd.randrange(20)
+        stream.append(Rating(u, item, 1.0, t))
+    out, lg = ps_online_learner_and_generator_device(
+        stream, n_users=50, n_items=100, batch_size=100, num_factors=8, range_min=-0.1, range_max=0.1,
+        learning_rate=0.1, negative_sample_rate=3, K=10, worker_k=10, user_memory=4, pull_limit=500)
+    assert len(out) == len(stream)
+    early = NDCGSink().consume(out[200:700]).hit_rate
+    late = NDCGSink().consume(out[-500:]).hit_rate
+    assert late > early and late > 0.3, (early, late)
+    s = lg.stats()
+    assert s["records"] > len(stream) and s["max_in_flight"] <= 500 and s["nan_count"] == 0
+
+
+def test_dump_load_round_trip_resumes_training():
+    """Checkpoint = the output stream; resume = load() (transform_with_double_model_load)."""
+    from fps_b200.models.mf.device import DeviceMF
+    g = torch.Generator().manual_seed(0)
+    n = 20_000
+    u = torch.randint(0, 500, (n,), generator=g, dtype=torch.int32).cuda()
+    i = torch.randint(0, 300, (n,), generator=g, dtype=torch.int32).cuda()
+    r = torch.rand(n, generator=g).cuda()
+    a = DeviceMF(500, 300, 12, 0.0, 0.2, 0.05, lazy=True, n_shards=3)
+    for _ in range(3):
+        a.step(u, i, r)
+    ckpt = a.dump()
+    b = DeviceMF(500, 300, 12, -9.0, 9.0, 0.05, lazy=True, n_shards=2, seed=99)   # different init and sharding
+    b.load(ckpt)
+    ua, ia = last_write_wins(lefts(ckpt)), last_write_wins(rights(ckpt))
+    ckpt_b = b.dump()
+    ub, ib = last_write_wins(lefts(ckpt_b)), last_write_wins(rights(ckpt_b))
+    assert ua.keys() == ub.keys() and ia.keys() == ib.keys()
+    for k in ua:
+        np.testing.assert_allclose(ub[k], ua[k], rtol=0, atol=1e-6)
+    for k in ia:
+        np.testing.assert_allclose(ib[k], ia[k], rtol=0, atol=1e-6)
+    assert abs(a.rmse(u, i, r) - b.rmse(u, i, r)) < 1e-5
+
+
+def test_probes_run_on_one_gpu():
+    import ctypes as C
+    from fps_b200.ops import _native as N
+    buf = N.DeviceBuffer(64 << 20)
+    t = buf.tensor((64 << 18,))
+    t.zero_()
+    ms = C.c_float()
+    for mode in (0, 1, 2):
+        N.check(N.lib().fps_p2p_probe(buf.ptr, buf.ptr, 64 << 20, mode, 2, C.byref(ms), N.current_stream()))
+        assert ms.value > 0
+    torch.cuda.synchronize()
+    assert float(t[:4].sum()) != 0.0            # stores / reds really landed
