@@ -531,3 +531,66 @@ int fps_topk_merge(const float* d_part_scores, const int32_t* d_part_ids, int32_
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// fps_lemp_topk_static: the same retrieval for callers that must not allocate.
+//
+// Who that is: a serving loop that answers queries while a training job (or another framework's
+// caching allocator) already owns all the device memory it is going to get, so a cudaMalloc in
+// the request path can fail at an arbitrary moment; and latency-sensitive callers for whom the
+// device-wide synchronisation that cudaMalloc / cudaFree imply is a stall they cannot afford per
+// request.  Such callers bring their inputs and outputs; the candidate buffers, the shared theta
+// array and the partial lists (the kernel's scratch) live in the fixed array below instead of a
+// caller- or library-allocated buffer.
+//
+// * The array is part of the module image: every GPU that loads the library carries these
+//   FPS_TOPK_STATIC_SCRATCH_BYTES until the process exits, used or not.
+// * Problems whose scratch need (fps_topk_scratch_bytes) exceeds the array are refused with
+//   FPS_E_TOO_LARGE; nothing is allocated as a fallback.  16 MiB covers up to 256 queries per call.
+// * The first call on a device looks the array's device address up (one-time set-up, under a
+//   mutex); make that first call outside any stream capture.
+// * All calls on a device share the one array and it keeps whatever the previous call left in it.
+//   The only part that must start clean - the shared theta keys - is cleared on the call's stream
+//   before the kernel.  Two calls whose GPU work overlaps (different streams, or different host
+//   threads) would write the same candidate slots: serialise them on one stream.
+// * No cudaMalloc, cudaFree, or allocating library routine is called on this path.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_topk_static_scratch[FPS_TOPK_STATIC_SCRATCH_BYTES];
+
+namespace {
+std::mutex g_static_mu;
+void* g_static_ptr[64] = {nullptr};   // device address of the array, per device ordinal
+}  // namespace
+
+extern "C" int fps_lemp_topk_static(const float* d_queries, int32_t q_stride, int64_t n_q, const float* d_items,
+                                    int32_t item_stride, const float* d_item_len, const int32_t* d_item_ids,
+                                    int64_t n_items, int32_t dim, int32_t k, int32_t use_pruning,
+                                    float* d_out_scores, int32_t* d_out_ids, uint64_t* d_stats, void* stream) {
+  FPS_REQUIRE(n_q > 0 && n_items > 0 && k >= 1, FPS_E_INVALID, "fps_lemp_topk_static: empty problem");
+  const size_t need = fps_topk_scratch_bytes(n_q, k, n_items);
+  FPS_REQUIRE(need <= (size_t)FPS_TOPK_STATIC_SCRATCH_BYTES, FPS_E_TOO_LARGE,
+              "fps_lemp_topk_static: %lld queries x k=%d need %zu bytes of scratch, the built-in array holds %u; "
+              "split the query batch or use fps_lemp_topk with your own scratch",
+              (long long)n_q, (int)k, need, (unsigned)FPS_TOPK_STATIC_SCRATCH_BYTES);
+  int dev = 0;
+  FPS_CUDA(cudaGetDevice(&dev));
+  FPS_REQUIRE(dev >= 0 && dev < 64, FPS_E_UNSUPPORTED, "fps_lemp_topk_static: device ordinal %d not supported", dev);
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (g_static_ptr[dev] == nullptr) {
+      // In host code the array's name is only a stand-in; the address a kernel can use has to be
+      // asked for, once per device, with that device current.
+      void* p = nullptr;
+      FPS_CUDA(cudaGetSymbolAddress((void**)&p, g_topk_static_scratch));
+      FPS_REQUIRE(p != nullptr, FPS_E_UNSUPPORTED, "fps_lemp_topk_static: no device address for the scratch array");
+      g_static_ptr[dev] = p;
+    }
+    scratch = g_static_ptr[dev];
+  }
+  return run_topk<true>(d_queries, q_stride, n_q, d_items, item_stride, d_item_len, d_item_ids, n_items, dim, k,
+                        use_pruning, scratch, (size_t)FPS_TOPK_STATIC_SCRATCH_BYTES, d_out_scores, d_out_ids,
+                        (unsigned long long*)d_stats, (cudaStream_t)stream);
+}

@@ -195,6 +195,20 @@ int fps_lemp_topk(const float* d_queries, int32_t q_stride, int64_t n_q,
                   const int32_t* d_item_ids, int64_t n_items, int32_t dim, int32_t k,
                   int32_t use_pruning, void* d_scratch, size_t scratch_bytes,
                   float* d_out_scores, int32_t* d_out_ids, uint64_t* d_stats, void* stream);
+/* fps_lemp_topk for callers that cannot allocate device memory - no counterpart in the reference.
+ * Meant for request paths where a cudaMalloc may fail (all device memory is already spoken for by
+ * a training job or another allocator) or would stall (it synchronises the device).  The scratch
+ * lives in an array built into the library (FPS_TOPK_STATIC_SCRATCH_BYTES, held by every GPU that
+ * loads the library); a problem needing more than that (fps_topk_scratch_bytes; about 256 queries
+ * per call) is refused with FPS_E_TOO_LARGE.  Calls share the array: issue them on one stream, never
+ * overlapping.  The first call on each device does a one-time address look-up and should be made
+ * outside stream capture.  Results are identical to fps_lemp_topk.                                */
+#define FPS_TOPK_STATIC_SCRATCH_BYTES (16u << 20)
+int fps_lemp_topk_static(const float* d_queries, int32_t q_stride, int64_t n_q,
+                         const float* d_items, int32_t item_stride, const float* d_item_len,
+                         const int32_t* d_item_ids, int64_t n_items, int32_t dim, int32_t k,
+                         int32_t use_pruning, float* d_out_scores, int32_t* d_out_ids,
+                         uint64_t* d_stats, void* stream);
 /* CUDA-core fp32 reference scorer with the same interface (baseline + oracle on device).          */
 int fps_topk_simt(const float* d_queries, int32_t q_stride, int64_t n_q,
                   const float* d_items, int32_t item_stride, const int32_t* d_item_ids,
