@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--unroll", type=int, default=0, help="kernel tuning: ratings in flight per sub-warp")
     ap.add_argument("--blocks-per-sm", type=int, default=0, help="kernel tuning: persistent CTAs per SM")
+    ap.add_argument("--min-blocks", type=int, default=0, help="kernel tuning: 8 = 32-register build of unroll 1")
     return ap.parse_args()
 
 
@@ -146,6 +147,7 @@ def main():
         model = DeviceMF(a.users, a.items, a.rank, -0.01, 0.01, a.lr, pull_limit=a.pull_limit, seed=7,
                          lazy=False, variant=a.variant, ctx=ctx)
         model.params.unroll, model.params.blocks_per_sm = a.unroll, a.blocks_per_sm
+        model.params.reserved = a.min_blocks
         step = lambda b: model.step(*b)                      # noqa: E731
         e2e_step = lambda b: model.step_from_host(*b)        # noqa: E731
         launches_per_step = 1

@@ -6,56 +6,30 @@
 #include "flow.cuh"
 #include "mf_core.cuh"
 
-extern "C" int fps_debug_set(int flags) {
-  FPS_CUDA(cudaMemcpyToSymbol(g_mf_dbg, &flags, sizeof(int)));
-  return 0;
-}
-
 namespace {
 
-template <int LANES, int VPL, bool LAZY, int UNROLL>
-__global__ void __launch_bounds__(MF_THREADS)
+template <int LANES, int VPL, bool LAZY, int UNROLL, int MINB = 1>
+__global__ void __launch_bounds__(MF_THREADS, MINB)
 k_mf_sgd(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
          const int* __restrict__ uid, const int* __restrict__ iid, const float* __restrict__ rating,
          long long n, const FpsMfParams p, int chunk, FpsFlow* flow) {
-  constexpr int GPB = MF_THREADS / LANES;   // sub-warps per CTA
-  constexpr int STEP = GPB * UNROLL;        // ratings a CTA retires per iteration
+  constexpr int GPB = MF_THREADS / LANES;   // ratings in flight per block pass
   const int grp = threadIdx.x / LANES;
   MfCounters c;
   c.clear();
-  // The CTA's work is chunk c = blockIdx.x, +gridDim.x, ... ; iterations are flattened over its
-  // chunks so the ids of iteration it+1 can be fetched while the rows of iteration it are in flight.
-  const int ipc = (chunk + STEP - 1) / STEP;                          // iterations per chunk
-  const long long n_chunks = (n + chunk - 1) / chunk;
-  const long long my_chunks = n_chunks > blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  const long long iters = my_chunks * ipc;
-  auto index_of = [&](long long it, int q) -> long long {
-    const long long ci = it / ipc;
-    const int k = (int)(it - ci * ipc) * STEP + grp * UNROLL + q;
-    const long long idx = ((long long)blockIdx.x + ci * gridDim.x) * chunk + k;
-    return (it < iters && k < chunk && idx < n) ? idx : -1;
-  };
-  MfIds cur[UNROLL], nxt[UNROLL];
+  for (long long base = (long long)blockIdx.x * chunk; base < n; base += (long long)gridDim.x * chunk) {
+    const int cnt = (int)min((long long)chunk, n - base);
+    if (p.pull_limit > 0) flow_acquire(flow, cnt, p.pull_limit);
+    for (int k0 = 0; k0 < cnt; k0 += GPB * UNROLL) {   // warp-uniform trip count (shuffles inside)
+      const int k = k0 + grp * UNROLL;
+      MfRec<VPL> rec[UNROLL];
 #pragma unroll
-  for (int q = 0; q < UNROLL; ++q) cur[q] = mf_fetch_ids(uid, iid, rating, index_of(0, q));
-  for (long long it = 0; it < iters; ++it) {
-    const int phase = (int)(it % ipc);
-    int cnt = 0;
-    if (p.pull_limit > 0) {
-      const long long base = ((long long)blockIdx.x + (it / ipc) * gridDim.x) * chunk;
-      cnt = (int)min((long long)chunk, n - base);
-      if (phase == 0) flow_acquire(flow, cnt, p.pull_limit);
+      for (int q = 0; q < UNROLL; ++q)
+        mf_load<LANES, VPL, LAZY>(rec[q], items, users, uid, iid, rating, base + k + q, k + q < cnt, p.local_shard, c);
+#pragma unroll
+      for (int q = 0; q < UNROLL; ++q) mf_update<LANES, VPL, LAZY>(rec[q], items, p, c);
     }
-#pragma unroll
-    for (int q = 0; q < UNROLL; ++q) nxt[q] = mf_fetch_ids(uid, iid, rating, index_of(it + 1, q));
-    MfRec<VPL> rec[UNROLL];
-#pragma unroll
-    for (int q = 0; q < UNROLL; ++q) mf_load_ids<LANES, VPL, LAZY>(rec[q], items, users, cur[q], p.local_shard, c);
-#pragma unroll
-    for (int q = 0; q < UNROLL; ++q) mf_update<LANES, VPL, LAZY>(rec[q], items, p, c);
-    if (p.pull_limit > 0 && phase == ipc - 1) flow_release(flow, cnt);
-#pragma unroll
-    for (int q = 0; q < UNROLL; ++q) cur[q] = nxt[q];
+    if (p.pull_limit > 0) flow_release(flow, cnt);
   }
   c.flush(flow);
 }
@@ -218,17 +192,33 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
   int chunk = MF_CHUNK;
   if (params->pull_limit > 0 && params->pull_limit < chunk) chunk = params->pull_limit;
   long long blocks = (n + chunk - 1) / chunk;
-  const int bps = params->blocks_per_sm > 0 ? params->blocks_per_sm : MF_BLOCKS_PER_SM;
+  // not persistent by default: with 4-8 resident CTAs per SM a grid of exactly 6 per SM ran 1.5
+  // waves (1.80 ms vs 1.55 ms); many short CTAs load-balance better than a tuned persistent grid
+  const int bps = params->blocks_per_sm > 0 ? params->blocks_per_sm : 64;
   const long long cap = (long long)fps_num_sms() * bps;
   if (blocks > cap) blocks = cap;
-  const int unroll = params->unroll;   // 0 = default (2)
+  if (params->pull_limit > 0) {
+    // With a limiter only ~pull_limit / chunk CTAs can hold credits at a time; launching thousands
+    // more just makes them fight over the counter (measured: 102 ms instead of ~10 ms per 4M
+    // ratings at limit 1600).  Twice that many keeps the limiter engaged without the stampede.
+    const long long useful = 2 * ((long long)params->pull_limit / chunk > 0 ? (long long)params->pull_limit / chunk : 1);
+    if (blocks > useful) blocks = useful;
+  }
+  const int unroll = params->unroll;   // 0 = default
+#define MF_ARGS <<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow)
+  // Default for eager tables up to rank 128: one rating per sub-warp, 32 registers, 8 CTAs/SM (64
+  // resident warps).  Measured on B200 (4.19M ratings, rank 128): 1.37 ms vs 1.55 ms for the
+  // 2-ratings-per-sub-warp build at 56 registers - thread-level parallelism hides the row-load
+  // latency better than per-warp ILP here.  `unroll` = 2 / 4 select the ILP builds explicitly.
 #define FN(L, V, Z)                                                                                   \
-  if (Z) k_mf_sgd<L, V, true, 1><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow); \
-  else if (unroll == 1) k_mf_sgd<L, V, false, 1><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow); \
-  else if (unroll == 4 && V == 1) k_mf_sgd<L, V, false, (V == 1 ? 4 : 1)><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow); \
-  else k_mf_sgd<L, V, false, (V <= 2 ? 2 : 1)><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow)
+  if (Z) k_mf_sgd<L, V, true, 1> MF_ARGS;                                                             \
+  else if (unroll == 4 && V == 1) k_mf_sgd<L, V, false, (V == 1 ? 4 : 1)> MF_ARGS;                    \
+  else if (unroll == 2 || V > 1) k_mf_sgd<L, V, false, (V <= 2 ? 2 : 1)> MF_ARGS;                     \
+  else if (params->reserved == 6) k_mf_sgd<L, V, false, 1> MF_ARGS;                                   \
+  else k_mf_sgd<L, V, false, 1, (V == 1 ? 8 : 1)> MF_ARGS
   MF_DISPATCH(FN);
 #undef FN
+#undef MF_ARGS
   FPS_LAUNCH_CHECK();
   return 0;
 }

@@ -6,10 +6,6 @@
 #define MF_CHUNK 256          // ratings a CTA handles per credit acquisition
 #define MF_BLOCKS_PER_SM 6
 
-// Debug switches for bisecting the memory path (set with fps_debug_set; 0 in production):
-// bit0 skip item-row load, bit1 skip item-row red, bit2 skip user-row load, bit3 skip user-row store.
-static __device__ int g_mf_dbg = 0;   // per translation unit; mf.cu owns the one that matters
-
 struct MfCounters {
   float loss;
   unsigned int records, remote, nan, bad;
@@ -112,8 +108,8 @@ __device__ __forceinline__ void mf_load_ids(MfRec<VPL>& rec, const FpsTableView&
   for (int q = 0; q < VPL; ++q) {
     const int b = lane + q * LANES;
     if (b < nvec) {
-      rec.v[q] = (g_mf_dbg & 1) ? make_float4(0.01f, 0.01f, 0.01f, 0.01f) : ld_row4(rec.vrow + b * 4);
-      rec.us[q] = (g_mf_dbg & 4) ? make_float4(0.01f, 0.01f, 0.01f, 0.01f) : ld_row4(rec.urow + b * 4);
+      rec.v[q] = ld_row4(rec.vrow + b * 4);
+      rec.us[q] = ld_row4(rec.urow + b * 4);
     } else {
       rec.v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
       rec.us[q] = rec.v[q];
@@ -195,8 +191,8 @@ __device__ __forceinline__ void mf_update(MfRec<VPL>& rec, const FpsTableView& i
       dv.y = fmaf(g, u.y, -decay * v.y);
       dv.z = fmaf(g, u.z, -decay * v.z);
       dv.w = fmaf(g, u.w, -decay * v.w);
-      if (!(g_mf_dbg & 8)) st_row4(rec.urow + b * 4, un);
-      if (!(g_mf_dbg & 2)) red_add4(rec.vrow + b * 4, dv);
+      st_row4(rec.urow + b * 4, un);
+      red_add4(rec.vrow + b * 4, dv);
     }
   }
   if (lane == 0) c.loss += e * e;

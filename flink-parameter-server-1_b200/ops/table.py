@@ -228,4 +228,6 @@ def read_flow(flow) -> dict:
     """Copy the flow block to the host and decode it."""
     raw = bytes(flow.cpu().numpy().tobytes())
     f = N.FpsFlow.from_buffer_copy(raw)
-    return {name: getattr(f, name) for name, _ in N.FpsFlow._fields_ if name != "reserved"}
+    d = {name: getattr(f, name) for name, _ in N.FpsFlow._fields_ if name != "reserved"}
+    d["combined_rows"] = int(f.reserved[0])      # item rows really pulled/pushed by the combine variant
+    return d

@@ -74,7 +74,7 @@ typedef struct FpsFlow {
   uint64_t  ring_done;               /* streaming kernel: records fully retired                  */
   int32_t   exit_reason;             /* 1 idle timeout, 2 stop flag, 3 lifetime cap              */
   int32_t   combined_groups;         /* hot-key groups pre-combined in shared memory             */
-  uint64_t  reserved[18];
+  uint64_t  reserved[18];            /* [0] = item rows actually pulled by the combine variant   */
 } FpsFlow;
 
 const char* fps_last_error(void);

@@ -64,11 +64,12 @@ def main():
             report("A probe " + nm, ms.value / 3)
         report("C0 MF all_local", time_steps(lambda: mf.step(users, local_items, ratings)))
         report("C1 MF all_remote (table, local_shard=rank)", time_steps(lambda: mf.step(users, remote_items, ratings)))
-        for dbg, nm in ((1, "no item load"), (2, "no item red"), (3, "no item load/red"), (4 | 8, "no user load/store"),
+        for dbg, nm in () if not hasattr(L, "fps_debug_set") else ((1, "no item load"), (2, "no item red"), (3, "no item load/red"), (4 | 8, "no user load/store"),
                         (1 | 4 | 8, "only item red"), (2 | 4 | 8, "only item load"), (8, "no user store"), (4, "no user load")):
             N.check(L.fps_debug_set(dbg))
             report(f"C MF all_remote dbg[{nm}]", time_steps(lambda: mf.step(users, remote_items, ratings)))
-        N.check(L.fps_debug_set(0))
+        if hasattr(L, "fps_debug_set"):
+            N.check(L.fps_debug_set(0))
         for span in (1 << 17, 1 << 19, 1 << 21, 5_000_000):
             it = ((base % span) * world + (rank + 1) % world).int().cuda()
             report(f"D MF all_remote span {span * 512 >> 20} MB", time_steps(lambda: mf.step(users, it, ratings)))

@@ -177,6 +177,54 @@ def test_nan_guard_counts_instead_of_poisoning(native):
     assert torch.isfinite(mf.items.gather(torch.arange(10))).all()
 
 
+@pytest.mark.parametrize("dim,shards", [(16, 1), (64, 3), (128, 2)])
+def test_combine_variant_equals_oracle_and_combines_hot_keys(native, dim, shards):
+    """Sorted, run-carrying kernel: exact on a conflict-free schedule; on a skewed batch it pulls
+    far fewer item rows than it processes records and still learns like the direct kernel."""
+    from fps_b200.models.mf.device import DeviceMF, conflict_free_waves
+    rng = np.random.default_rng(dim)
+    nu, ni, n = 400, 150, 3000
+    u = rng.integers(0, nu, n).astype(np.int32)
+    i = rng.integers(0, ni, n).astype(np.int32)
+    r = rng.random(n).astype(np.float32)
+    mf = DeviceMF(nu, ni, dim, 0.0, 0.3, 0.05, lambda_=0.01, n_shards=shards, seed=5, variant="combine")
+    U0 = mf.users.expected_init(np.arange(nu))
+    V0 = mf.items.expected_init(np.arange(ni))
+    du, di, dr = (torch.from_numpy(x).cuda() for x in (u, i, r))
+    ou, oi, orr = [], [], []
+    for wu, wi, wv in conflict_free_waves(du, di, dr):
+        mf.step(wu, wi, wv)
+        # inside a wave every item is distinct, so the kernel's sorted order is a valid serial order
+        order = torch.argsort(wi, stable=True)
+        ou += wu[order].tolist(); oi += wi[order].tolist(); orr += wv[order].tolist()
+    torch.cuda.synchronize()
+    U, V = serial_sgd_oracle(ou, oi, orr, U0, V0, 0.05, 0.01)
+    s = mf.stats()
+    assert s["records"] == n and s["bad_ids"] == 0 and s["combined_rows"] == n
+    np.testing.assert_allclose(mf.items.gather(torch.arange(ni)).cpu().numpy(), V, rtol=2e-4, atol=2e-5)
+    np.testing.assert_allclose(mf.users.gather(torch.arange(nu)).cpu().numpy(), U, rtol=2e-4, atol=2e-5)
+
+    # skewed Hogwild batch: compare with the direct kernel
+    g = torch.Generator().manual_seed(3)
+    m = 200_000
+    uu = torch.randint(0, 20_000, (m,), generator=g, dtype=torch.int32).cuda()
+    ii = (torch.rand(m, generator=g) ** 3 * 5_000).int().cuda()
+    rr = (0.5 + 0.3 * torch.sin(uu.float()) * torch.cos(ii.float())).cuda()
+    res = {}
+    for variant in ("direct", "combine"):
+        m2 = DeviceMF(20_000, 5_000, dim, 0.0, 0.5 / dim ** 0.5, 0.01, n_shards=shards, seed=9, variant=variant,
+                      pull_limit=1600)
+        for _ in range(8):
+            m2.step(uu, ii, rr)
+        torch.cuda.synchronize()
+        res[variant] = (m2.rmse(uu, ii, rr), m2.stats(check_nan=False))
+        assert res[variant][1]["nan_count"] == 0, (variant, res[variant][1])
+    assert res["combine"][1]["records"] == 8 * m and res["combine"][1]["max_in_flight"] <= 1600
+    assert res["combine"][1]["combined_rows"] < 0.8 * 8 * m           # hot keys really were combined
+    assert abs(res["combine"][0] - res["direct"][0]) < 0.05, res
+    assert res["combine"][0] < 0.4
+
+
 def test_streaming_kernel_idle_timeout_and_results(native):
     """N2: persistent ring consumer exits by itself after iteration_wait_ms of idleness."""
     from fps_b200.models.mf.device import DeviceMF
