@@ -36,7 +36,8 @@ def parse():
     ap.add_argument("--items", type=int, default=10_000_000)
     ap.add_argument("--rank", type=int, default=128, help="number of factors")
     ap.add_argument("--item-dist", default="movielens", choices=["movielens", "uniform"])
-    ap.add_argument("--variant", default="direct", choices=["direct", "staged", "combine"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "direct", "staged", "combine"],
+                    help="auto = direct on one GPU, combine (hot-key pre-combining) when items are sharded over several")
     ap.add_argument("--pull-limit", type=int, default=0)
     ap.add_argument("--lr", type=float, default=0.01)
     ap.add_argument("--pool", type=int, default=4, help="distinct pre-generated batches rotated through")
@@ -231,7 +232,7 @@ def main():
             "config": {"model": f"mf_sgd_rank{a.rank}_{a.users}x{a.items}",
                        "global_batch": a.batch * world, "seq_len": None,
                        "parallelism": f"w{world}xps{world}", "item_dist": a.item_dist,
-                       "variant": a.variant if a.impl == "ours" else None, "pull_limit": a.pull_limit,
+                       "variant": model.variant if a.impl == "ours" else None, "pull_limit": a.pull_limit,
                        "l2": f"working set per step {hbm_bytes * 2 // 5 >> 20} MiB of random rows >> 126 MB L2; "
                              f"{a.pool} distinct batches rotated"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * a.steps,
