@@ -1,0 +1,238 @@
+#!/usr/bin/env python
+"""The other BASELINE.json configs (bench.py covers config 5, the headline):
+
+  1  offline SGD MF, rank 10, MovieLens-100K-shaped (943 users x 1682 items, 100K ratings), 10 epochs
+     - device engine vs the C++ CPU restatement with workerParallelism = psParallelism = 4
+  2  online (streaming) SGD MF, rank 64, MovieLens-20M-shaped stream (138K users x 27K items)
+  3  binary passive-aggressive, RCV1-shaped (47 236 features, ~75 nnz), pull limiter on
+  4  multiclass passive-aggressive (one-vs-all), 100 classes, 1M features, ~100 nnz
+  6  LEMP top-K retrieval, rank 128, 1M items: tcgen05 kernel vs the CUDA-core twin vs torch matmul+topk
+
+    python benchmarks/run_configs.py [--configs 1,2,3,4,6] [--out gpurun_out/configs.jsonl]
+    torchrun --nproc-per-node N benchmarks/run_configs.py --configs 2,3,4       (multi-GPU)
+
+Synthetic data of the named shapes, random-init parameters, CUDA-event timing (max over ranks),
+3 warm-up + 10 timed launches unless stated.  One JSON line per config (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from fps_b200.parallel.device_context import init_context  # noqa: E402
+
+
+def timed(fn, warmup=3, steps=10):
+    import torch.distributed as dist
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist.is_initialized():
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / steps], device="cuda", dtype=torch.float64)
+    if dist.is_initialized():
+        dist.barrier()
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def zipf_items(n, n_items, g, power=3.0):
+    return (torch.rand(n, generator=g, dtype=torch.float64) ** power * n_items).long().clamp_(max=n_items - 1)
+
+
+def config1(ctx):
+    """Offline MF rank 10 on ML-100K-shaped data: whole job = 10 epochs over 100K ratings."""
+    from fps_b200.models.mf.device import DeviceMF
+    from fps_b200.parallel import cpu_baseline
+    nu, ni, n, dim, epochs = 943, 1682, 100_000, 10, 10
+    g = torch.Generator().manual_seed(1)
+    u = torch.randint(0, nu, (n,), generator=g).int()
+    i = zipf_items(n, ni, g, 2.0).int()
+    truth_u, truth_i = torch.randn(nu, 4, generator=g), torch.randn(ni, 4, generator=g)
+    r = ((truth_u[u.long()] * truth_i[i.long()]).sum(1) * 0.1 + 0.6).clamp(0.2, 1.0).float()   # stars / 5
+    out = {"config": 1, "what": "offline MF rank 10, ML-100K-shaped, 10 epochs", "ratings_per_job": n * epochs}
+    if ctx.world_size == 1:
+        mf = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=0, seed=1, ctx=ctx, variant="direct")
+        du, di, dr = u.cuda(), i.cuda(), r.cuda()
+
+        def job():
+            for _ in range(epochs):
+                mf.step(du, di, dr)
+        ms = timed(job, 2, 5)
+        fresh = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=0, seed=1, ctx=ctx, variant="direct")
+        for _ in range(epochs):
+            fresh.step(du, di, dr)
+        st = fresh.stats(check_nan=False)
+        out.update(device_ms_per_job=ms, device_ratings_per_sec=n * epochs / ms * 1e3,
+                   rmse_after_10_epochs=fresh.rmse(du, di, dr), nan_count=st["nan_count"])
+        # CPU restatement, W = PS = 4 (the reference's own parallelism for this config)
+        W = S = 4
+        per = n // W
+        uw = np.zeros((W, per), np.int32)
+        iw = np.zeros((W, per), np.int32)
+        rw = np.zeros((W, per), np.float32)
+        un, inn, rn = u.numpy(), i.numpy(), r.numpy()
+        for w in range(W):
+            idx = np.nonzero(un % W == w)[0][:per]
+            uw[w, : len(idx)] = un[idx] // W
+            iw[w, : len(idx)] = inn[idx]
+            rw[w, : len(idx)] = rn[idx]
+        ut = np.random.default_rng(0).uniform(-0.01, 0.01, (W, (nu + W - 1) // W, dim))
+        it = np.random.default_rng(1).uniform(-0.01, 0.01, (S, (ni + S - 1) // S, dim))
+        secs = 0.0
+        for _ in range(epochs):
+            s, _sse = cpu_baseline.run_mf(uw, iw, rw, ut, it, 0.01, 1600)
+            secs += s
+        out.update(cpu_restatement_ms_per_job=secs * 1e3, cpu_restatement_ratings_per_sec=per * W * epochs / secs,
+                   cpu_note="C++ restatement of the PS loop (not Flink), 4 worker + 4 server threads, fp64")
+    return out
+
+
+def config2(ctx):
+    """Online MF rank 64, ML-20M-shaped stream, micro-batches of 1M ratings per GPU."""
+    from fps_b200.models.mf.device import DeviceMF
+    nu, ni, dim, B = 138_493, 26_744, 64, 1 << 20
+    W, rank = ctx.world_size, ctx.rank
+    mf = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=0, seed=2, ctx=ctx)
+    g = torch.Generator().manual_seed(2 + rank)
+    batches = []
+    for _ in range(4):
+        u = (torch.randint(0, (nu + W - 1) // W, (B,), generator=g) * W + rank).clamp_(max=nu - 1)
+        u = u - ((u - rank) % W)
+        batches.append((u.int().cuda(), zipf_items(B, ni, g).int().cuda(), (torch.rand(B, generator=g) * 4 + 1).cuda()))
+    k = [0]
+
+    def step():
+        mf.step(*batches[k[0] % 4])
+        k[0] += 1
+    ms = timed(step, 3, 20)
+    return {"config": 2, "what": "online MF rank 64, ML-20M-shaped stream", "n_gpus": W, "variant": mf.variant,
+            "batch_per_gpu": B, "ms_per_step": ms, "ratings_per_sec": B * W / ms * 1e3}
+
+
+def _csr_batch(n_ex, n_feat, nnz, g, device):
+    idx = torch.randint(0, n_feat, (n_ex, nnz), generator=g)
+    idx = torch.sort(idx, dim=1).values
+    val = torch.randn(n_ex, nnz, generator=g)
+    indptr = torch.arange(0, (n_ex + 1) * nnz, nnz, dtype=torch.int64)
+    return indptr.to(device), idx.reshape(-1).int().to(device), val.reshape(-1).float().to(device)
+
+
+def config3(ctx):
+    """Binary PA on RCV1-shaped vectors (47 236 features, 75 nnz), pull limiter 10 000."""
+    from fps_b200.models.pa.device import DevicePA
+    F, nnz, B = 47_236, 75, 1 << 17
+    pa = DevicePA(F, algorithm="binary", variant="pa_i", aggressiveness=1.0, range_partitioning=True,
+                  pull_limit=0, lazy=False, ctx=ctx)
+    g = torch.Generator().manual_seed(3 + ctx.rank)
+    indptr, idx, val = _csr_batch(B, F, nnz, g, "cuda")
+    lab = (torch.randint(0, 2, (B,), generator=g) * 2 - 1).int().cuda()
+    ms = timed(lambda: pa.step(indptr, idx, val, lab), 3, 20)
+    pa.params.pull_limit = 10_000
+    ms_lim = timed(lambda: pa.step(indptr, idx, val, lab), 2, 5)
+    s = pa.stats()
+    return {"config": 3, "what": "binary PA-I, RCV1-shaped (47K features, 75 nnz)", "n_gpus": ctx.world_size,
+            "examples_per_gpu": B, "ms_per_step": ms, "examples_per_sec": B * ctx.world_size / ms * 1e3,
+            "pull_rows_per_sec": B * nnz * ctx.world_size / ms * 1e3,
+            "with_pull_limit_10000": {"ms_per_step": ms_lim, "max_in_flight": s["max_in_flight"]}}
+
+
+def config4(ctx):
+    """Multiclass one-vs-all PA, 100 classes, 1M features, 100 nnz."""
+    from fps_b200.models.pa.device import DevicePA
+    F, L, nnz, B = 1_000_000, 100, 100, 1 << 15
+    pa = DevicePA(F, label_count=L, algorithm="ova", variant="pa_i", aggressiveness=0.1,
+                  range_partitioning=True, pull_limit=0, lazy=False, ctx=ctx)
+    g = torch.Generator().manual_seed(4 + ctx.rank)
+    indptr, idx, val = _csr_batch(B, F, nnz, g, "cuda")
+    lab = torch.randint(0, L, (B,), generator=g).int().cuda()
+    ms = timed(lambda: pa.step(indptr, idx, val, lab), 3, 20)
+    rows = B * nnz * ctx.world_size
+    return {"config": 4, "what": "multiclass OVA PA-I, 100 classes, 1M features, 100 nnz", "n_gpus": ctx.world_size,
+            "examples_per_gpu": B, "ms_per_step": ms, "examples_per_sec": B * ctx.world_size / ms * 1e3,
+            "pull_rows_per_sec": rows / ms * 1e3, "push_rows_per_sec": rows / ms * 1e3,
+            "row_bytes": L * 4, "gather_scatter_gbs": rows * L * 4 * 3 / ms / 1e6}
+
+
+def config6(ctx):
+    """LEMP top-K, rank 128: 4096 queries x 1M items, k = 100."""
+    from fps_b200.ops.topk import lemp_topk, sort_items_by_length, topk_simt
+    if ctx.world_size > 1:
+        return {"config": 6, "skipped": "single-GPU kernel benchmark"}
+    dim, n_q, n_items, k = 128, 4096, 1_000_000, 100
+    g = torch.Generator(device="cuda").manual_seed(6)
+    q = torch.randn(n_q, dim, device="cuda", generator=g)
+    lens = torch.rand(n_items, 1, device="cuda", generator=g) ** 4 * 5 + 0.05       # long-tailed lengths
+    items = torch.nn.functional.normalize(torch.randn(n_items, dim, device="cuda", generator=g), dim=1) * lens
+    it_s, len_s, ids_s = sort_items_by_length(items)
+    stats = torch.zeros(4, device="cuda", dtype=torch.int64)
+    out = {"config": 6, "what": f"LEMP top-{k}, rank {dim}, {n_q} queries x {n_items} items"}
+    ms_p = timed(lambda: lemp_topk(q, it_s, k, item_len=len_s, item_ids=ids_s, use_pruning=True, stats=stats), 2, 5)
+    st = stats.tolist()
+    ms_np = timed(lambda: lemp_topk(q, it_s, k, item_ids=ids_s, use_pruning=False), 1, 3)
+    ms_simt = timed(lambda: topk_simt(q, it_s, k, item_ids=ids_s), 1, 2)
+
+    def torch_ref():
+        best_v = best_i = None
+        for s in range(0, n_items, 1 << 17):
+            sc = q @ it_s[s:s + (1 << 17)].T
+            v, i = sc.topk(k, dim=1)
+            i = i + s
+            if best_v is None:
+                best_v, best_i = v, i
+            else:
+                cv, ci = torch.cat([best_v, v], 1), torch.cat([best_i, i], 1)
+                best_v, sel = cv.topk(k, dim=1)
+                best_i = torch.gather(ci, 1, sel)
+        return best_v
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ms_torch = timed(torch_ref, 1, 3)
+    flops = 2.0 * n_q * n_items * dim
+    out.update(tcgen05_pruned_ms=ms_p, tiles_scored_fraction=st[0] / max(st[1], 1), tcgen05_all_tiles_ms=ms_np,
+               tcgen05_all_tiles_tflops_fp32_equiv=flops / ms_np / 1e9, cuda_core_twin_ms=ms_simt,
+               torch_fp32_matmul_topk_ms=ms_torch, queries_per_sec_pruned=n_q / ms_p * 1e3)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", default="1,2,3,4,6")
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "configs.jsonl"))
+    a = ap.parse_args()
+    ctx = init_context()
+    fns = {1: config1, 2: config2, 3: config3, 4: config4, 6: config6}
+    os.makedirs(os.path.dirname(a.out), exist_ok=True)
+    for c in [int(x) for x in a.configs.split(",")]:
+        try:
+            res = fns[c](ctx)
+        except Exception as e:  # noqa: BLE001
+            res = {"config": c, "error": repr(e)[:400]}
+        if ctx.rank == 0:
+            line = json.dumps(res)
+            print(line, flush=True)
+            with open(a.out, "a") as f:
+                f.write(line + "\n")
+        torch.cuda.synchronize()
+        ctx.barrier()
+    if ctx.distributed:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
