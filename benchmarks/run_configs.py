@@ -186,6 +186,18 @@ def config6(ctx):
     st = stats.tolist()
     ms_np = timed(lambda: lemp_topk(q, it_s, k, item_ids=ids_s, use_pruning=False), 1, 3)
     ms_simt = timed(lambda: topk_simt(q, it_s, k, item_ids=ids_s), 1, 2)
+    from fps_b200.ops.topk import PackedItems, lemp_topk_packed
+    t0 = time.time()
+    packed = PackedItems(it_s, len_s, ids_s)
+    torch.cuda.synchronize()
+    pack_ms = (time.time() - t0) * 1e3
+    stats.zero_()
+    ms_pk_p = timed(lambda: lemp_topk_packed(q, packed, k, use_pruning=True, stats=stats), 2, 5)
+    st2 = stats.tolist()
+    ms_pk_np = timed(lambda: lemp_topk_packed(q, packed, k, use_pruning=False), 1, 3)
+    out.update(packed_pipeline_all_tiles_ms=ms_pk_np, packed_pipeline_pruned_ms=ms_pk_p,
+               packed_tiles_scored_fraction=st2[0] / max(st2[1], 1), pack_once_ms=pack_ms,
+               packed_all_tiles_tflops_fp32_equiv=2.0 * n_q * n_items * dim / ms_pk_np / 1e9)
 
     def torch_ref():
         best_v = best_i = None

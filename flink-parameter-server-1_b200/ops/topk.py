@@ -70,6 +70,44 @@ def lemp_topk(queries, items, k: int, *, item_len=None, item_ids=None, use_pruni
     return _run("tc", queries, items, k, item_len, item_ids, use_pruning, scratch, stats)
 
 
+class PackedItems:
+    """Item matrix pre-split (tf32 hi / lo) and pre-swizzled into 64-item tiles - the image the
+    tensor cores read.  Built once per model refresh (``fps_topk_pack_items``), then streamed by
+    the TMA engine on every query batch (``lemp_topk_packed``).  Costs 2x the fp32 item bytes."""
+
+    def __init__(self, items_sorted, item_len=None, item_ids=None):
+        import torch
+        it = _pad4(items_sorted.float())
+        self.n_items, self.dim = it.shape[0], items_sorted.shape[1]
+        nbytes = int(N.lib().fps_topk_packed_bytes(self.n_items, self.dim))
+        if nbytes == 0:
+            raise ValueError("packed top-K supports ranks up to 128")
+        self.data = torch.empty(nbytes, device="cuda", dtype=torch.uint8)
+        N.check(N.lib().fps_topk_pack_items(N.ptr(it), it.shape[1], self.n_items, self.dim, N.ptr(self.data),
+                                            N.current_stream()), "fps_topk_pack_items")
+        self.item_len = (torch.linalg.vector_norm(items_sorted.float(), dim=1) if item_len is None else item_len).contiguous()
+        self.item_ids = None if item_ids is None else item_ids.int().contiguous()
+
+
+def lemp_topk_packed(queries, packed: PackedItems, k: int, *, use_pruning: bool = True, scratch=None, stats=None):
+    """Same result as ``lemp_topk`` on the items ``packed`` was built from (sorted by length
+    descending when ``use_pruning``)."""
+    import torch
+    assert queries.shape[1] == packed.dim
+    q = _pad4(queries.float())
+    n_q = q.shape[0]
+    need = scratch_bytes(n_q, k, packed.n_items)
+    if scratch is None:
+        scratch = torch.empty(need, device="cuda", dtype=torch.uint8)
+    out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
+    out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
+    N.check(N.lib().fps_lemp_topk_packed(N.ptr(q), q.shape[1], n_q, N.ptr(packed.data), N.ptr(packed.item_len),
+                                         N.ptr(packed.item_ids), packed.n_items, packed.dim, k, int(use_pruning),
+                                         N.ptr(scratch), scratch.numel(), N.ptr(out_s), N.ptr(out_i), N.ptr(stats),
+                                         N.current_stream()), "fps_lemp_topk_packed")
+    return out_s, out_i
+
+
 def topk_simt(queries, items, k: int, *, item_ids=None, scratch=None):
     return _run("simt", queries, items, k, None, item_ids, False, scratch, None)
 

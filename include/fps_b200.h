@@ -195,6 +195,19 @@ int fps_lemp_topk(const float* d_queries, int32_t q_stride, int64_t n_q,
                   const int32_t* d_item_ids, int64_t n_items, int32_t dim, int32_t k,
                   int32_t use_pruning, void* d_scratch, size_t scratch_bytes,
                   float* d_out_scores, int32_t* d_out_ids, uint64_t* d_stats, void* stream);
+/* Second-generation path: pack the (length-sorted) items once into per-tile tf32 hi/lo images in
+ * the swizzled layout the tensor cores read (2x the fp32 bytes; fps_topk_packed_bytes), then score
+ * query batches with fps_lemp_topk_packed, which streams the tiles with TMA bulk copies into a
+ * warp-specialised tcgen05 pipeline (double-buffered TMEM accumulators).  Same results, same
+ * scratch contract as fps_lemp_topk.                                                              */
+size_t fps_topk_packed_bytes(int64_t n_items, int32_t dim);
+int fps_topk_pack_items(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim,
+                        void* d_packed, void* stream);
+int fps_lemp_topk_packed(const float* d_queries, int32_t q_stride, int64_t n_q, const void* d_packed,
+                         const float* d_item_len, const int32_t* d_item_ids, int64_t n_items,
+                         int32_t dim, int32_t k, int32_t use_pruning, void* d_scratch,
+                         size_t scratch_bytes, float* d_out_scores, int32_t* d_out_ids,
+                         uint64_t* d_stats, void* stream);
 /* fps_lemp_topk for callers that cannot allocate device memory - no counterpart in the reference.
  * Meant for request paths where a cudaMalloc may fail (all device memory is already spoken for by
  * a training job or another allocator) or would stall (it synchronises the device).  The scratch
