@@ -19,8 +19,10 @@
 
 namespace {
 
-constexpr int TP_THREADS = 160;       // 4 selection warps + 1 issuer warp
-constexpr int TP_TMEM_COLS = 128;     // two 64-column accumulators
+constexpr int TP_THREADS = 192;       // 4 selection warps + TMA producer warp + MMA issuer warp
+constexpr int TP_TMEM_COLS = 512;     // 2 x 64 accumulator columns + 2 x 128 query (hi, lo) columns
+constexpr int TP_A_COL = 128;         // first TMEM column of the query operand
+constexpr int TP_STAGES = 3;          // shared-memory stages of packed item tiles (64 KB each at rank 128)
 
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
@@ -79,13 +81,42 @@ k_pack_items(const float* __restrict__ items, int stride, long long n_items, int
 }
 
 struct PackedShared {
-  uint64_t b_full;          // TMA landed the tile
-  uint64_t acc_full[2];     // MMAs of the tile using accumulator b are complete
-  uint64_t acc_empty[2];    // all four selection warps have read accumulator b
+  uint64_t b_full[TP_STAGES];      // TMA landed the tile in stage s
+  uint64_t stage_free[TP_STAGES];  // the MMAs that read stage s are complete
+  uint64_t acc_full[2];            // MMAs of the tile using accumulator b are complete
+  uint64_t acc_empty[2];           // all four selection warps have read accumulator b
   uint32_t tmem;
-  volatile int skip_from[4];   // per selection warp: first tile ordinal that may be skipped
-  volatile int issued_final;   // number of tiles the issuer really issued (-1 while running)
+  volatile int skip_from[4];       // per selection warp: first tile ordinal that may be skipped
+  volatile int issued_final;       // number of tiles the producer really fetched (-1 while running)
 };
+
+// 32 consecutive TMEM columns of this thread's lane <- registers
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+      "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      ::"r"(taddr),
+        "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+        "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+        "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+        "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15])),
+        "r"(__float_as_uint(v[16])), "r"(__float_as_uint(v[17])), "r"(__float_as_uint(v[18])), "r"(__float_as_uint(v[19])),
+        "r"(__float_as_uint(v[20])), "r"(__float_as_uint(v[21])), "r"(__float_as_uint(v[22])), "r"(__float_as_uint(v[23])),
+        "r"(__float_as_uint(v[24])), "r"(__float_as_uint(v[25])), "r"(__float_as_uint(v[26])), "r"(__float_as_uint(v[27])),
+        "r"(__float_as_uint(v[28])), "r"(__float_as_uint(v[29])), "r"(__float_as_uint(v[30])), "r"(__float_as_uint(v[31]))
+      : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]^T : the query operand never touches shared memory
+__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 
 __global__ void __launch_bounds__(TP_THREADS, 1)
 k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_q,
@@ -94,10 +125,8 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
                    int use_pruning, TopkScratch sc, unsigned long long* __restrict__ stats) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  const int a_floats = TK_M * kblks * TK_KB, b_floats = TK_N * kblks * TK_KB;
-  float* sA_hi = (float*)base;
-  float* sA_lo = sA_hi + a_floats;
-  float* sB = sA_lo + a_floats;            // [hi | lo], exactly one packed tile
+  const int b_floats = TK_N * kblks * TK_KB;
+  float* sB = (float*)base;                 // TP_STAGES x [hi | lo] packed tiles
   __shared__ PackedShared sh;
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
@@ -107,10 +136,14 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
   const long long n_tiles = (n_items + TK_N - 1) / TK_N;
   const int my_tiles = n_tiles > split ? (int)((n_tiles - split + n_splits - 1) / n_splits) : 0;
   const uint32_t tile_bytes = (uint32_t)(2 * b_floats * sizeof(float));
+  const int stage_floats = 2 * b_floats;
 
   if (warp == 4) tmem_alloc((uint32_t*)&sh.tmem, TP_TMEM_COLS);
   if (t == 0) {
-    mbar_init(&sh.b_full, 1);
+    for (int s = 0; s < TP_STAGES; ++s) {
+      mbar_init(&sh.b_full[s], 1);
+      mbar_init(&sh.stage_free[s], 1);
+    }
     mbar_init(&sh.acc_full[0], 1);
     mbar_init(&sh.acc_full[1], 1);
     mbar_init(&sh.acc_empty[0], 4);
@@ -119,58 +152,93 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
     for (int w = 0; w < 4; ++w) sh.skip_from[w] = 0x7fffffff;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  // queries -> shared (hi / lo, swizzled) once per CTA; the 128 selection threads do it
-  if (t < TK_THREADS) stage_tile<true>(sA_hi, sA_lo, queries + q0 * q_stride, q_stride, TK_M, q_valid, dim, kblks);
-  float qlen = 0.f;
-  if (t < q_valid) {
-    const float* qp = queries + (q0 + t) * q_stride;
-    float s = 0.f;
-    for (int j = 0; j < dim; ++j) s = fmaf(qp[j], qp[j], s);
-    qlen = sqrtf(s);
-  }
   tc_fence_before();
-  fence_async_smem();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = sh.tmem;
+  // TMEM map: columns [0,128) two accumulators, [128,256) query hi, [256,384) query lo
+  const uint32_t tmem_a_hi = tmem_base + TP_A_COL, tmem_a_lo = tmem_base + TP_A_COL + 128;
+
+  // ---- queries -> TMEM (thread t = lane t = query t), split into tf32 hi / lo on the way
+  float qlen = 0.f;
+  if (warp < 4) {
+    const float* qp = queries + (q0 + t) * q_stride;
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+    float s = 0.f;
+    for (int c0 = 0; c0 < kblks * TK_KB; c0 += 32) {
+      float hi[32], lo[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int col = c0 + j;
+        const float x = (t < q_valid && col < dim) ? qp[col] : 0.f;
+        s = fmaf(x, x, s);
+        hi[j] = to_tf32(x);
+        lo[j] = to_tf32(x - hi[j]);
+      }
+      tmem_st32(tmem_a_hi + lane_off + c0, hi);
+      tmem_st32(tmem_a_lo + lane_off + c0, lo);
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    qlen = sqrtf(s);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
 
   if (warp == 4) {
-    // ===================== issuer: TMA + MMA, one elected lane =====================
+    // ===================== producer: TMA bulk copies of packed tiles =====================
     if (lane == 0) {
       int issued = 0;
       for (int j = 0; j < my_tiles; ++j) {
-        if (j > 0) mbar_wait(&sh.acc_full[(j - 1) & 1], ((j - 1) >> 1) & 1);   // MMA(j-1) done: sB is free
+        const int s = j % TP_STAGES, n = j / TP_STAGES;
+        if (n > 0) mbar_wait(&sh.stage_free[s], (n - 1) & 1);
         if (use_pruning) {
           const int s0 = sh.skip_from[0], s1 = sh.skip_from[1], s2 = sh.skip_from[2], s3 = sh.skip_from[3];
           if (s0 <= j && s1 <= j && s2 <= j && s3 <= j) break;                // LEMP early exit
         }
         const long long tile = split + (long long)j * n_splits;
-        const float* src = packed + tile * 2 * (long long)b_floats;
-        mbar_expect_tx(&sh.b_full, tile_bytes);
+        const float* src = packed + tile * (long long)stage_floats;
+        float* dst = sB + (size_t)s * stage_floats;
+        mbar_expect_tx(&sh.b_full[s], tile_bytes);
         for (int part = 0; part < 2 * kblks; ++part)       // 8 KB per copy
-          tma_bulk_g2s(sB + part * TK_N * TK_KB, src + part * TK_N * TK_KB, TK_N * TK_KB * 4, &sh.b_full);
-        mbar_wait(&sh.b_full, j & 1);
-        if (j >= 2) mbar_wait(&sh.acc_empty[j & 1], ((j >> 1) - 1) & 1);      // accumulator drained
-        tc_fence_after();
-        const uint32_t acc_addr = tmem_base + (uint32_t)(j & 1) * TK_N;
-        uint32_t acc = 0;
-        for (int kb = 0; kb < kblks; ++kb) {
-#pragma unroll
-          for (int ks = 0; ks < TK_KB / 8; ++ks) {
-            const uint32_t a_off = (uint32_t)(kb * TK_M * TK_KB + ks * 8) * 4, b_off = (uint32_t)(kb * TK_N * TK_KB + ks * 8) * 4;
-            const uint64_t ah = make_desc(smem_u32(sA_hi) + a_off), al = make_desc(smem_u32(sA_lo) + a_off);
-            const uint64_t bh = make_desc(smem_u32(sB) + b_off), bl = make_desc(smem_u32(sB + b_floats) + b_off);
-            umma_tf32(acc_addr, al, bh, TK_IDESC, acc);
-            umma_tf32(acc_addr, ah, bl, TK_IDESC, 1);
-            umma_tf32(acc_addr, ah, bh, TK_IDESC, 1);
-            acc = 1;
-          }
-        }
-        umma_commit(&sh.acc_full[j & 1]);
+          tma_bulk_g2s(dst + part * TK_N * TK_KB, src + part * TK_N * TK_KB, TK_N * TK_KB * 4, &sh.b_full[s]);
         issued = j + 1;
       }
       __threadfence_block();
       sh.issued_final = issued;
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      for (int j = 0; j < my_tiles; ++j) {
+        const int s = j % TP_STAGES, n = j / TP_STAGES;
+        bool have = false;
+        while (true) {
+          if (mbar_try(&sh.b_full[s], n & 1)) { have = true; break; }
+          const int fin = sh.issued_final;
+          if (fin >= 0 && j >= fin) break;
+        }
+        if (!have) break;
+        if (j >= 2) mbar_wait(&sh.acc_empty[j & 1], ((j >> 1) - 1) & 1);      // accumulator drained
+        tc_fence_after();
+        const uint32_t acc_addr = tmem_base + (uint32_t)(j & 1) * TK_N;
+        const float* bh_s = sB + (size_t)s * stage_floats;
+        uint32_t acc = 0;
+        for (int kb = 0; kb < kblks; ++kb) {
+#pragma unroll
+          for (int ks = 0; ks < TK_KB / 8; ++ks) {
+            const uint32_t a_col = (uint32_t)(kb * TK_KB + ks * 8);
+            const uint32_t b_off = (uint32_t)(kb * TK_N * TK_KB + ks * 8) * 4;
+            const uint64_t bh = make_desc(smem_u32(bh_s) + b_off), bl = make_desc(smem_u32(bh_s + b_floats) + b_off);
+            umma_tf32_ts(acc_addr, tmem_a_lo + a_col, bh, TK_IDESC, acc);   // small terms first
+            umma_tf32_ts(acc_addr, tmem_a_hi + a_col, bl, TK_IDESC, 1);
+            umma_tf32_ts(acc_addr, tmem_a_hi + a_col, bh, TK_IDESC, 1);
+            acc = 1;
+          }
+        }
+        umma_commit(&sh.stage_free[s]);
+        umma_commit(&sh.acc_full[j & 1]);
+      }
     }
   } else {
     // ===================== selection warps =====================
@@ -182,7 +250,7 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
     unsigned long long tiles_done = 0, accepted = 0, prunes = 0;
     for (int j = 0; j < my_tiles; ++j) {
       const int b = j & 1;
-      // wait for tile j, or learn that the issuer stopped before it
+      // wait for tile j, or learn that the producer stopped before it
       bool have = false;
       while (true) {
         if (mbar_try(&sh.acc_full[b], (j >> 1) & 1)) { have = true; break; }
@@ -302,7 +370,8 @@ int fps_lemp_topk_packed(const float* d_queries, int32_t q_stride, int64_t n_q, 
   sc.part_i = (int*)(sb + p.off_part_i);
   FPS_CUDA(cudaMemsetAsync(sc.theta, 0, (size_t)p.n_q_tiles * TK_M * sizeof(uint32_t), st));
   const size_t a_bytes = (size_t)TK_M * p.kblks * TK_KB * 4, b_bytes = (size_t)TK_N * p.kblks * TK_KB * 4;
-  const size_t smem = 1024 + 2 * a_bytes + 2 * b_bytes;
+  (void)a_bytes;
+  const size_t smem = 1024 + (size_t)TP_STAGES * 2 * b_bytes;
   FPS_CUDA(cudaFuncSetAttribute(k_lemp_topk_packed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   k_lemp_topk_packed<<<p.n_ctas, TP_THREADS, smem, st>>>(d_queries, q_stride, n_q, (const float*)d_packed, d_item_len,
                                                          d_item_ids, n_items, dim, p.kblks, k, p.n_splits,

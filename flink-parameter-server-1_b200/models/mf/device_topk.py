@@ -26,7 +26,7 @@ import numpy as np
 from ...ops import _native as N
 from ...ops import philox
 from ...ops.table import ShardedTable, new_flow, read_flow
-from ...ops.topk import lemp_topk, sort_items_by_length, topk_merge
+from ...ops.topk import PackedItems, lemp_topk, lemp_topk_packed, sort_items_by_length, topk_merge
 
 
 class _LocalItems:
@@ -37,10 +37,19 @@ class _LocalItems:
         self.rows = self.lens = self.ids = None
 
     def refresh(self, ids, rows) -> None:
+        self.packed = None
         if ids.numel() == 0:
             self.rows = self.lens = self.ids = None
             return
         self.rows, self.lens, self.ids = sort_items_by_length(rows.contiguous(), ids.int())
+        if self.rows.shape[1] <= 128:
+            # one-time split + swizzle so that every query batch streams the tiles with TMA
+            self.packed = PackedItems(self.rows, self.lens, self.ids)
+
+    def topk(self, q, k: int, use_pruning: bool):
+        if getattr(self, "packed", None) is not None:
+            return lemp_topk_packed(q, self.packed, k, use_pruning=use_pruning)
+        return lemp_topk(q, self.rows, k, item_len=self.lens, item_ids=self.ids, use_pruning=use_pruning)
 
     @property
     def empty(self) -> bool:
@@ -130,9 +139,7 @@ class DeviceTopK:
         if self.items.empty:
             return (torch.full((n_q, self.worker_k), -float("inf"), device="cuda"),
                     torch.full((n_q, self.worker_k), -1, device="cuda", dtype=torch.int32))
-        k = min(self.worker_k, 128)
-        return lemp_topk(q, self.items.rows, k, item_len=self.items.lens, item_ids=self.items.ids,
-                         use_pruning=self.use_pruning)
+        return self.items.topk(q, min(self.worker_k, 128), self.use_pruning)
 
     def query(self, user_ids: List[int], apply_seen: bool = True):
         """Every rank calls this with the same ``user_ids``.  Returns ``(scores, item_ids)``
@@ -214,8 +221,7 @@ class DeviceLearnerGenerator:
             ls = torch.full((n_q, self.worker_k), -float("inf"), device="cuda")
             li = torch.full((n_q, self.worker_k), -1, device="cuda", dtype=torch.int32)
         else:
-            ls, li = lemp_topk(q, self.local.rows, self.worker_k, item_len=self.local.lens,
-                               item_ids=self.local.ids, use_pruning=self.use_pruning)
+            ls, li = self.local.topk(q, self.worker_k, self.use_pruning)
         ps, pi = _all_gather_parts(self.ctx, ls, li)
         out_s, out_i = topk_merge(ps, pi, min(self.K, ps.shape[1] * ps.shape[2]), self.seen.matrix(users))
         s_np, i_np = out_s.cpu().numpy(), out_i.cpu().numpy()
