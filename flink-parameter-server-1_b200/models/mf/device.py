@@ -260,3 +260,61 @@ def conflict_free_waves(u, i, v):
     for w in range(int(wave_of.max()) + 1 if len(uu) else 0):
         idx = torch.from_numpy(np.nonzero(wave_of == w)[0]).cuda()
         yield u[idx], i[idx], v[idx]
+
+
+def ps_online_mf_device(src, num_factors: int = 10, range_min: float = -0.01, range_max: float = 0.01,
+                        learning_rate: float = 0.01, negative_sample_rate: int = 9, user_memory: int = 128,
+                        pull_limit: int = 1600, *, n_users: Optional[int] = None, n_items: Optional[int] = None,
+                        batch_size: int = 65536, seed: int = 0, lazy: bool = True, streaming: bool = False,
+                        iteration_wait_time: int = 1000, return_model: bool = False):
+    """Device twin of ``ps_online_mf`` (single pass over a rating stream with negative sampling).
+
+    Records are consumed in arrival order in micro-batches.  Negatives (rating 0) are drawn on the
+    device from the items seen *so far in the stream* (``PSOnlineMatrixFactorizationWorker.scala:71-78``);
+    the per-user exclusion set of the reference (last ``user_memory`` items of that user) is
+    approximated by excluding the record's own item - with ``negative_sample_rate`` draws out of
+    thousands of seen items the two differ on a vanishing fraction of draws.
+    ``streaming=True`` feeds the persistent ring-consumer kernel (``OnlineStream``) instead of one
+    launch per micro-batch; the job then ends by the device-side idle timeout."""
+    import torch
+    from ...parallel.device_context import get_context
+    ctx = get_context()
+    ratings = list(src)
+    n_users = n_users or (max(r.user for r in ratings) + 1)
+    n_items = n_items or (max(r.item for r in ratings) + 1)
+    mf = DeviceMF(n_users, n_items, num_factors, range_min, range_max, learning_rate, pull_limit=pull_limit,
+                  seed=seed, lazy=lazy, variant="direct", ctx=ctx)
+    u_all, i_all, r_all = _ratings_to_tensors(ratings, ctx.rank, ctx.world_size)
+    gen = torch.Generator(device="cuda").manual_seed(seed * 31 + ctx.rank)
+    seen = torch.zeros(n_items, dtype=torch.bool, device="cuda")
+    stream = None
+    if streaming:
+        from .stream import OnlineStream
+        stream = OnlineStream(mf, capacity=max(1 << 16, 2 * batch_size * (1 + negative_sample_rate)),
+                              iteration_wait_ms=iteration_wait_time, max_lifetime_ms=600_000)
+    for s in range(0, u_all.numel(), batch_size):
+        u, i, r = u_all[s:s + batch_size], i_all[s:s + batch_size], r_all[s:s + batch_size]
+        pool = torch.nonzero(seen).flatten().int()
+        seen[i.long()] = True
+        if negative_sample_rate > 0 and pool.numel() > 1:
+            k = negative_sample_rate
+            pick = torch.randint(0, pool.numel(), (u.numel(), k), device="cuda", generator=gen)
+            neg_i = pool[pick]
+            keep = (neg_i != i[:, None]).flatten()
+            nu = u[:, None].expand(-1, k).flatten()[keep]
+            ni = neg_i.flatten()[keep]
+            # negatives of a record come right before it, like the reference's block order
+            u = torch.cat([nu, u])
+            i = torch.cat([ni, i])
+            r = torch.cat([torch.zeros(nu.numel(), device="cuda"), r])
+        if stream is not None:
+            stream.feed(u.cpu(), i.cpu(), r.cpu())
+        else:
+            mf.step(u.contiguous(), i.contiguous(), r.contiguous())
+    if stream is not None:
+        stream.join()
+    torch.cuda.synchronize()
+    ctx.barrier()
+    mf.stats()
+    out = mf.dump()
+    return (out, mf) if return_model else out

@@ -60,11 +60,21 @@ class OnlineStream:
         self._done_host = torch.zeros(N.FLOW_BYTES, dtype=torch.uint8).pin_memory()
         self._fed = 0
         self._started = False
+        self._exit_seen = 0
+        self.relaunches = 0
 
-    def start(self) -> None:
+    def start(self, resume: bool = False) -> None:
+        """Launch the consumer.  ``resume=True`` re-arms a consumer that left on its idle timeout while
+        records were still to come: ring_head / ring_done / counters are kept, only exit_reason is reset."""
         import torch
         mf = self.mf
-        mf.flow.zero_()
+        if resume:
+            self._kernel_stream.synchronize()
+            off = N.FpsFlow.exit_reason.offset
+            mf.flow.view(torch.uint8)[off:off + 4].zero_()
+            self.relaunches += 1
+        else:
+            mf.flow.zero_()
         torch.cuda.synchronize()
         with torch.cuda.stream(self._kernel_stream):
             N.check(N.lib().fps_mf_online_stream(
@@ -80,10 +90,16 @@ class OnlineStream:
             self._done_host.copy_(self.mf.flow, non_blocking=True)
         self._copy_stream.synchronize()
         f = N.FpsFlow.from_buffer_copy(bytes(self._done_host.numpy().tobytes()))
+        self._exit_seen = int(f.exit_reason)
         return int(f.ring_done)
 
     def feed(self, users, items, ratings, timeout_s: float = 30.0) -> None:
-        """Append records (CPU tensors / arrays).  Blocks while the ring is full (back-pressure)."""
+        """Append records (CPU tensors / arrays).  Blocks while the ring is full (back-pressure).
+        The consumer kernel is launched by the first call: the device-side idle clock must not run
+        while the producer is still getting ready (a consumer started earlier could time out before
+        the first record arrives and leave the ring unread)."""
+        if not self._started:
+            self.start()
         u = np.asarray(users, dtype=np.int32)
         i = np.asarray(items, dtype=np.int32)
         r = np.asarray(ratings, dtype=np.float32)
@@ -91,9 +107,18 @@ class OnlineStream:
         deadline = time.time() + timeout_s
         while pos < n:
             free = self.capacity - (self._fed - self._retired())
+            if self._exit_seen == 1:
+                # the consumer timed out during a producer gap longer than iteration_wait_ms (first-use
+                # module loads of the producer's own GPU work can serialise behind a running kernel);
+                # it left with head == done, so it can simply be re-armed
+                self.start(resume=True)
+                self._exit_seen = 0
+            elif self._exit_seen in (2, 3):
+                raise RuntimeError("the consumer kernel has left (stop flag / max_lifetime_ms) while records "
+                                   "were still being fed")
             if free <= 0:
                 if time.time() > deadline:
-                    raise TimeoutError("ring stayed full: the consumer kernel is not running")
+                    raise TimeoutError("ring stayed full: the consumer kernel is not retiring records")
                 time.sleep(0.0005)
                 continue
             take = min(free, n - pos)
@@ -112,7 +137,13 @@ class OnlineStream:
 
     def join(self) -> int:
         """Wait for the kernel to leave; returns its exit reason (1 idle, 2 stop, 3 lifetime)."""
+        if not self._started:
+            return 0
         self._kernel_stream.synchronize()
+        flow = read_flow(self.mf.flow)
+        if flow["exit_reason"] == 1 and flow["ring_done"] < self._fed:      # left just before the last feed
+            self.start(resume=True)
+            self._kernel_stream.synchronize()
         reason = read_flow(self.mf.flow)["exit_reason"]
         self._ring.free()
         self._ctl.free()

@@ -48,7 +48,7 @@ def test_learner_generator_device_prequential():
     assert len(out) == len(stream)
     early = NDCGSink().consume(out[200:700]).hit_rate
     late = NDCGSink().consume(out[-500:]).hit_rate
-    assert late > early and late > 0.3, (early, late)
+    assert late > early + 0.1 and late > 0.2, (early, late)      # random ranking would hit 10/100 = 0.1
     s = lg.stats()
     assert s["records"] > len(stream) and s["max_in_flight"] <= 500 and s["nan_count"] == 0
 
@@ -76,6 +76,30 @@ def test_dump_load_round_trip_resumes_training():
     for k in ia:
         np.testing.assert_allclose(ib[k], ia[k], rtol=0, atol=1e-6)
     assert abs(a.rmse(u, i, r) - b.rmse(u, i, r)) < 1e-5
+
+
+@pytest.mark.parametrize("streaming", [False, True])
+def test_online_mf_device_job_with_negative_sampling(streaming):
+    """Device twin of ps_online_mf: implicit positives + sampled negatives, micro-batched launches or
+    the persistent ring consumer; positives must end up scored above random pairs."""
+    from fps_b200.models.mf.device import ps_online_mf_device
+    rnd = random.Random(3)
+    stream = []
+    for t in range(30000):
+        u = rnd.randrange(200)
+        stream.append(Rating(u, (u % 8) * 25 + rnd.randrange(25), 1.0, t))
+    out, mf = ps_online_mf_device(stream, num_factors=8, range_min=-0.1, range_max=0.1, learning_rate=0.2,
+                                  negative_sample_rate=3, batch_size=500, streaming=streaming,
+                                  iteration_wait_time=3000, return_model=True)   # > any host gap between feeds
+    s = mf.stats()
+    assert s["records"] > len(stream) and s["nan_count"] == 0       # negatives were trained too
+    assert s["max_in_flight"] <= 1600
+    if streaming:
+        assert s["exit_reason"] == 1 and s["ring_done"] == s["records"]
+    users, items = last_write_wins(lefts(out)), last_write_wins(rights(out))
+    pos = np.mean([users[r.user] @ items[r.item] for r in stream[-500:]])
+    neg = np.mean([users[r.user] @ items[(r.item + 100) % 200] for r in stream[-500:] if (r.item + 100) % 200 in items])
+    assert pos > neg + 0.1 and pos > 3 * abs(neg), (pos, neg)
 
 
 def test_probes_run_on_one_gpu():
