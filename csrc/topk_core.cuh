@@ -158,8 +158,14 @@ __device__ __forceinline__ int prune_candidates(float* cs, int* ci, int cnt, int
     }
     return cnt;
   }
-  uint32_t T = 0;
-  for (int b = 31; b >= 0; --b) {
+  // the keys of one list share their leading bits (scores of similar magnitude): one pass finds the
+  // highest bit in which any two differ, the bitwise search starts there instead of at bit 31
+  const uint32_t key0 = f2key(cs[0]);
+  uint32_t diff = 0;
+  for (int j = 1; j < cnt; ++j) diff |= f2key(cs[j * TK_M]) ^ key0;
+  const int hb = diff ? 31 - __clz(diff) : -1;
+  uint32_t T = hb >= 0 ? (key0 & ~((2u << hb) - 1u)) : key0;
+  for (int b = hb; b >= 0; --b) {
     const uint32_t trial = T | (1u << b);
     int n = 0;
     for (int j = 0; j < cnt; ++j) n += (f2key(cs[j * TK_M]) >= trial);
@@ -239,7 +245,9 @@ struct Plan {
   size_t off_cand_i, off_theta, off_part_s, off_part_i, total;
 };
 
-Plan make_plan(long long n_q, int k, long long n_items, int dim) {
+// `groups` = candidate lists per (CTA, query): 1 for topk.cu, the number of selection groups for
+// topk_packed.cu (each group also writes its own partial list)
+Plan make_plan(long long n_q, int k, long long n_items, int dim, int groups = 1) {
   Plan p;
   p.n_q_tiles = (int)((n_q + TK_M - 1) / TK_M);
   const long long n_tiles = (n_items + TK_N - 1) / TK_N;
@@ -253,15 +261,15 @@ Plan make_plan(long long n_q, int k, long long n_items, int dim) {
   p.kblks = (dim + TK_KB - 1) / TK_KB;
   auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
   size_t o = 0;
-  o = align(o + (size_t)p.n_ctas * TK_CAP * TK_M * sizeof(float));
+  o = align(o + (size_t)p.n_ctas * groups * TK_CAP * TK_M * sizeof(float));
   p.off_cand_i = o;
-  o = align(o + (size_t)p.n_ctas * TK_CAP * TK_M * sizeof(int));
+  o = align(o + (size_t)p.n_ctas * groups * TK_CAP * TK_M * sizeof(int));
   p.off_theta = o;
   o = align(o + (size_t)p.n_q_tiles * TK_M * sizeof(uint32_t));
   p.off_part_s = o;
-  o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * k * sizeof(float));
+  o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * groups * k * sizeof(float));
   p.off_part_i = o;
-  o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * k * sizeof(int));
+  o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * groups * k * sizeof(int));
   p.total = o;
   return p;
 }

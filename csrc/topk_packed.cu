@@ -7,21 +7,37 @@
 // per model refresh), so here the hi/lo split and the SWIZZLE_128B layout are computed once by
 // `fps_topk_pack_items` into an image that is byte-for-byte what the UMMA descriptors expect in
 // shared memory.  Scoring then is:
-//   warp 4 (one elected lane): cp.async.bulk (TMA, UBLKCP) of the next packed tile into shared
-//       memory, completion on an mbarrier; tcgen05.mma (3 x kind::tf32 per K step) into one of two
-//       TMEM accumulators; tcgen05.commit to that accumulator's mbarrier.
-//   warps 0-3: wait for the accumulator, tcgen05.ld it (thread t = TMEM lane t = query t), hand the
-//       TMEM buffer back, then run the LEMP selection (threshold append + pruning) while the
-//       next tile's copy and MMAs are already in flight.
+//   prologue (warps 0-3): the CTA's 128 queries are split into tf32 hi / lo once and written to
+//       TMEM with tcgen05.st (columns TP_A_COL..), so the A operand never touches shared memory
+//       again (TS-mode MMA) and all of shared memory is free for item tiles.
+//   producer warp (one elected lane): cp.async.bulk (TMA, UBLKCP) of the next packed tile into a
+//       TP_STAGES-deep shared-memory ring, completion on the stage's "full" mbarrier.
+//   MMA warp (one elected lane): waits for "full", issues tcgen05.mma (3 x kind::tf32 per K step,
+//       A from TMEM, descriptors = base + compile-time constants) into one of four TMEM
+//       accumulators, tcgen05.commit to that accumulator's mbarrier and to the stage's "empty"
+//       mbarrier.
+//   selection warps, G groups of four (G = 1, 2 or 4): group g takes tiles g, g + G, ...; it waits
+//       for the accumulator, tcgen05.ld's it (thread = TMEM lane = query), hands the TMEM buffer
+//       back, then runs the LEMP selection (group-of-4 max filter, threshold append,
+//       warp-synchronous pruning) while the next tiles' copies and MMAs are in flight.  The third
+//       ncu capture (profiles/r1_topk) showed the kernel bound by the latency of this branchy code
+//       with one warp per scheduler - hence the groups.
 // The LEMP bucket test (||q|| * tileMaxLen <= theta for every query of the CTA) is evaluated by the
-// selection warps and published per warp; the issuer stops fetching tiles once all four agree.
+// selection warps and published per warp; the producer stops fetching tiles once every lane quarter
+// has one group that agrees.
+#include <cstdlib>
+
 #include "topk_core.cuh"
 
 namespace {
 
-constexpr int TP_THREADS = 192;       // 4 selection warps + TMA producer warp + MMA issuer warp
-constexpr int TP_TMEM_COLS = 512;     // 2 x 64 accumulator columns + 2 x 128 query (hi, lo) columns
-constexpr int TP_A_COL = 128;         // first TMEM column of the query operand
+constexpr int TP_MAX_GROUPS = 4;      // selection groups (4 warps each) per CTA
+constexpr int TP_DEFAULT_GROUPS = 1;  // measured (config 6): 6.31 / 6.43 / 7.32 ms for 1 / 2 / 4 groups - every extra
+                                      // list per query multiplies accepted candidates and prunes
+constexpr int TP_MAX_THREADS = (4 * TP_MAX_GROUPS + 2) * 32;   // + TMA producer warp + MMA issuer warp
+constexpr int TP_ACC = 4;             // TMEM accumulators of TK_N columns
+constexpr int TP_TMEM_COLS = 512;     // 4 x 64 accumulator columns + 2 x 128 query (hi, lo) columns
+constexpr int TP_A_COL = TP_ACC * TK_N;   // first TMEM column of the query operand
 constexpr int TP_STAGES = 3;          // shared-memory stages of packed item tiles (64 KB each at rank 128)
 
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
@@ -83,11 +99,12 @@ k_pack_items(const float* __restrict__ items, int stride, long long n_items, int
 struct PackedShared {
   uint64_t b_full[TP_STAGES];      // TMA landed the tile in stage s
   uint64_t stage_free[TP_STAGES];  // the MMAs that read stage s are complete
-  uint64_t acc_full[2];            // MMAs of the tile using accumulator b are complete
-  uint64_t acc_empty[2];           // all four selection warps have read accumulator b
+  uint64_t acc_full[TP_ACC];       // MMAs of the tile using accumulator b are complete
+  uint64_t acc_empty[TP_ACC];      // the four selection warps of the owning group have read accumulator b
   uint32_t tmem;
-  volatile int skip_from[4];       // per selection warp: first tile ordinal that may be skipped
+  volatile int skip_from[4 * TP_MAX_GROUPS];   // per selection warp: first tile ordinal that may be skipped
   volatile int issued_final;       // number of tiles the producer really fetched (-1 while running)
+  float qlen[TK_M];
 };
 
 // 32 consecutive TMEM columns of this thread's lane <- registers
@@ -108,21 +125,140 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) 
       : "memory");
 }
 // D[tmem] (+)= A[tmem] * B[smem]^T : the query operand never touches shared memory
-__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
-                                             uint32_t accumulate) {
+// Executed by the whole (converged) MMA warp; elect.sync picks the issuing lane inside the asm so
+// that the compiler keeps every operand in uniform registers and emits one UTCHMMA per call (an
+// `if (lane == 0)` around it costs an ELECT / BRA.U.ANY loop per MMA - seen in the SASS).
+__device__ __forceinline__ uint32_t elect_one() {
+  uint32_t r;
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
+      "{\n\t.reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, e;\n\t}"
+      : "=r"(r));
+  return r;
+}
+template <bool ACC>
+__device__ __forceinline__ void umma_tf32_ts(uint32_t leader, uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t"
+      "setp.ne.b32 e, %5, 0;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(TK_IDESC), "r"(ACC ? 1u : 0u), "r"(leader)
       : "memory");
 }
+__device__ __forceinline__ void umma_commit_elected(uint32_t leader, uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t"
+      "setp.ne.b32 e, %1, 0;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+      ::"r"(smem_u32(bar)), "r"(leader) : "memory");
+}
 
-__global__ void __launch_bounds__(TP_THREADS, 1)
+// All MMAs of one tile: 3 x tf32 per 8-wide K step, KBLKS*4 steps.  The shared-memory descriptors of
+// the steps differ from the stage's base descriptor by compile-time constants (32 B per K step, one
+// [64 x 128 B] slab per K block, the lo image b_bytes after the hi image), so the issuing thread
+// executes a couple of uniform adds per MMA instead of rebuilding descriptors.
+template <int KBLKS>
+__device__ __forceinline__ void issue_tile_mmas(uint32_t leader, uint32_t acc_addr, uint32_t a_hi, uint32_t a_lo,
+                                                uint64_t desc_hi0) {
+  constexpr uint64_t LO_OFF = ((uint64_t)TK_N * KBLKS * TK_KB * 4) >> 4;      // lo image, in 16-byte units
+#pragma unroll
+  for (int kb = 0; kb < KBLKS; ++kb) {
+#pragma unroll
+    for (int ks = 0; ks < TK_KB / 8; ++ks) {
+      const uint32_t a_col = (uint32_t)(kb * TK_KB + ks * 8);
+      const uint64_t off = ((uint64_t)(kb * TK_N * TK_KB + ks * 8) * 4) >> 4;
+      const uint64_t bh = desc_hi0 + off, bl = desc_hi0 + off + LO_OFF;
+      if (kb == 0 && ks == 0) umma_tf32_ts<false>(leader, acc_addr, a_lo + a_col, bh);   // small terms first
+      else umma_tf32_ts<true>(leader, acc_addr, a_lo + a_col, bh);
+      umma_tf32_ts<true>(leader, acc_addr, a_hi + a_col, bl);
+      umma_tf32_ts<true>(leader, acc_addr, a_hi + a_col, bh);
+    }
+  }
+}
+
+// Append the entries of v[0..31] that beat theta.  Nearly all entries fail, so groups of four are
+// rejected with one max3 + max + compare; only a group with a hit runs the per-element code.
+// The candidate lists of the packed kernel are row-major: list of (CTA, group, query) = TK_CAP
+// consecutive floats / ints, so that a warp can prune one list cooperatively with coalesced loads.
+// The append itself is rare per thread; kept out of line so that the hot filter code stays small
+// (the unrolled version was 79 KB of SASS and showed instruction-fetch stalls).
+__device__ __noinline__ int append4(float a, float b, float c, float d, float theta, int item0, float* rs, int* ri, int cnt) {
+  if (a > theta) { rs[cnt] = a; ri[cnt] = item0; ++cnt; }
+  if (b > theta) { rs[cnt] = b; ri[cnt] = item0 + 1; ++cnt; }
+  if (c > theta) { rs[cnt] = c; ri[cnt] = item0 + 2; ++cnt; }
+  if (d > theta) { rs[cnt] = d; ri[cnt] = item0 + 3; ++cnt; }
+  return cnt;
+}
+// Two-level filter over 32 scores: eight group-of-4 maxima (independent FMNMX3 pairs), their maximum,
+// ONE branch when nothing beats theta (the common case even per warp), else a branch per group.
+__device__ __forceinline__ void select32(const float (&v)[32], float theta, int item0, float* rs, int* ri, int& cnt) {
+  float m[8];
+#pragma unroll
+  for (int g = 0; g < 8; ++g) m[g] = fmaxf(fmaxf(v[4 * g], v[4 * g + 1]), fmaxf(v[4 * g + 2], v[4 * g + 3]));
+  const float mm = fmaxf(fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3])), fmaxf(fmaxf(m[4], m[5]), fmaxf(m[6], m[7])));
+  if (mm > theta) {
+#pragma unroll
+    for (int g = 0; g < 8; ++g)
+      if (m[g] > theta) cnt = append4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3], theta, item0 + 4 * g, rs, ri, cnt);
+  }
+}
+
+// Warp-cooperative exact prune of one row-major list (c > k entries, c <= TK_CAP = 8 per lane) back to
+// its k best; returns the k-th best score.  Everything after the 16 coalesced loads runs in
+// registers: common-prefix skip, then one REDUX per remaining key bit, then a ballot compaction.
+__device__ __forceinline__ float prune_row(float* rs, int* ri, int c, int k, int lane) {
+  constexpr int PER = TK_CAP / 32;
+  uint32_t key[PER];
+  int id[PER];
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int idx = lane + 32 * i;
+    const bool valid = idx < c;
+    key[i] = valid ? f2key(rs[idx]) : 0u;      // 0 sorts below every real score
+    id[i] = valid ? ri[idx] : -1;
+  }
+  const uint32_t key0 = __shfl_sync(0xffffffffu, key[0], 0);
+  uint32_t diff = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) diff |= (lane + 32 * i < c) ? (key[i] ^ key0) : 0u;
+  diff = __reduce_or_sync(0xffffffffu, diff);
+  const int hb = diff ? 31 - __clz(diff) : -1;
+  uint32_t T = hb >= 0 ? (key0 & ~((2u << hb) - 1u)) : key0;
+  for (int b = hb; b >= 0; --b) {
+    const uint32_t trial = T | (1u << b);
+    int n = 0;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) n += (key[i] >= trial);
+    n = __reduce_add_sync(0xffffffffu, n);
+    if (n >= k) T = trial;
+  }
+  int n_above = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) n_above += (key[i] > T);
+  n_above = __reduce_add_sync(0xffffffffu, n_above);
+  const int ties_left = k - n_above;
+  const uint32_t lt = (1u << lane) - 1u;
+  int base_a = 0, base_t = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const bool a = key[i] > T, t = key[i] == T && (lane + 32 * i < c);
+    const uint32_t ma = __ballot_sync(0xffffffffu, a), mt = __ballot_sync(0xffffffffu, t);
+    const int pa = base_a + __popc(ma & lt), pt = base_t + __popc(mt & lt);
+    if (a) { rs[pa] = key2f(key[i]); ri[pa] = id[i]; }
+    else if (t && pt < ties_left) { rs[n_above + pt] = key2f(key[i]); ri[n_above + pt] = id[i]; }
+    base_a += __popc(ma);
+    base_t += __popc(mt);
+  }
+  return key2f(T);
+}
+
+__global__ void __launch_bounds__(TP_MAX_THREADS, 1)
 k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_q,
                    const float* __restrict__ packed, const float* __restrict__ item_len,
                    const int* __restrict__ item_ids, long long n_items, int dim, int kblks, int k, int n_splits,
-                   int use_pruning, TopkScratch sc, unsigned long long* __restrict__ stats) {
+                   int groups, int use_pruning, TopkScratch sc, unsigned long long* __restrict__ stats) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int b_floats = TK_N * kblks * TK_KB;
@@ -130,6 +266,7 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
   __shared__ PackedShared sh;
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int n_sel_warps = 4 * groups;       // warps [0, 4*groups) select, then the producer, then the MMA issuer
   const int qt = blockIdx.x / n_splits, split = blockIdx.x - qt * n_splits;
   const long long q0 = (long long)qt * TK_M;
   const int q_valid = (int)min((long long)TK_M, n_q - q0);
@@ -138,29 +275,28 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
   const uint32_t tile_bytes = (uint32_t)(2 * b_floats * sizeof(float));
   const int stage_floats = 2 * b_floats;
 
-  if (warp == 4) tmem_alloc((uint32_t*)&sh.tmem, TP_TMEM_COLS);
+  if (warp == n_sel_warps) tmem_alloc((uint32_t*)&sh.tmem, TP_TMEM_COLS);
   if (t == 0) {
     for (int s = 0; s < TP_STAGES; ++s) {
       mbar_init(&sh.b_full[s], 1);
       mbar_init(&sh.stage_free[s], 1);
     }
-    mbar_init(&sh.acc_full[0], 1);
-    mbar_init(&sh.acc_full[1], 1);
-    mbar_init(&sh.acc_empty[0], 4);
-    mbar_init(&sh.acc_empty[1], 4);
+    for (int b = 0; b < TP_ACC; ++b) {
+      mbar_init(&sh.acc_full[b], 1);
+      mbar_init(&sh.acc_empty[b], 4);
+    }
     sh.issued_final = -1;
-    for (int w = 0; w < 4; ++w) sh.skip_from[w] = 0x7fffffff;
+    for (int w = 0; w < 4 * TP_MAX_GROUPS; ++w) sh.skip_from[w] = 0x7fffffff;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = sh.tmem;
-  // TMEM map: columns [0,128) two accumulators, [128,256) query hi, [256,384) query lo
+  // TMEM map: columns [0,256) four accumulators, [256,384) query hi, [384,512) query lo
   const uint32_t tmem_a_hi = tmem_base + TP_A_COL, tmem_a_lo = tmem_base + TP_A_COL + 128;
 
   // ---- queries -> TMEM (thread t = lane t = query t), split into tf32 hi / lo on the way
-  float qlen = 0.f;
   if (warp < 4) {
     const float* qp = queries + (q0 + t) * q_stride;
     const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
@@ -179,13 +315,13 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
       tmem_st32(tmem_a_lo + lane_off + c0, lo);
     }
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-    qlen = sqrtf(s);
+    sh.qlen[t] = sqrtf(s);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
 
-  if (warp == 4) {
+  if (warp == n_sel_warps) {
     // ===================== producer: TMA bulk copies of packed tiles =====================
     if (lane == 0) {
       int issued = 0;
@@ -193,8 +329,15 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
         const int s = j % TP_STAGES, n = j / TP_STAGES;
         if (n > 0) mbar_wait(&sh.stage_free[s], (n - 1) & 1);
         if (use_pruning) {
-          const int s0 = sh.skip_from[0], s1 = sh.skip_from[1], s2 = sh.skip_from[2], s3 = sh.skip_from[3];
-          if (s0 <= j && s1 <= j && s2 <= j && s3 <= j) break;                // LEMP early exit
+          // a lane quarter may skip from tile j on as soon as ONE group says so: each group's theta is a
+          // lower bound of the same queries' k-th best score
+          bool all = true;
+          for (int sub = 0; sub < 4; ++sub) {
+            int first = 0x7fffffff;
+            for (int g = 0; g < groups; ++g) first = min(first, sh.skip_from[g * 4 + sub]);
+            all = all && (first <= j);
+          }
+          if (all) break;                                                      // LEMP early exit
         }
         const long long tile = split + (long long)j * n_splits;
         const float* src = packed + tile * (long long)stage_floats;
@@ -207,53 +350,64 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
       __threadfence_block();
       sh.issued_final = issued;
     }
-  } else if (warp == 5) {
+  } else if (warp == n_sel_warps + 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      for (int j = 0; j < my_tiles; ++j) {
-        const int s = j % TP_STAGES, n = j / TP_STAGES;
-        bool have = false;
-        while (true) {
-          if (mbar_try(&sh.b_full[s], n & 1)) { have = true; break; }
-          const int fin = sh.issued_final;
-          if (fin >= 0 && j >= fin) break;
-        }
-        if (!have) break;
-        if (j >= 2) mbar_wait(&sh.acc_empty[j & 1], ((j >> 1) - 1) & 1);      // accumulator drained
-        tc_fence_after();
-        const uint32_t acc_addr = tmem_base + (uint32_t)(j & 1) * TK_N;
-        const float* bh_s = sB + (size_t)s * stage_floats;
-        uint32_t acc = 0;
-        for (int kb = 0; kb < kblks; ++kb) {
-#pragma unroll
-          for (int ks = 0; ks < TK_KB / 8; ++ks) {
-            const uint32_t a_col = (uint32_t)(kb * TK_KB + ks * 8);
-            const uint32_t b_off = (uint32_t)(kb * TK_N * TK_KB + ks * 8) * 4;
-            const uint64_t bh = make_desc(smem_u32(bh_s) + b_off), bl = make_desc(smem_u32(bh_s + b_floats) + b_off);
-            umma_tf32_ts(acc_addr, tmem_a_lo + a_col, bh, TK_IDESC, acc);   // small terms first
-            umma_tf32_ts(acc_addr, tmem_a_hi + a_col, bl, TK_IDESC, 1);
-            umma_tf32_ts(acc_addr, tmem_a_hi + a_col, bh, TK_IDESC, 1);
-            acc = 1;
-          }
-        }
-        umma_commit(&sh.stage_free[s]);
-        umma_commit(&sh.acc_full[j & 1]);
+    // The whole warp runs this loop converged (all lanes poll the same barriers); one elected lane
+    // issues.  tmem_base goes through a shuffle so that the compiler treats it as warp-uniform.
+    const uint32_t leader = elect_one();
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t a_hi = tb + TP_A_COL, a_lo = tb + TP_A_COL + 128;
+    for (int j = 0; j < my_tiles; ++j) {
+      const int s = j % TP_STAGES, n = j / TP_STAGES;
+      bool have = false;
+      while (true) {
+        if (mbar_try(&sh.b_full[s], n & 1)) { have = true; break; }
+        const int fin = sh.issued_final;
+        if (fin >= 0 && j >= fin) break;
       }
+      have = __shfl_sync(0xffffffffu, have ? 1 : 0, 0) != 0;
+      if (!have) break;
+      const int b = j % TP_ACC;
+      if (j >= TP_ACC) mbar_wait(&sh.acc_empty[b], ((j / TP_ACC) - 1) & 1);      // accumulator drained
+      tc_fence_after();
+      const uint32_t acc_addr = tb + (uint32_t)b * TK_N;
+      const uint64_t d0 = make_desc(smem_u32(sB + (size_t)s * stage_floats));
+      switch (kblks) {
+        case 1: issue_tile_mmas<1>(leader, acc_addr, a_hi, a_lo, d0); break;
+        case 2: issue_tile_mmas<2>(leader, acc_addr, a_hi, a_lo, d0); break;
+        case 3: issue_tile_mmas<3>(leader, acc_addr, a_hi, a_lo, d0); break;
+        default: issue_tile_mmas<4>(leader, acc_addr, a_hi, a_lo, d0); break;
+      }
+      umma_commit_elected(leader, &sh.stage_free[s]);
+      umma_commit_elected(leader, &sh.acc_full[b]);
     }
   } else {
     // ===================== selection warps =====================
-    float* cs = sc.cand_s + (size_t)blockIdx.x * TK_CAP * TK_M + t;
-    int* ci = sc.cand_i + (size_t)blockIdx.x * TK_CAP * TK_M + t;
-    volatile uint32_t* theta_g = sc.theta + q0 + t;
+    // group g = warp / 4 takes the tiles j = g, g + groups, ...; inside a group warp (w & 3) owns TMEM
+    // lanes 32 (w & 3) .. +31, thread = one query.  More groups = more warps per scheduler to hide
+    // the latency of this branchy code; every group keeps its own candidate list per query.
+    const int grp = warp >> 2, sub = warp & 3;
+    const int tq = sub * 32 + lane;                      // query (TMEM lane) of this thread
+    const size_t row0 = (((size_t)blockIdx.x * groups + grp) * TK_M + sub * 32) * TK_CAP;   // this warp's 32 lists
+    float* const rs_w = sc.cand_s + row0;
+    int* const ri_w = sc.cand_i + row0;
+    float* const rs = rs_w + (size_t)lane * TK_CAP;
+    int* const ri = ri_w + (size_t)lane * TK_CAP;
+    volatile uint32_t* theta_g = sc.theta + q0 + tq;
+    const bool q_ok = tq < q_valid;
+    const float qlen = sh.qlen[tq];
     int cnt = 0;
-    float theta = -INFINITY;
+    float theta = q_ok ? -INFINITY : INFINITY;           // padding queries never accept anything
     unsigned long long tiles_done = 0, accepted = 0, prunes = 0;
-    for (int j = 0; j < my_tiles; ++j) {
-      const int b = j & 1;
+    for (int j = grp; j < my_tiles; j += groups) {
+      const int b = j % TP_ACC;
+      // the bound published by the other groups / splits: the load is issued before the wait so that
+      // its latency hides behind it (it was 7 % of the selection warps' samples after the wait)
+      const uint32_t theta_key = *theta_g;
       // wait for tile j, or learn that the producer stopped before it
       bool have = false;
       while (true) {
-        if (mbar_try(&sh.acc_full[b], (j >> 1) & 1)) { have = true; break; }
+        if (mbar_try(&sh.acc_full[b], (j / TP_ACC) & 1)) { have = true; break; }
         const int fin = sh.issued_final;
         if (fin >= 0 && j >= fin) break;
       }
@@ -263,69 +417,95 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
       const long long i0 = tile * TK_N;
       const int i_valid = (int)min((long long)TK_N, n_items - i0);
       float v0[32], v1[32];
-      const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)b * TK_N;
+      const uint32_t lane_addr = tmem_base + ((uint32_t)(sub * 32) << 16) + (uint32_t)b * TK_N;
       tmem_ld32(lane_addr, v0);
       tmem_ld32(lane_addr + 32, v1);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&sh.acc_empty[b]);
-      if (use_pruning) theta = fmaxf(theta, key2f(*theta_g));
-      if (t < q_valid) {
+      if (q_ok) theta = fmaxf(theta, key2f(theta_key));
+      if (i_valid < TK_N) {                              // ragged last tile
 #pragma unroll
         for (int jj = 0; jj < 32; ++jj) {
-          if (jj < i_valid && v0[jj] > theta) { cs[cnt * TK_M] = v0[jj]; ci[cnt * TK_M] = (int)(i0 + jj); ++cnt; ++accepted; }
-        }
-#pragma unroll
-        for (int jj = 0; jj < 32; ++jj) {
-          if (32 + jj < i_valid && v1[jj] > theta) { cs[cnt * TK_M] = v1[jj]; ci[cnt * TK_M] = (int)(i0 + 32 + jj); ++cnt; ++accepted; }
+          if (jj >= i_valid) v0[jj] = -INFINITY;
+          if (32 + jj >= i_valid) v1[jj] = -INFINITY;
         }
       }
-      // Prune warp-synchronously: the selection loop costs the same for 1 lane or 32, so when any
-      // lane's buffer is about to overflow every lane of the warp with more than k candidates
-      // prunes now.  (Per-lane pruning made the warp run this loop on ~40 % of the tiles and was
-      // 90 % of the kernel's instructions in the first ncu capture.)
+      const int before = cnt;
+      select32(v0, theta, (int)i0, rs, ri, cnt);
+      select32(v1, theta, (int)i0 + 32, rs, ri, cnt);
+      accepted += (unsigned)(cnt - before);
+      // Prune warp-synchronously and cooperatively: when any lane's list is about to overflow, every
+      // list of the warp with more than k entries is pruned, one list at a time by all 32 lanes.
+      // (Per-lane pruning was 90 % of the kernel's instructions in the first ncu capture; per-thread
+      // pruning in lockstep was bound by 28 dependent passes over L2-resident lists in the third.)
       if (__any_sync(0xffffffffu, cnt > TK_CAP - TK_N)) {
-        if (t < q_valid && cnt > k) {
-          cnt = prune_candidates(cs, ci, cnt, k, theta);
-          ++prunes;
-          if (use_pruning) atomicMax((uint32_t*)theta_g, f2key(theta));
+        __syncwarp();
+        for (int src = 0; src < 32; ++src) {
+          const int c = __shfl_sync(0xffffffffu, cnt, src);
+          if (c > k) {
+            const float th = prune_row(rs_w + (size_t)src * TK_CAP, ri_w + (size_t)src * TK_CAP, c, k, lane);
+            if (lane == src) {
+              cnt = k;
+              theta = fmaxf(theta, th);
+              ++prunes;
+              atomicMax((uint32_t*)theta_g, f2key(theta));
+            }
+          }
         }
+        __syncwarp();
       }
       ++tiles_done;
       // LEMP bucket test for the tiles after this one (lengths descend, theta only grows)
       if (use_pruning && j + 1 < my_tiles) {
         const long long nxt = (split + (long long)(j + 1) * n_splits) * TK_N;
-        const bool can_skip = (t >= q_valid) || (theta > -INFINITY && qlen * item_len[nxt] <= theta);
+        const bool can_skip = !q_ok || (theta > -INFINITY && qlen * item_len[nxt] <= theta);
         if (__all_sync(0xffffffffu, can_skip) && lane == 0 && sh.skip_from[warp] == 0x7fffffff) sh.skip_from[warp] = j + 1;
       }
     }
-    if (t < q_valid) {
-      cnt = prune_candidates(cs, ci, cnt, k, theta);
-      float* ps = sc.part_s + ((size_t)(q0 + t) * n_splits + split) * k;
-      int* pi = sc.part_i + ((size_t)(q0 + t) * n_splits + split) * k;
-      for (int j = 0; j < k; ++j) {
-        if (j < cnt) {
-          const int slot = ci[j * TK_M];
-          ps[j] = cs[j * TK_M];
-          pi[j] = item_ids ? item_ids[slot] : slot;
-        } else {
-          ps[j] = -INFINITY;
-          pi[j] = -1;
-        }
+    // final prune + partial list of (query, split, group), again one list at a time by the whole warp
+    __syncwarp();
+    for (int src = 0; src < 32; ++src) {
+      const int qi = sub * 32 + src;
+      if (qi >= q_valid) break;                          // warp-uniform
+      int c = __shfl_sync(0xffffffffu, cnt, src);
+      float* r_s = rs_w + (size_t)src * TK_CAP;
+      int* r_i = ri_w + (size_t)src * TK_CAP;
+      if (c > k) {
+        prune_row(r_s, r_i, c, k, lane);
+        c = k;
+        __syncwarp();
+      }
+      const size_t part = ((size_t)(q0 + qi) * n_splits * groups + (size_t)split * groups + grp) * k;
+      for (int jj = lane; jj < k; jj += 32) {
+        const bool in = jj < c;
+        const int slot = in ? r_i[jj] : -1;
+        sc.part_s[part + jj] = in ? r_s[jj] : -INFINITY;
+        sc.part_i[part + jj] = in ? (item_ids ? item_ids[slot] : slot) : -1;
       }
     }
     if (stats != nullptr) {
-      if (t == 0) {
+      if (tq == 0) {
         atomicAdd(&stats[0], tiles_done);
-        atomicAdd(&stats[1], (unsigned long long)my_tiles);
+        if (grp == 0) atomicAdd(&stats[1], (unsigned long long)my_tiles);
       }
-      atomicAdd(&stats[2], accepted);
+      if (q_ok) atomicAdd(&stats[2], accepted);
       if (prunes) atomicAdd(&stats[3], prunes);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc(tmem_base, TP_TMEM_COLS);
+  if (warp == n_sel_warps) tmem_dealloc(tmem_base, TP_TMEM_COLS);
+}
+
+int packed_groups() {
+  static int g = -1;
+  if (g < 0) {
+    const char* e = getenv("FPS_TOPK_GROUPS");
+    int v = e ? atoi(e) : TP_DEFAULT_GROUPS;
+    g = (v == 1 || v == 2 || v == 4) ? v : TP_DEFAULT_GROUPS;
+  }
+  return g;
 }
 
 }  // namespace
@@ -337,6 +517,11 @@ size_t fps_topk_packed_bytes(int64_t n_items, int32_t dim) {
   const int kblks = (dim + TK_KB - 1) / TK_KB;
   const size_t n_tiles = (size_t)((n_items + TK_N - 1) / TK_N);
   return n_tiles * 2 * (size_t)TK_N * kblks * TK_KB * sizeof(float);
+}
+
+size_t fps_topk_packed_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items) {
+  if (n_q <= 0 || k <= 0 || n_items <= 0) return 0;
+  return make_plan(n_q, k, n_items, 128, packed_groups()).total;
 }
 
 int fps_topk_pack_items(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim, void* d_packed,
@@ -359,7 +544,14 @@ int fps_lemp_topk_packed(const float* d_queries, int32_t q_stride, int64_t n_q, 
   FPS_REQUIRE(dim <= 128 && q_stride % 4 == 0, FPS_E_UNSUPPORTED, "fps_lemp_topk_packed: rank <= 128 and q_stride %% 4 == 0 required");
   FPS_REQUIRE(!use_pruning || d_item_len != nullptr, FPS_E_INVALID, "fps_lemp_topk_packed: pruning needs item lengths");
   cudaStream_t st = (cudaStream_t)stream;
-  const Plan p = make_plan(n_q, k, n_items, dim);
+  // More selection groups hide more latency but every group keeps its own candidate list; fall back to
+  // fewer groups when the caller's scratch was sized for fewer (fps_topk_scratch_bytes = one group).
+  int groups = packed_groups();
+  Plan p = make_plan(n_q, k, n_items, dim, groups);
+  while (groups > 1 && (scratch_bytes < p.total || (long long)p.n_splits * groups * k > 8192)) {
+    groups >>= 1;
+    p = make_plan(n_q, k, n_items, dim, groups);
+  }
   FPS_REQUIRE(scratch_bytes >= p.total, FPS_E_INVALID, "fps_lemp_topk_packed: scratch too small (%zu < %zu)", scratch_bytes, p.total);
   uint8_t* sb = (uint8_t*)d_scratch;
   TopkScratch sc;
@@ -369,15 +561,15 @@ int fps_lemp_topk_packed(const float* d_queries, int32_t q_stride, int64_t n_q, 
   sc.part_s = (float*)(sb + p.off_part_s);
   sc.part_i = (int*)(sb + p.off_part_i);
   FPS_CUDA(cudaMemsetAsync(sc.theta, 0, (size_t)p.n_q_tiles * TK_M * sizeof(uint32_t), st));
-  const size_t a_bytes = (size_t)TK_M * p.kblks * TK_KB * 4, b_bytes = (size_t)TK_N * p.kblks * TK_KB * 4;
-  (void)a_bytes;
+  const size_t b_bytes = (size_t)TK_N * p.kblks * TK_KB * 4;
   const size_t smem = 1024 + (size_t)TP_STAGES * 2 * b_bytes;
   FPS_CUDA(cudaFuncSetAttribute(k_lemp_topk_packed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  k_lemp_topk_packed<<<p.n_ctas, TP_THREADS, smem, st>>>(d_queries, q_stride, n_q, (const float*)d_packed, d_item_len,
-                                                         d_item_ids, n_items, dim, p.kblks, k, p.n_splits,
-                                                         use_pruning, sc, (unsigned long long*)d_stats);
+  k_lemp_topk_packed<<<p.n_ctas, (4 * groups + 2) * 32, smem, st>>>(d_queries, q_stride, n_q, (const float*)d_packed,
+                                                                    d_item_len, d_item_ids, n_items, dim, p.kblks, k,
+                                                                    p.n_splits, groups, use_pruning, sc,
+                                                                    (unsigned long long*)d_stats);
   FPS_LAUNCH_CHECK();
-  return launch_merge(sc.part_s, sc.part_i, p.n_splits, n_q, k, k, nullptr, 0, d_out_scores, d_out_ids, st);
+  return launch_merge(sc.part_s, sc.part_i, p.n_splits * groups, n_q, k, k, nullptr, 0, d_out_scores, d_out_ids, st);
 }
 
 }  // extern "C"

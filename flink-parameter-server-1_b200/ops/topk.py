@@ -96,9 +96,9 @@ def lemp_topk_packed(queries, packed: PackedItems, k: int, *, use_pruning: bool 
     assert queries.shape[1] == packed.dim
     q = _pad4(queries.float())
     n_q = q.shape[0]
-    need = scratch_bytes(n_q, k, packed.n_items)
-    if scratch is None:
-        scratch = torch.empty(need, device="cuda", dtype=torch.uint8)
+    if scratch is None:      # room for every selection group's candidate lists (a smaller caller buffer = fewer groups)
+        scratch = torch.empty(int(N.lib().fps_topk_packed_scratch_bytes(n_q, k, packed.n_items)), device="cuda",
+                              dtype=torch.uint8)
     out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
     out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
     N.check(N.lib().fps_lemp_topk_packed(N.ptr(q), q.shape[1], n_q, N.ptr(packed.data), N.ptr(packed.item_len),

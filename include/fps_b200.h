@@ -198,9 +198,12 @@ int fps_lemp_topk(const float* d_queries, int32_t q_stride, int64_t n_q,
 /* Second-generation path: pack the (length-sorted) items once into per-tile tf32 hi/lo images in
  * the swizzled layout the tensor cores read (2x the fp32 bytes; fps_topk_packed_bytes), then score
  * query batches with fps_lemp_topk_packed, which streams the tiles with TMA bulk copies into a
- * warp-specialised tcgen05 pipeline (double-buffered TMEM accumulators).  Same results, same
- * scratch contract as fps_lemp_topk.                                                              */
+ * warp-specialised tcgen05 pipeline (four TMEM accumulators, 1 / 2 / 4 groups of selection warps;
+ * env FPS_TOPK_GROUPS).  Same results as fps_lemp_topk.  Scratch: fps_topk_packed_scratch_bytes
+ * lets every selection group keep its own candidate lists; with less (down to
+ * fps_topk_scratch_bytes) the kernel runs with fewer groups.                                      */
 size_t fps_topk_packed_bytes(int64_t n_items, int32_t dim);
+size_t fps_topk_packed_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items);
 int fps_topk_pack_items(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim,
                         void* d_packed, void* stream);
 int fps_lemp_topk_packed(const float* d_queries, int32_t q_stride, int64_t n_q, const void* d_packed,
