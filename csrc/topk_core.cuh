@@ -247,14 +247,27 @@ struct Plan {
 
 // `groups` = candidate lists per (CTA, query): 1 for topk.cu, the number of selection groups for
 // topk_packed.cu (each group also writes its own partial list)
-Plan make_plan(long long n_q, int k, long long n_items, int dim, int groups = 1) {
+// `multi_wave`: allow more CTAs than SMs when that fills the machine better (32 query tiles: 4 splits
+// = 128 CTAs leave 20 of 148 SMs idle, 9 splits = 288 CTAs run as 1.95 waves); later CTAs start with
+// the theta the earlier ones published, so the extra lists cost little.  `forced_splits` > 0 overrides.
+Plan make_plan(long long n_q, int k, long long n_items, int dim, int groups = 1, int multi_wave = 0,
+               int forced_splits = 0) {
   Plan p;
   p.n_q_tiles = (int)((n_q + TK_M - 1) / TK_M);
   const long long n_tiles = (n_items + TK_N - 1) / TK_N;
   const int sms = fps_num_sms();
-  long long splits = sms / (p.n_q_tiles > 0 ? p.n_q_tiles : 1);
+  const int qt = p.n_q_tiles > 0 ? p.n_q_tiles : 1;
+  long long splits = sms / qt;
   if (splits < 1) splits = 1;
   if (splits > 16) splits = 16;
+  if (multi_wave) {
+    auto eff = [&](long long s) { return (double)(qt * s) / (double)(((qt * s + sms - 1) / sms) * sms); };
+    long long best = splits;
+    for (long long s = splits + 1; s <= 16; ++s)
+      if (s * groups * k <= 8192 && eff(s) > eff(best) + 0.03) best = s;
+    splits = best;
+  }
+  if (forced_splits > 0) splits = forced_splits > 16 ? 16 : forced_splits;
   if (splits > n_tiles) splits = n_tiles > 0 ? n_tiles : 1;
   p.n_splits = (int)splits;
   p.n_ctas = p.n_q_tiles * p.n_splits;

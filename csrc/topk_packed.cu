@@ -507,6 +507,33 @@ int packed_groups() {
   }
   return g;
 }
+int packed_forced_splits() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("FPS_TOPK_SPLITS");
+    v = e ? atoi(e) : 0;
+    if (v < 0) v = 0;
+  }
+  return v;
+}
+// the richest plan that fits the caller's scratch: all selection groups + multi-wave splits first, then
+// single-wave splits, then fewer groups (fps_topk_scratch_bytes covers one group, single wave)
+Plan packed_plan(long long n_q, int k, long long n_items, int dim, size_t scratch_bytes, int* groups_out) {
+  int groups = packed_groups();
+  Plan p;
+  while (true) {
+    // multi-wave splits are opt-in (FPS_TOPK_SPLITS): measured on config 6, 9 splits (1.95 waves, all SMs
+    // busy) take 6.96 ms against 6.19 ms for 4 splits (128 of 148 SMs) - each extra list per query
+    // adds accepted candidates and prunes that cost more than the idle SMs
+    p = make_plan(n_q, k, n_items, dim, groups, 0, packed_forced_splits());
+    if (scratch_bytes >= p.total && (long long)p.n_splits * groups * k <= 8192) break;
+    p = make_plan(n_q, k, n_items, dim, groups, 0, 0);
+    if ((scratch_bytes >= p.total && (long long)p.n_splits * groups * k <= 8192) || groups == 1) break;
+    groups >>= 1;
+  }
+  *groups_out = groups;
+  return p;
+}
 
 }  // namespace
 
@@ -521,7 +548,8 @@ size_t fps_topk_packed_bytes(int64_t n_items, int32_t dim) {
 
 size_t fps_topk_packed_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items) {
   if (n_q <= 0 || k <= 0 || n_items <= 0) return 0;
-  return make_plan(n_q, k, n_items, 128, packed_groups()).total;
+  int groups;
+  return packed_plan(n_q, k, n_items, 128, (size_t)-1, &groups).total;
 }
 
 int fps_topk_pack_items(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim, void* d_packed,
@@ -546,12 +574,8 @@ int fps_lemp_topk_packed(const float* d_queries, int32_t q_stride, int64_t n_q, 
   cudaStream_t st = (cudaStream_t)stream;
   // More selection groups hide more latency but every group keeps its own candidate list; fall back to
   // fewer groups when the caller's scratch was sized for fewer (fps_topk_scratch_bytes = one group).
-  int groups = packed_groups();
-  Plan p = make_plan(n_q, k, n_items, dim, groups);
-  while (groups > 1 && (scratch_bytes < p.total || (long long)p.n_splits * groups * k > 8192)) {
-    groups >>= 1;
-    p = make_plan(n_q, k, n_items, dim, groups);
-  }
+  int groups;
+  const Plan p = packed_plan(n_q, k, n_items, dim, scratch_bytes, &groups);
   FPS_REQUIRE(scratch_bytes >= p.total, FPS_E_INVALID, "fps_lemp_topk_packed: scratch too small (%zu < %zu)", scratch_bytes, p.total);
   uint8_t* sb = (uint8_t*)d_scratch;
   TopkScratch sc;
