@@ -149,6 +149,9 @@ def config3(ctx):
     return {"config": 3, "what": "binary PA-I, RCV1-shaped (47K features, 75 nnz)", "n_gpus": ctx.world_size,
             "examples_per_gpu": B, "ms_per_step": ms, "examples_per_sec": B * ctx.world_size / ms * 1e3,
             "pull_rows_per_sec": B * nnz * ctx.world_size / ms * 1e3,
+            "table": ("replicated, deferred delta exchange" if pa.table.deferred else
+                      "replicated, multimem.red pushes" if pa.table.multicast else "replicated, red.add per replica")
+            if pa.table.replicated else "sharded",
             "with_pull_limit_10000": {"ms_per_step": ms_lim, "max_in_flight": s["max_in_flight"]}}
 
 

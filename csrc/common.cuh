@@ -147,6 +147,33 @@ __device__ __forceinline__ void red_add4(float* p, float4 v) {
 __device__ __forceinline__ void red_add1(float* p, float v) {
   asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
 }
+// Push into a REPLICATED table: one multimem.red on the multicast alias and NVSwitch applies the
+// add to every GPU's replica (NVLS in-switch reduction) - the sender pays for one copy on its link.
+__device__ __forceinline__ void mc_red_add4(float* p, float4 v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x),
+               "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void mc_red_add1(float* p, float v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+// param_update = add on row `off` (in floats from the shard base) of the row's owner - or, for a
+// replicated table, on every replica: deferred (local replica + local delta array, exchanged by
+// fps_table_flush_delta), or immediately through the multicast alias, or one red.add per replica.
+__device__ __forceinline__ void push_add1(const FpsTableView& t, int owner, long long off, float v) {
+  if (t.n_replicas <= 1) red_add1(t.rows[owner] + off, v);
+  else if (t.delta_rows != nullptr) { red_add1(t.rows[0] + off, v); red_add1(t.delta_rows + off, v); }
+  else if (t.mc_rows != nullptr) mc_red_add1(t.mc_rows + off, v);
+  else
+    for (int r = 0; r < t.n_replicas; ++r) red_add1(t.replica_rows[r] + off, v);
+}
+__device__ __forceinline__ void push_add4(const FpsTableView& t, int owner, long long off, float4 v) {
+  if (t.n_replicas <= 1) red_add4(t.rows[owner] + off, v);
+  else if (t.delta_rows != nullptr) { red_add4(t.rows[0] + off, v); red_add4(t.delta_rows + off, v); }
+  else if (t.mc_rows != nullptr) mc_red_add4(t.mc_rows + off, v);
+  else
+    for (int r = 0; r < t.n_replicas; ++r) red_add4(t.replica_rows[r] + off, v);
+}
 
 __device__ __forceinline__ uint64_t globaltimer_ns() {
   uint64_t t;

@@ -123,7 +123,7 @@ k_pa_binary(const __grid_constant__ FpsTableView t, const long long* __restrict_
             const RowRef r = locate(t, id);
             if (!in_table(t, id, r)) continue;
             if (t.lazy) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
-            red_add1(t.rows[r.owner] + r.slot * t.stride, mult * values[k]);
+            push_add1(t, r.owner, r.slot * t.stride, mult * values[k]);
             ++c.pushes;
           }
         }
@@ -258,11 +258,11 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
           const float x = values[k];
           const RowRef r = locate(t, id);
           if (!in_table(t, id, r)) continue;
-          float* row = t.rows[r.owner] + r.slot * t.stride;
+          const long long row = r.slot * t.stride;
           if (t.lazy && lane == 0) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
           for (int vb = lane; vb < nvec; vb += 32) {
             const float4 m4 = *reinterpret_cast<const float4*>(s_d + vb * 4);
-            red_add4(row + vb * 4, make_float4(x * m4.x, x * m4.y, x * m4.z, x * m4.w));
+            push_add4(t, r.owner, row + vb * 4, make_float4(x * m4.x, x * m4.y, x * m4.z, x * m4.w));
           }
           if (lane == 0) ++c.pushes;
         }
@@ -274,10 +274,10 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
           const float x = values[k];
           const RowRef r = locate(t, id);
           if (!in_table(t, id, r)) continue;
-          float* row = t.rows[r.owner] + r.slot * t.stride;
+          const long long row = r.slot * t.stride;
           if (t.lazy) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
-          red_add1(row + y, tau * x);
-          red_add1(row + q, -tau * x);
+          push_add1(t, r.owner, row + y, tau * x);
+          push_add1(t, r.owner, row + q, -tau * x);
           ++c.pushes;
         }
       }

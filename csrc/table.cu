@@ -112,9 +112,13 @@ k_scatter(const __grid_constant__ FpsTableView t, const long long* __restrict__ 
           if (j + 2 >= t.dim) d.z = old.z;
           if (j + 3 >= t.dim) d.w = old.w;
         }
-        st_row4(row + j, d);
+        if (t.n_replicas > 1) {   // model load into a replicated table: every replica gets the value
+          for (int rr = 0; rr < t.n_replicas; ++rr) st_row4(t.replica_rows[rr] + r.slot * t.stride + j, d);
+        } else {
+          st_row4(row + j, d);
+        }
       } else {
-        red_add4(row + j, d);
+        push_add4(t, r.owner, r.slot * t.stride + j, d);
       }
     }
     if (mode == 2 && t.stride > t.dim) {
@@ -227,9 +231,14 @@ k_scatter_scalar(const __grid_constant__ FpsTableView t, const long long* __rest
     float d = vals[g * val_stride];
     if (mode == 1) {
       if (state == FPS_ROW_PULLED) d -= scalar_init_value(t, id);
-      asm volatile("st.global.cg.f32 [%0], %1;" ::"l"(row), "f"(d) : "memory");
+      if (t.n_replicas > 1) {
+        for (int rr = 0; rr < t.n_replicas; ++rr)
+          asm volatile("st.global.cg.f32 [%0], %1;" ::"l"(t.replica_rows[rr] + r.slot), "f"(d) : "memory");
+      } else {
+        asm volatile("st.global.cg.f32 [%0], %1;" ::"l"(row), "f"(d) : "memory");
+      }
     } else {
-      red_add1(row, d);
+      push_add1(t, r.owner, r.slot, d);
     }
     ++done;
   }
@@ -277,11 +286,54 @@ int check_view(const FpsTableView* v, const char* who) {
   return 0;
 }
 
+// ---- replicated tables with deferred pushes: exchange the accumulated deltas ----------------------
+// Runs after the step kernels on their stream.  Every 16-byte chunk of the local delta array that is
+// not all zero is added to the same place of every OTHER replica (the local one already has it) and
+// cleared.  A weight pushed thousands of times during the step crosses NVLink once per peer.
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+k_flush_delta(const __grid_constant__ FpsTableView t, long long n_floats) {
+  const long long n_items = VEC ? n_floats / 4 : n_floats;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_items; i += (long long)gridDim.x * blockDim.x) {
+    if (VEC) {
+      float4* dp = reinterpret_cast<float4*>(t.delta_rows) + i;
+      const float4 d = *dp;
+      if (d.x == 0.f && d.y == 0.f && d.z == 0.f && d.w == 0.f) continue;
+      *dp = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = 0; r < t.n_replicas; ++r)
+        if (r != t.replica_rank) red_add4(t.replica_rows[r] + i * 4, d);
+    } else {
+      const float d = t.delta_rows[i];
+      if (d == 0.f) continue;
+      t.delta_rows[i] = 0.f;
+      for (int r = 0; r < t.n_replicas; ++r)
+        if (r != t.replica_rank) red_add1(t.replica_rows[r] + i, d);
+    }
+  }
+}
+
 }  // namespace
 
 int fps_check_view(const FpsTableView* v, const char* who) { return check_view(v, who); }
 
 extern "C" {
+
+int fps_table_flush_delta(const FpsTableView* view, void* stream) {
+  if (int e = check_view(view, "fps_table_flush_delta")) return e;
+  if (view->n_replicas <= 1 || view->delta_rows == nullptr) return 0;
+  FPS_REQUIRE(view->replica_rank >= 0 && view->replica_rank < view->n_replicas, FPS_E_INVALID,
+              "fps_table_flush_delta: replica_rank %d outside [0, %d)", view->replica_rank, view->n_replicas);
+  const long long n_floats = (long long)view->rows_per_shard * view->stride;
+  const bool vec = (n_floats % 4 == 0) && (((uintptr_t)view->delta_rows) % 16 == 0);
+  long long blocks = ((vec ? n_floats / 4 : n_floats) + 255) / 256;
+  const long long cap = (long long)fps_num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  if (vec) k_flush_delta<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(*view, n_floats);
+  else k_flush_delta<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(*view, n_floats);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
 
 int fps_table_init_shard(const FpsTableView* view, int shard, int64_t n_rows, void* stream) {
   if (int e = check_view(view, "fps_table_init_shard")) return e;

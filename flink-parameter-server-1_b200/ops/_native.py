@@ -34,6 +34,11 @@ class FpsTableView(C.Structure):
         ("seed", C.c_uint64),
         ("stream_tag", C.c_int32),
         ("lazy", C.c_int32),
+        ("mc_rows", C.c_void_p),
+        ("delta_rows", C.c_void_p),
+        ("replica_rows", C.c_void_p * FPS_MAX_SHARDS),
+        ("n_replicas", C.c_int32),
+        ("replica_rank", C.c_int32),
     ]
 
 
@@ -137,6 +142,7 @@ def lib() -> C.CDLL:
                                            P(FpsMfParams), C.c_uint32, C.c_uint32, vp, vp]),
         "fps_pa_step": (C.c_int, [P(FpsTableView), vp, vp, vp, vp, i64, P(FpsPaParams), vp, vp, vp]),
         "fps_pa_step_cost": (C.c_int, [P(FpsTableView), vp, vp, vp, vp, i64, P(FpsPaParams), vp, vp, vp, vp]),
+        "fps_table_flush_delta": (C.c_int, [vp, vp]),
         "fps_topk_scratch_bytes": (C.c_size_t, [i64, i32, i64]),
         "fps_lemp_topk": (C.c_int, [vp, i32, i64, vp, i32, vp, vp, i64, i32, i32, i32, vp, C.c_size_t,
                                     vp, vp, vp, vp]),

@@ -43,10 +43,18 @@ class ShardedTable:
                  init_range: Tuple[float, float] = (0.0, 0.0), seed: int = 0,
                  stream_tag: int = philox.STREAM_ITEM, lazy: bool = False, aux_cols: int = 0,
                  ctx=None, local_only: bool = False, scalar: bool = False,
-                 peer_mapping: Optional[str] = None):
+                 peer_mapping: Optional[str] = None, replicated: bool = False):
         """``local_only`` = a worker-resident table (MF user factors): sharded by the same formula
         but a rank only ever touches its own shard, so no peer mapping is made.
-        ``scalar`` = one float per id with no padding (binary PA weights)."""
+        ``scalar`` = one float per id with no padding (binary PA weights).
+        ``replicated`` (several ranks only) = every GPU holds the whole table and pulls are local.
+        Pushes are *deferred* by default: a push adds to the local replica and to a local delta array,
+        ``flush_deltas()`` (called by the step functions after each launch) adds the accumulated
+        deltas to the other replicas - a hot weight crosses NVLink once per launch instead of once
+        per push.  ``FPS_REPLICA_PUSH=immediate`` applies every push to all replicas at once with one
+        ``multimem.red`` on the NVLS multicast alias (or one ``red.add`` per replica without
+        multicast); measured 15x slower for 4-byte rows (single-word packets cap near 5 G/s per GPU).
+        For small hot tables, where sharding would send 4-byte rows across NVLink one by one."""
         import torch
         from ..parallel.device_context import get_context
         self.ctx = ctx or get_context()
@@ -56,8 +64,11 @@ class ShardedTable:
             raise ValueError("a scalar table has dim 1 and no aux columns")
         self.stride = 1 if scalar else padded_stride(dim, aux_cols)
         self.aux_cols = aux_cols
-        self.n_shards = int(n_shards or world)
-        if world > 1 and self.n_shards != world:
+        self.replicated = bool(replicated) and world > 1 and not local_only
+        if self.replicated and lazy and tuple(init_range) != (0.0, 0.0):
+            raise ValueError("a replicated lazy table needs a zero initialiser (state bytes are per replica)")
+        self.n_shards = 1 if self.replicated else int(n_shards or world)
+        if world > 1 and not self.replicated and self.n_shards != world:
             raise ValueError("with several ranks the table has exactly one shard per rank")
         if not 1 <= self.n_shards <= N.FPS_MAX_SHARDS:
             raise ValueError(f"n_shards must be in [1, {N.FPS_MAX_SHARDS}]")
@@ -67,7 +78,7 @@ class ShardedTable:
         self.init_range = (float(init_range[0]), float(init_range[1]))
         self.seed, self.stream_tag, self.lazy = int(seed), int(stream_tag), bool(lazy)
         self.local_only = local_only
-        self.local_shards = [self.ctx.rank] if world > 1 else list(range(self.n_shards))
+        self.local_shards = [0] if self.replicated else ([self.ctx.rank] if world > 1 else list(range(self.n_shards)))
 
         self._bufs: dict = {}
         self._state_bufs: dict = {}
@@ -82,9 +93,38 @@ class ShardedTable:
         v.init_lo, v.init_hi = self.init_range
         v.seed, v.stream_tag, v.lazy = self.seed, self.stream_tag, int(self.lazy)
         n_state = ((self.rows_per_shard + 3) // 4) * 4
-        shared = world > 1 and not local_only
+        shared = world > 1 and not local_only and not self.replicated
+        self.multicast = False
+        self.deferred = False
+        if self.replicated:
+            self.rows[0], ptrs = _symm_alloc((self.rows_per_shard, self.stride), torch.float32, self.ctx, self._symm)
+            v.rows[0] = ptrs[self.ctx.rank]
+            for r in range(world):
+                v.replica_rows[r] = ptrs[r]
+            v.n_replicas = world
+            v.replica_rank = self.ctx.rank
+            self.deferred = os.environ.get("FPS_REPLICA_PUSH", "deferred") != "immediate"
+            if self.deferred:
+                # pushes add to the local replica and to this array; flush_deltas() forwards the sums
+                self._delta = torch.zeros((self.rows_per_shard, self.stride), device="cuda", dtype=torch.float32)
+                v.delta_rows = self._delta.data_ptr()
+            mc = 0
+            if os.environ.get("FPS_NO_MULTICAST", "0") != "1":
+                try:
+                    mc = int(self._symm[-1][1].multicast_ptr or 0)
+                except Exception:
+                    mc = 0
+            v.mc_rows = mc or None
+            self.multicast = bool(mc)
+            if self.lazy:
+                sb = N.DeviceBuffer(n_state)
+                self._state_bufs[0] = sb
+                self.state[0] = sb.tensor((n_state,), "|u1")
+                v.state[0] = sb.ptr
         self.peer_mapping = (peer_mapping or os.environ.get("FPS_PEER_MAPPING", "vmm")) if shared else "none"
-        if shared and self.peer_mapping == "vmm":
+        if self.replicated:
+            pass
+        elif shared and self.peer_mapping == "vmm":
             # cuMem (VMM) allocations exchanged through torch symmetric memory.  Measured on 2xB200:
             # random 512-byte rows over a 2.4 GB peer shard run at the NVLink rate (2.2 ms / 2M rows)
             # through this mapping but 8x slower (17 ms) through cudaIpcOpenMemHandle mappings, which
@@ -174,9 +214,19 @@ class ShardedTable:
         if vals.dim() == 1:
             vals = vals[:, None]
         m = {"add": 0, "overwrite": 1, "add_norm": 2}[mode]
+        if self.replicated and m == 2:
+            raise ValueError("add_norm is not available on a replicated table")
         N.check(N.lib().fps_table_scatter(C.byref(self._view), N.ptr(ids), ids.numel(), N.ptr(vals),
                                           vals.shape[1], m, N.ptr(flow), N.current_stream()),
                 "fps_table_scatter")
+        if m == 0:
+            self.flush_deltas()
+
+    def flush_deltas(self) -> None:
+        """Replicated table with deferred pushes: forward the deltas accumulated since the last
+        flush to the other replicas (no-op for every other kind of table)."""
+        if self.deferred:
+            N.check(N.lib().fps_table_flush_delta(C.byref(self._view), N.current_stream()), "fps_table_flush_delta")
 
     def load(self, ids, vals) -> None:
         """Model load (``transform_with_model_load``): store the given values; rows become
@@ -187,6 +237,17 @@ class ShardedTable:
         """``(ids, rows[:, :dim+aux])`` of the live rows of the local shard(s), sorted by id -
         the on-close model dump (``Right((id, value))`` records)."""
         import torch
+        if self.replicated:
+            # replicas hold the same values; which rows are live is the union of every replica's touches
+            import torch.distributed as dist
+            self.flush_deltas()
+            torch.cuda.synchronize()
+            self.ctx.barrier()
+            if self.lazy:
+                dist.all_reduce(self.state[0], op=dist.ReduceOp.MAX, group=self.ctx.group)
+            if self.ctx.rank != 0:
+                return (torch.empty(0, device="cuda", dtype=torch.int64),
+                        torch.empty((0, self.dim + self.aux_cols), device="cuda", dtype=torch.float32))
         ids_out, rows_out = [], []
         for s in self.local_shards:
             cap = self.rows_per_shard
@@ -203,6 +264,17 @@ class ShardedTable:
         rows = torch.cat(rows_out)
         order = torch.argsort(ids)
         return ids[order], rows[order]
+
+    def resync(self, src: int = 0) -> None:
+        """Replicated table: make every replica bit-identical to rank ``src``'s (replicas apply the
+        same adds in different orders, so they drift by fp32 rounding)."""
+        if self.replicated:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.synchronize()
+            self.ctx.barrier()
+            dist.broadcast(self.rows[0], src=src, group=self.ctx.group)
+            torch.cuda.synchronize()
 
     def expected_init(self, ids):
         """Host oracle of ``init(id)`` (numpy, fp32)."""

@@ -52,6 +52,21 @@ typedef struct FpsTableView {
   uint64_t  seed;
   int32_t   stream_tag;              /* Philox stream: 0 = PS-side table, 1 = worker-side table  */
   int32_t   lazy;                    /* 1 = use the state bytes                                  */
+  /* Replicated table (small hot tables, e.g. 47K binary-PA weights): every GPU holds the whole
+   * table (n_shards = 1, rows[0] = the local replica, pulls never leave the GPU) and a push is
+   * applied to all replicas - with ONE multimem.red on `mc_rows`, the NVLS multicast alias of the
+   * replicas (NVSwitch does the fan-out), or, without multicast support, one red.add per entry of
+   * replica_rows.  With `delta_rows` (a local zeroed array of the table's shape) pushes are deferred:
+   * a push adds to the local replica and to delta_rows, and fps_table_flush_delta sends the
+   * accumulated deltas to the other replicas after the step - thousands of 4-byte pushes to one hot
+   * weight cross NVLink as one add (measured: single-word multimem.red / red.add top out near 5 G
+   * packets/s per GPU whatever the payload).  n_replicas = 0 for an ordinary sharded table.  No
+   * counterpart in the reference (its shards are always partitions).                           */
+  float*    mc_rows;
+  float*    delta_rows;
+  float*    replica_rows[FPS_MAX_SHARDS];
+  int32_t   n_replicas;
+  int32_t   replica_rank;            /* index of the local replica in replica_rows                */
 } FpsTableView;
 
 /* Device-side flow control + observability block (one per worker; 256 B, zero it before use).
@@ -147,6 +162,11 @@ int fps_mf_online_stream(const FpsTableView* items, const FpsTableView* users,
                          const volatile int32_t* stop, const FpsMfParams* params,
                          uint32_t iteration_wait_ms, uint32_t max_lifetime_ms, FpsFlow* d_flow,
                          void* stream);
+
+/* Replicated table with deferred pushes: add the locally accumulated deltas to every other replica
+ * (red.add.v4 per peer, all-zero 16-byte chunks are skipped) and clear them.  Run it on the stream of
+ * the step kernels, after them.                                                                    */
+int fps_table_flush_delta(const FpsTableView* t, void* stream);
 
 /* Predict r_hat = u.v for n (user, item) pairs (RMSE evaluation).                                */
 int fps_mf_predict(const FpsTableView* items, const FpsTableView* users, const int32_t* d_user_ids,

@@ -1,9 +1,10 @@
 #!/bin/bash
-# launch list + one full ncu capture of the fused MF kernel (run only after the plain command passed)
+# one full ncu capture of a fused MF kernel (run only after the plain command passed)
+#   bash scripts/gpu_ncu_mf.sh direct k_mf_sgd      |  bash scripts/gpu_ncu_mf.sh combine k_mf_sgd_combine
 mkdir -p gpurun_out
-CMD="python bench.py --steps 3 --warmup 3 --no-e2e --users 20000000 --items 2000000"
-$CMD > gpurun_out/plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -c 40 --csv --log-file gpurun_out/launches_mf.csv $CMD > gpurun_out/ncu_launches.log 2>&1
-$CMD > gpurun_out/plain2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:k_mf_sgd -s 3 -c 1 -o gpurun_out/prof_mf $CMD > gpurun_out/ncu_full.log 2>&1
-tail -3 gpurun_out/ncu_full.log; ls -la gpurun_out/
+VARIANT=${1:-direct}
+KERNEL=${2:-k_mf_sgd}
+CMD="python bench.py --steps 3 --warmup 3 --no-e2e --users 20000000 --items 2000000 --variant $VARIANT"
+timeout 600 $CMD > gpurun_out/plain_$VARIANT.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:$KERNEL -s 3 -c 1 -f -o gpurun_out/prof_mf_$VARIANT $CMD > gpurun_out/ncu_full_$VARIANT.log 2>&1
+tail -n 2 gpurun_out/plain_$VARIANT.log; tail -n 3 gpurun_out/ncu_full_$VARIANT.log

@@ -77,6 +77,56 @@ def main():
     ok &= ok4
     print(f"[rank {rank}] all ranks read identical item rows: {ok4}", flush=True)
 
+    # 3b. replicated table: pulls are local, one multimem.red (or a red.add per replica) updates every copy
+    if world > 1:
+        for scalar, dim in ((True, 1), (False, 12)):
+            rt = ShardedTable(5_000, dim, init_range=(0.0, 0.0), ctx=ctx, replicated=True, scalar=scalar, lazy=True)
+            rid = torch.arange(0, 5_000, 3)
+            ctx.barrier()
+            rt.scatter(rid, torch.full((rid.numel(), dim), float(rank + 1)), "add")
+            rt.scatter(rid[:50], torch.full((50, dim), 1.0), "add")
+            torch.cuda.synchronize()
+            ctx.barrier()
+            local = rt.rows[0][:, :dim].cpu().numpy()
+            want_r = np.zeros((5_000, dim), np.float32)
+            want_r[rid.numpy()] = inc
+            want_r[rid[:50].numpy()] += world
+            ok5 = bool(np.array_equal(local, want_r))
+            rt.load(torch.tensor([1, 2]), torch.full((2, dim), 7.0 + rank)) if rank == world - 1 else None
+            torch.cuda.synchronize()
+            ctx.barrier()
+            ok5 &= bool(np.all(rt.rows[0][1:3, :dim].cpu().numpy() == 7.0 + world - 1))
+            d_ids, d_rows = rt.dump()
+            ok5 &= (d_ids.numel() == (rid.numel() + 2 if rank == 0 else 0))
+            ok &= ok5
+            print(f"[rank {rank}] replicated table (scalar={scalar}, multicast={rt.multicast}): every replica holds "
+                  f"the sum of all pushes, load reaches all replicas, dump on rank 0 only: {ok5}", flush=True)
+        from fps_b200.models.pa.device import DevicePA
+        from fps_b200.models.pa.sparse import SparseVector
+        rng = np.random.default_rng(100 + rank)
+        w_true = np.random.default_rng(7).normal(size=300)
+        vecs, labs = [], []
+        for _ in range(4000):
+            ix = np.sort(rng.choice(300, 12, replace=False))
+            vv = rng.normal(size=12)
+            vecs.append(SparseVector(ix, vv, 300))
+            labs.append(bool(vv @ w_true[ix] > 0))
+        pa = DevicePA(300, algorithm="binary", variant="pa_i", aggressiveness=0.5, ctx=ctx)
+        for b0 in range(0, 4000, 500):
+            pa.step_vectors(vecs[b0:b0 + 500], labs[b0:b0 + 500])
+        torch.cuda.synchronize()
+        ctx.barrier()
+        pred = pa.step_vectors(vecs[:1000], None).cpu().numpy() > 0
+        acc = float(np.mean(pred == np.asarray(labs[:1000])))
+        wl = pa.table.rows[0].flatten().clone()
+        ws = [torch.empty_like(wl) for _ in range(world)]
+        dist.all_gather(ws, wl)
+        drift = max(float((x - ws[0]).abs().max()) for x in ws)
+        ok6 = pa.table.replicated and acc > 0.9 and drift < 1e-3 and pa.stats()["remote_pulls"] == 0
+        ok &= ok6
+        print(f"[rank {rank}] replicated binary PA: accuracy {acc:.3f}, replica drift {drift:.2e}, remote pulls "
+              f"{pa.stats()['remote_pulls']}: {ok6}", flush=True)
+
     # 4. P2P probe (rank 0 drives; peer = shard 1)
     res = {}
     if world > 1:
