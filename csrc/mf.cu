@@ -8,7 +8,7 @@
 
 namespace {
 
-template <int LANES, int VPL, bool LAZY, int UNROLL, int MINB = 1>
+template <int LANES, int VPL, bool LAZY, int UNROLL, int MINB = 1, bool REPL = false>
 __global__ void __launch_bounds__(MF_THREADS, MINB)
 k_mf_sgd(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
          const int* __restrict__ uid, const int* __restrict__ iid, const float* __restrict__ rating,
@@ -27,7 +27,7 @@ k_mf_sgd(const __grid_constant__ FpsTableView items, const __grid_constant__ Fps
       for (int q = 0; q < UNROLL; ++q)
         mf_load<LANES, VPL, LAZY>(rec[q], items, users, uid, iid, rating, base + k + q, k + q < cnt, p.local_shard, c);
 #pragma unroll
-      for (int q = 0; q < UNROLL; ++q) mf_update<LANES, VPL, LAZY>(rec[q], items, p, c);
+      for (int q = 0; q < UNROLL; ++q) mf_update<LANES, VPL, LAZY, REPL>(rec[q], items, p, c);
     }
     if (p.pull_limit > 0) flow_release(flow, cnt);
   }
@@ -183,6 +183,12 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
   FPS_REQUIRE(params != nullptr && d_flow != nullptr, FPS_E_INVALID, "fps_mf_sgd_step: params and flow are required");
   if (n <= 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
+  const bool repl = items->n_replicas > 1;
+  if (repl) {
+    FPS_REQUIRE(items->delta_rows != nullptr && !items->lazy && !users->lazy, FPS_E_UNSUPPORTED,
+                "fps_mf_sgd_step: a replicated item table must be eager and use deferred pushes (delta_rows)");
+    FPS_REQUIRE(params->variant == 0, FPS_E_UNSUPPORTED, "fps_mf_sgd_step: replicated items run the direct variant");
+  }
   if (params->variant == 1) {
     return fps_mf_sgd_staged(items, users, d_user_ids, d_item_ids, d_ratings, n, params, d_flow, st);
   }
@@ -211,7 +217,8 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
   // 2-ratings-per-sub-warp build at 56 registers - thread-level parallelism hides the row-load
   // latency better than per-warp ILP here.  `unroll` = 2 / 4 select the ILP builds explicitly.
 #define FN(L, V, Z)                                                                                   \
-  if (Z) k_mf_sgd<L, V, true, 1> MF_ARGS;                                                             \
+  if (repl) k_mf_sgd<L, V, false, 1, 1, true> MF_ARGS;                                                \
+  else if (Z) k_mf_sgd<L, V, true, 1> MF_ARGS;                                                        \
   else if (unroll == 4 && V == 1) k_mf_sgd<L, V, false, (V == 1 ? 4 : 1)> MF_ARGS;                    \
   else if (unroll == 2 || V > 1) k_mf_sgd<L, V, false, (V <= 2 ? 2 : 1)> MF_ARGS;                     \
   else if (params->reserved == 6) k_mf_sgd<L, V, false, 1> MF_ARGS;                                   \
@@ -249,6 +256,7 @@ int fps_mf_online_stream(const FpsTableView* items, const FpsTableView* users, c
                          FpsFlow* d_flow, void* stream) {
   if (int e = check_pair(items, users, "fps_mf_online_stream")) return e;
   FPS_REQUIRE(params && d_flow && tail && stop && ring_capacity > 0, FPS_E_INVALID, "fps_mf_online_stream: bad arguments");
+  FPS_REQUIRE(items->n_replicas <= 1, FPS_E_UNSUPPORTED, "fps_mf_online_stream: replicated item tables are not supported");
   FPS_REQUIRE(max_lifetime_ms > 0 && max_lifetime_ms <= 600000u, FPS_E_INVALID,
               "fps_mf_online_stream: max_lifetime_ms must be in (0, 600000]");
   cudaStream_t st = (cudaStream_t)stream;

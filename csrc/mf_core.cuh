@@ -161,7 +161,9 @@ __device__ __forceinline__ void mf_load(MfRec<VPL>& rec, const FpsTableView& ite
 
 // Compute + push: e = r - u.v; user row updated in place (worker-resident half), item delta
 // reduced into the owner's row.
-template <int LANES, int VPL, bool LAZY>
+// REPL: `items` is a replicated table with deferred pushes - the delta also goes to the local delta
+// array, which fps_table_flush_delta forwards to the other replicas after the launch.
+template <int LANES, int VPL, bool LAZY, bool REPL = false>
 __device__ __forceinline__ void mf_update(MfRec<VPL>& rec, const FpsTableView& items, const FpsMfParams& p,
                                           MfCounters& c) {
   const int lane = threadIdx.x % LANES;
@@ -193,6 +195,7 @@ __device__ __forceinline__ void mf_update(MfRec<VPL>& rec, const FpsTableView& i
       dv.w = fmaf(g, u.w, -decay * v.w);
       st_row4(rec.urow + b * 4, un);
       red_add4(rec.vrow + b * 4, dv);
+      if (REPL) red_add4(items.delta_rows + (rec.vrow - items.rows[0]) + b * 4, dv);
     }
   }
   if (lane == 0) c.loss += e * e;

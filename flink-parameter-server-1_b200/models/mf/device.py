@@ -30,6 +30,7 @@ from ...ops.table import ShardedTable, new_flow, read_flow
 from .vector import FactorIsNotANumberException
 
 VARIANTS = {"direct": 0, "staged": 1, "combine": 2}
+REPLICATE_BELOW_BYTES = 16 << 20
 # "auto": the direct kernel on one GPU (HBM-bound, the sort would only cost time); the combining
 # kernel when items are sharded over several GPUs (NVLink-bound: measured 8.4 vs 4.0 G ratings/s on
 # 8 GPUs with MovieLens-shaped popularity, 6.7 vs 5.7 with uniform items).
@@ -39,14 +40,27 @@ class DeviceMF:
     def __init__(self, n_users: int, n_items: int, num_factors: int = 10, range_min: float = -0.01,
                  range_max: float = 0.01, learning_rate: float = 0.01, *, lambda_: float = 0.0,
                  pull_limit: int = 0, seed: int = 0, lazy: bool = False, variant: str = "auto",
-                 ctx=None, n_shards: Optional[int] = None):
+                 ctx=None, n_shards: Optional[int] = None, replicate_items: Optional[bool] = None):
+        """``replicate_items`` (several GPUs, eager tables): every GPU keeps the whole item table, pulls
+        stay local and the item deltas of a launch cross NVLink once per touched row
+        (``ShardedTable(replicated=True)``).  Default: item tables up to ``REPLICATE_BELOW_BYTES``."""
         import torch
         from ...parallel.device_context import get_context
         self.ctx = ctx or get_context()
         self.n_users, self.n_items, self.num_factors = n_users, n_items, num_factors
+        if replicate_items is None:
+            replicate_items = (self.ctx.distributed and not lazy and variant in ("auto", "direct")
+                               and n_items * ((num_factors + 3) // 4 * 4) * 4 <= REPLICATE_BELOW_BYTES)
+        if replicate_items and lazy:
+            raise ValueError("a replicated item table must be eager (lazy=False)")
         self.items = ShardedTable(n_items, num_factors, n_shards=n_shards, partition="hash",
                                   init_range=(range_min, range_max), seed=seed,
-                                  stream_tag=philox.STREAM_ITEM, lazy=lazy, ctx=self.ctx)
+                                  stream_tag=philox.STREAM_ITEM, lazy=lazy, ctx=self.ctx,
+                                  replicated=bool(replicate_items))
+        if self.items.replicated:
+            if not self.items.deferred:
+                raise ValueError("replicated MF items need deferred pushes (unset FPS_REPLICA_PUSH=immediate)")
+            variant = "direct"
         self.users = ShardedTable(n_users, num_factors, n_shards=n_shards, partition="hash",
                                   init_range=(range_min, range_max), seed=seed,
                                   stream_tag=philox.STREAM_USER, lazy=lazy, ctx=self.ctx,
@@ -54,7 +68,7 @@ class DeviceMF:
         self.params = N.FpsMfParams()
         self.params.lr, self.params.lambda_ = learning_rate, lambda_
         self.params.pull_limit = int(pull_limit)
-        self.params.local_shard = self.ctx.rank if self.ctx.distributed else -1
+        self.params.local_shard = 0 if self.items.replicated else (self.ctx.rank if self.ctx.distributed else -1)
         if variant == "auto":
             variant = "combine" if (self.ctx.distributed and not lazy) else "direct"
         self.variant = variant
@@ -72,6 +86,7 @@ class DeviceMF:
         N.check(N.lib().fps_mf_sgd_step(self.items.view_ref(), self.users.view_ref(), N.ptr(users),
                                         N.ptr(items), N.ptr(ratings), n, C.byref(self.params),
                                         N.ptr(self.flow), N.current_stream()), "fps_mf_sgd_step")
+        self.items.flush_deltas()                # replicated items: this launch's summed deltas -> the other replicas
         self.launches += 1
 
     def _ensure_staging(self, n: int):

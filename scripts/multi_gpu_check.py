@@ -49,7 +49,7 @@ def main():
 
     # 3. fused MF across ranks
     n_users, n_items, dim = 200_000, 50_000, 64
-    mf = DeviceMF(n_users, n_items, dim, 0.0, 0.2, 0.05, pull_limit=1600, seed=1, ctx=ctx)
+    mf = DeviceMF(n_users, n_items, dim, 0.0, 0.2, 0.05, pull_limit=1600, seed=1, ctx=ctx, replicate_items=False)
     g = torch.Generator().manual_seed(10 + rank)
     n = 400_000
     users = (torch.randint(0, n_users // world, (n,), generator=g) * world + rank).int().cuda()
@@ -76,6 +76,24 @@ def main():
     ok4 = all(torch.equal(gathered[0], x) for x in gathered)
     ok &= ok4
     print(f"[rank {rank}] all ranks read identical item rows: {ok4}", flush=True)
+
+    # 3a. the same job with the (12.8 MB) item table replicated on every GPU: local pulls, deferred delta exchange
+    if world > 1:
+        mfr = DeviceMF(n_users, n_items, dim, 0.0, 0.2, 0.05, pull_limit=1600, seed=1, ctx=ctx)
+        for _ in range(15):
+            mfr.step(users, items, ratings)
+        torch.cuda.synchronize()
+        ctx.barrier()
+        r2 = mfr.rmse(users, items, ratings)
+        sr = mfr.stats()
+        mine_r = mfr.items.rows[0][::97].clone()
+        gathered_r = [torch.empty_like(mine_r) for _ in range(world)]
+        dist.all_gather(gathered_r, mine_r)
+        drift_r = max(float((x - gathered_r[0]).abs().max()) for x in gathered_r)
+        ok3a = mfr.items.replicated and r2 < 0.6 * r0 and sr["remote_pulls"] == 0 and drift_r < 1e-3 and sr["max_in_flight"] <= 1600
+        ok &= ok3a
+        print(f"[rank {rank}] MF with replicated items: rmse {r0:.4f} -> {r2:.4f} (sharded {r1:.4f}), replica drift "
+              f"{drift_r:.2e}, remote pulls {sr['remote_pulls']}: {ok3a}", flush=True)
 
     # 3b. replicated table: pulls are local, one multimem.red (or a red.add per replica) updates every copy
     if world > 1:

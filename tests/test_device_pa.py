@@ -122,3 +122,40 @@ def test_cost_matrix_and_wide_rows():
     dumped = dict(r.value for r in pa.dump())
     for i in x.indices.tolist():
         np.testing.assert_allclose(dumped[i], W.get(i, np.zeros(L)), rtol=2e-3, atol=2e-4)
+
+
+@pytest.mark.parametrize("deferred", [True, False])
+@pytest.mark.parametrize("scalar", [True, False])
+def test_replicated_table_push_paths_on_one_gpu(deferred, scalar):
+    """The replicated-table push paths, exercised on ONE GPU by pointing the view at two buffers that
+    play two replicas: deferred (local replica + delta array, then fps_table_flush_delta) and
+    immediate without multicast (one red.add per replica).  The multimem.red path needs two GPUs and
+    is covered by scripts/multi_gpu_check.py."""
+    import ctypes as C
+    from fps_b200.ops import _native as N
+    from fps_b200.ops.table import ShardedTable
+    dim = 1 if scalar else 8
+    t = ShardedTable(1000, dim, n_shards=1, init_range=(0.0, 0.0), scalar=scalar)
+    other = torch.zeros_like(t.rows[0])
+    delta = torch.zeros_like(t.rows[0])
+    v = t._view
+    v.n_replicas, v.replica_rank = 2, 0
+    v.replica_rows[0], v.replica_rows[1] = v.rows[0], other.data_ptr()
+    if deferred:
+        v.delta_rows = delta.data_ptr()
+    ids = torch.tensor([3, 3, 3, 10, 999, 10])
+    vals = torch.arange(1, 7, dtype=torch.float32)[:, None].repeat(1, dim)
+    t.scatter(ids, vals, "add")
+    torch.cuda.synchronize()
+    want = torch.zeros(1000, dim)
+    want.index_add_(0, ids, vals)
+    assert torch.equal(t.rows[0][:, :dim].cpu(), want)
+    if deferred:
+        assert torch.equal(delta[:, :dim].cpu(), want) and float(other.abs().sum()) == 0.0
+        N.check(N.lib().fps_table_flush_delta(C.byref(v), N.current_stream()), "flush")
+        torch.cuda.synchronize()
+        assert float(delta.abs().sum()) == 0.0
+    assert torch.equal(other[:, :dim].cpu(), want)
+    t.load(torch.tensor([5]), torch.full((1, dim), 2.5))          # a model load reaches every replica
+    torch.cuda.synchronize()
+    assert float(other[5, 0]) == 2.5 and float(t.rows[0][5, 0]) == 2.5
