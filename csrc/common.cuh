@@ -57,6 +57,14 @@ struct RowRef {
 
 __device__ __forceinline__ RowRef locate(const FpsTableView& t, long long id) {
   RowRef r;
+  if (t.n_shards == 1) {   // one shard (single GPU, replicated table): no arithmetic at all
+    r.owner = 0;
+    r.slot = id;
+    return r;
+  }
+  // 64-bit division costs ~100 instructions on the GPU and sat on top of the PA kernels' profile;
+  // ids and divisors that fit 32 bits (every table below 4G rows) take the 32-bit path
+  const bool small = ((unsigned long long)id | (unsigned long long)t.div) <= 0xffffffffull;
   if (t.partition == FPS_PART_HASH) {
     // n_shards is tiny; the compiler turns the common power-of-two cases into shifts only when
     // it can see them, so special-case them by hand.
@@ -64,10 +72,17 @@ __device__ __forceinline__ RowRef locate(const FpsTableView& t, long long id) {
     if ((n & (n - 1)) == 0) {
       r.owner = (int)(id & (n - 1));
       r.slot = id >> (31 - __clz(n));
+    } else if (small) {
+      const unsigned q = (unsigned)id / (unsigned)n;
+      r.owner = (int)((unsigned)id - q * (unsigned)n);
+      r.slot = q;
     } else {
       r.owner = (int)(id % n);
       r.slot = id / n;
     }
+  } else if (small) {
+    r.owner = (int)((unsigned)id / (unsigned)t.div);
+    r.slot = (long long)((unsigned)id - (unsigned)r.owner * (unsigned)t.div);
   } else {
     r.owner = (int)(id / t.div);
     r.slot = id - (long long)r.owner * t.div;
