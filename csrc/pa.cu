@@ -165,27 +165,49 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
     for (int v0 = 0; v0 < nvec; v0 += 32) {
       const int vb = v0 + lane;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (long long k = b + warp; k < end; k += WPB) {
-        const long long id = indices[k];
-        const float x = values[k];
-        const RowRef r = locate(t, id);
-        if (!in_table(t, id, r)) { if (lane == 0 && v0 == 0) ++c.bad; continue; }
-        if (v0 == 0 && lane == 0) {
-          n2 = fmaf(x, x, n2);
-          ++c.pulls;
-          if (r.owner != p.local_shard) ++c.remote;
+      // PULL_U features of this warp in flight at once: ids first, then all row loads, then the FMAs
+      // (one feature per iteration left the warp waiting on a dependent id -> row load chain)
+      constexpr int PULL_U = 2;
+      for (long long k0 = b + warp; k0 < end; k0 += WPB * PULL_U) {
+        long long id[PULL_U];
+        float x[PULL_U];
+        RowRef r[PULL_U];
+        bool ok[PULL_U];
+        float4 w[PULL_U];
+#pragma unroll
+        for (int u = 0; u < PULL_U; ++u) {
+          const long long k = k0 + (long long)u * WPB;
+          const bool have = k < end;
+          id[u] = have ? (long long)indices[k] : 0;
+          x[u] = have ? values[k] : 0.f;
+          r[u] = locate(t, id[u]);
+          ok[u] = have && in_table(t, id[u], r[u]);
+          if (have && !ok[u] && lane == 0 && v0 == 0) ++c.bad;
         }
-        if (vb < nvec) {
-          float4 w = ld_row4(t.rows[r.owner] + r.slot * t.stride + vb * 4);
-          if (t.lazy) {
-            const int s = touch_state(t.state[r.owner], r.slot, FPS_ROW_PULLED);
-            if (s == FPS_ROW_PULLED && !(t.init_lo == 0.f && t.init_hi == 0.f)) {
-              const float4 i4 = init_block(t, id, vb);
-              w.x += i4.x; w.y += i4.y; w.z += i4.z; w.w += i4.w;
-            }
+#pragma unroll
+        for (int u = 0; u < PULL_U; ++u) {
+          w[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (ok[u] && vb < nvec) w[u] = ld_row4(t.rows[r[u].owner] + r[u].slot * t.stride + vb * 4);
+        }
+#pragma unroll
+        for (int u = 0; u < PULL_U; ++u) {
+          if (!ok[u]) continue;
+          if (v0 == 0 && lane == 0) {
+            n2 = fmaf(x[u], x[u], n2);
+            ++c.pulls;
+            if (r[u].owner != p.local_shard) ++c.remote;
           }
-          acc.x = fmaf(x, w.x, acc.x); acc.y = fmaf(x, w.y, acc.y);
-          acc.z = fmaf(x, w.z, acc.z); acc.w = fmaf(x, w.w, acc.w);
+          if (vb < nvec) {
+            if (t.lazy) {
+              const int s = touch_state(t.state[r[u].owner], r[u].slot, FPS_ROW_PULLED);
+              if (s == FPS_ROW_PULLED && !(t.init_lo == 0.f && t.init_hi == 0.f)) {
+                const float4 i4 = init_block(t, id[u], vb);
+                w[u].x += i4.x; w[u].y += i4.y; w[u].z += i4.z; w[u].w += i4.w;
+              }
+            }
+            acc.x = fmaf(x[u], w[u].x, acc.x); acc.y = fmaf(x[u], w[u].y, acc.y);
+            acc.z = fmaf(x[u], w[u].z, acc.z); acc.w = fmaf(x[u], w[u].w, acc.w);
+          }
         }
       }
       if (vb < nvec) *reinterpret_cast<float4*>(s_part + warp * t.stride + vb * 4) = acc;
