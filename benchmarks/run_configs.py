@@ -224,13 +224,51 @@ def config6(ctx):
     return out
 
 
+def config7(ctx):
+    """Prequential recommend-then-learn (psOnlineLearnerAndGenerator) on a stream shaped like the authors'
+    session log (69K events, 12.5K users, 19K items; Notebooks/Data_Manipulation.ipynb): device engine
+    vs the host engine (the exact-semantics Python event loop) on a prefix."""
+    import random
+    import time
+    from fps_b200.models.mf import Rating, ps_online_learner_and_generator
+    from fps_b200.models.mf.device_topk import ps_online_learner_and_generator_device
+    from fps_b200.utils.evaluation import NDCGSink
+    if ctx.world_size > 1:
+        return {"config": 7, "skipped": "single-GPU job benchmark"}
+    rnd = random.Random(7)
+    n_users, n_items, n_events = 12_547, 19_048, 69_064
+    pop = [int(n_items * rnd.random() ** 3) for _ in range(n_events)]          # long-tailed popularity
+    stream = [Rating(rnd.randrange(n_users) if rnd.random() < 0.3 else (pop[t] * 7) % n_users, pop[t], 1.0, t)
+              for t in range(n_events)]
+    kw = dict(num_factors=10, range_min=-0.01, range_max=0.01, learning_rate=0.05, negative_sample_rate=9,
+              K=100, worker_k=75, pull_limit=500)
+    res = {"config": 7, "what": "prequential learner+generator, 69K events / 12.5K users / 19K items, rank 10, K=100, 9 negatives"}
+    for bs in (256, 2048):
+        torch.cuda.synchronize()
+        t0 = time.time()
+        out, lg = ps_online_learner_and_generator_device(stream, n_users=n_users, n_items=n_items, batch_size=bs,
+                                                         user_memory=128, **kw)
+        torch.cuda.synchronize()
+        dt = time.time() - t0
+        sink = NDCGSink().consume(out[-20000:])
+        res[f"device_batch{bs}"] = {"events_per_sec": n_events / dt, "seconds": dt, "ndcg_last20k": sink.ndcg,
+                                    "hit_rate_last20k": sink.hit_rate}
+    n_host = 3000
+    t0 = time.time()
+    out_h = ps_online_learner_and_generator(stream[:n_host], user_memory=128, worker_parallelism=4, ps_parallelism=4,
+                                            iteration_wait_time=0, **kw)
+    dt = time.time() - t0
+    res["host_engine_prefix"] = {"events": n_host, "events_per_sec": n_host / dt, "seconds": dt, "outputs": len(out_h)}
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="1,2,3,4,6")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "configs.jsonl"))
     a = ap.parse_args()
     ctx = init_context()
-    fns = {1: config1, 2: config2, 3: config3, 4: config4, 6: config6}
+    fns = {1: config1, 2: config2, 3: config3, 4: config4, 6: config6, 7: config7}
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     for c in [int(x) for x in a.configs.split(",")]:
         try:
