@@ -83,17 +83,39 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
   const long long n_chunks = (n + chunk - 1) / chunk;
   const long long my_chunks = n_chunks > blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   const long long iters = my_chunks * ipc;
-  auto index_of = [&](long long it, int q) -> long long {
-    const long long ci = it / ipc;
-    const int k = (int)(it - ci * ipc) * UNROLL + q;          // position inside the sub-warp's slice
-    // Chunks are visited in a scattered order (multiplicative permutation of the chunk index):
-    // in sorted order a hot item's records sit in adjacent chunks, and adjacent chunks running at
-    // the same time would all start from the same stale row.  Scattering spreads them over the
-    // launch, which restores the staleness profile of the unsorted kernel.
-    const long long lin = (long long)blockIdx.x + ci * gridDim.x;
-    const long long chunk_id = (lin * chunk_mul) % n_chunks;
-    const long long idx = chunk_id * chunk + (long long)grp * slice + k;
-    return (it < iters && k < slice && idx < n) ? idx : -1;
+  static_assert(UNROLL == 1, "the record cursor below walks one record per iteration");
+  // Record cursor.  Chunks are visited in a scattered order (multiplicative permutation of the chunk
+  // index): in sorted order a hot item's records sit in adjacent chunks, and adjacent chunks running
+  // at the same time would all start from the same stale row; scattering spreads them over the
+  // launch, which restores the staleness profile of the unsorted kernel.  The permutation needs a
+  // 64-bit modulo; the cursor evaluates it once per chunk (the first version recomputed it, and two
+  // more 64-bit divisions, for every record: ~250 of the kernel's 340 instructions per record).
+  struct Cursor {
+    long long ci;      // ordinal of this block's chunk
+    int k;             // position inside the sub-warp's slice
+    long long base;    // first record of this sub-warp's slice in that chunk, -1 past the end
+    long long cbase;   // first record of the chunk
+  };
+  auto load_chunk = [&](Cursor& cu) {
+    if (cu.ci < my_chunks) {
+      const long long lin = (long long)blockIdx.x + cu.ci * gridDim.x;
+      cu.cbase = ((lin * chunk_mul) % n_chunks) * chunk;
+      cu.base = cu.cbase + (long long)grp * slice;
+    } else {
+      cu.cbase = 0;
+      cu.base = -1;
+    }
+  };
+  auto index_at = [&](const Cursor& cu) -> long long {
+    const long long idx = cu.base + cu.k;
+    return (cu.base >= 0 && idx < n) ? idx : -1;
+  };
+  auto advance = [&](Cursor& cu) {
+    if (++cu.k == ipc) {
+      cu.k = 0;
+      ++cu.ci;
+      load_chunk(cu);
+    }
   };
   MfCounters c;
   c.clear();
@@ -103,18 +125,19 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
   cy.row = nullptr;
   cy.remote = false;
   MfIds cur[UNROLL], nxt[UNROLL];
-#pragma unroll
-  for (int q = 0; q < UNROLL; ++q) cur[q] = mf_fetch_ids(suid, siid, srating, index_of(0, q));
+  Cursor here{0, 0, -1, 0};
+  load_chunk(here);
+  Cursor ahead = here;
+  advance(ahead);
+  cur[0] = mf_fetch_ids(suid, siid, srating, index_at(here));
   for (long long it = 0; it < iters; ++it) {
-    const int phase = (int)(it % ipc);
+    const int phase = here.k;
     int cnt = 0;
     if (p.pull_limit > 0) {
-      const long long base = ((((long long)blockIdx.x + (it / ipc) * gridDim.x) * chunk_mul) % n_chunks) * chunk;
-      cnt = (int)min((long long)chunk, n - base);
+      cnt = (int)min((long long)chunk, n - here.cbase);
       if (phase == 0) flow_acquire(flow, cnt, p.pull_limit);
     }
-#pragma unroll
-    for (int q = 0; q < UNROLL; ++q) nxt[q] = mf_fetch_ids(suid, siid, srating, index_of(it + 1, q));
+    nxt[0] = mf_fetch_ids(suid, siid, srating, index_at(ahead));
     // ---- issue the loads of this iteration: user rows always, item rows only at run starts
     float4 us[UNROLL][VPL], vn[UNROLL][VPL];
     float* urow[UNROLL];
@@ -205,8 +228,9 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
       carry_flush<LANES, VPL>(cy, nvec);      // slice boundary: bounded staleness
       if (p.pull_limit > 0) flow_release(flow, cnt);
     }
-#pragma unroll
-    for (int q = 0; q < UNROLL; ++q) cur[q] = nxt[q];
+    cur[0] = nxt[0];
+    here = ahead;
+    advance(ahead);
   }
   carry_flush<LANES, VPL>(cy, nvec);
   // rows actually pulled / pushed (after combining) are reported separately from records
