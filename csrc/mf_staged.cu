@@ -71,7 +71,7 @@ __device__ __forceinline__ void carry_flush(Carry<LANES, VPL>& cy, int nvec) {
 }
 
 template <int LANES, int VPL, int UNROLL>
-__global__ void __launch_bounds__(MF_THREADS, (VPL == 1 ? 4 : 1))
+__global__ void __launch_bounds__(MF_THREADS, (VPL == 1 ? (UNROLL == 1 ? 4 : UNROLL == 2 ? 3 : 2) : 1))
 k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
                  const int* __restrict__ suid, const int* __restrict__ siid, const float* __restrict__ srating,
                  long long n, const FpsMfParams p, int chunk, long long chunk_mul, FpsFlow* flow) {
@@ -83,7 +83,6 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
   const long long n_chunks = (n + chunk - 1) / chunk;
   const long long my_chunks = n_chunks > blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   const long long iters = my_chunks * ipc;
-  static_assert(UNROLL == 1, "the record cursor below walks one record per iteration");
   // Record cursor.  Chunks are visited in a scattered order (multiplicative permutation of the chunk
   // index): in sorted order a hot item's records sit in adjacent chunks, and adjacent chunks running
   // at the same time would all start from the same stale row; scattering spreads them over the
@@ -106,9 +105,10 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
       cu.base = -1;
     }
   };
-  auto index_at = [&](const Cursor& cu) -> long long {
-    const long long idx = cu.base + cu.k;
-    return (cu.base >= 0 && idx < n) ? idx : -1;
+  auto index_at = [&](const Cursor& cu, int q) -> long long {   // record q of the UNROLL records of this iteration
+    const int pos = cu.k * UNROLL + q;
+    const long long idx = cu.base + pos;
+    return (cu.base >= 0 && pos < slice && idx < n) ? idx : -1;
   };
   auto advance = [&](Cursor& cu) {
     if (++cu.k == ipc) {
@@ -129,7 +129,8 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
   load_chunk(here);
   Cursor ahead = here;
   advance(ahead);
-  cur[0] = mf_fetch_ids(suid, siid, srating, index_at(here));
+#pragma unroll
+  for (int q = 0; q < UNROLL; ++q) cur[q] = mf_fetch_ids(suid, siid, srating, index_at(here, q));
   for (long long it = 0; it < iters; ++it) {
     const int phase = here.k;
     int cnt = 0;
@@ -137,7 +138,8 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
       cnt = (int)min((long long)chunk, n - here.cbase);
       if (phase == 0) flow_acquire(flow, cnt, p.pull_limit);
     }
-    nxt[0] = mf_fetch_ids(suid, siid, srating, index_at(ahead));
+#pragma unroll
+    for (int q = 0; q < UNROLL; ++q) nxt[q] = mf_fetch_ids(suid, siid, srating, index_at(ahead, q));
     // ---- issue the loads of this iteration: user rows always, item rows only at run starts
     float4 us[UNROLL][VPL], vn[UNROLL][VPL];
     float* urow[UNROLL];
@@ -228,7 +230,8 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
       carry_flush<LANES, VPL>(cy, nvec);      // slice boundary: bounded staleness
       if (p.pull_limit > 0) flow_release(flow, cnt);
     }
-    cur[0] = nxt[0];
+#pragma unroll
+    for (int q = 0; q < UNROLL; ++q) cur[q] = nxt[q];
     here = ahead;
     advance(ahead);
   }
@@ -321,7 +324,16 @@ int fps_mf_sgd_combine(const FpsTableView* items, const FpsTableView* users, con
   auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };
   while (chunk_mul > 1 && gcd(chunk_mul, n_chunks) != 1) chunk_mul -= 2;
   if (chunk_mul < 1) chunk_mul = 1;
-#define LAUNCH(L, V) k_mf_sgd_combine<L, V, 1><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, su, keys, sr, n, *params, chunk, chunk_mul, flow)
+  // records in flight per sub-warp: 1 is best when the rows are in local HBM (bandwidth-bound), more
+  // when they come over NVLink (latency-bound: ~3x the load latency at the same occupancy)
+  const int unroll = params->unroll;
+#define LAUNCH_U(L, V, U) k_mf_sgd_combine<L, V, U><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, su, keys, sr, n, *params, chunk, chunk_mul, flow)
+#define LAUNCH(L, V)                                   \
+  do {                                                 \
+    if (V == 1 && unroll == 2) LAUNCH_U(L, V, 2);      \
+    else if (V == 1 && unroll == 4) LAUNCH_U(L, V, 4); \
+    else LAUNCH_U(L, V, 1);                            \
+  } while (0)
   if (vpl == 1) {
     switch (lanes) {
       case 1: LAUNCH(1, 1); break;
@@ -334,6 +346,7 @@ int fps_mf_sgd_combine(const FpsTableView* items, const FpsTableView* users, con
   } else if (vpl == 2) { LAUNCH(32, 2); }
   else { LAUNCH(32, 4); }
 #undef LAUNCH
+#undef LAUNCH_U
   FPS_LAUNCH_CHECK();
   return 0;
 }
