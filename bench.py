@@ -36,7 +36,7 @@ def parse():
     ap.add_argument("--items", type=int, default=10_000_000)
     ap.add_argument("--rank", type=int, default=128, help="number of factors")
     ap.add_argument("--item-dist", default="movielens", choices=["movielens", "uniform"])
-    ap.add_argument("--variant", default="auto", choices=["auto", "direct", "staged", "combine"],
+    ap.add_argument("--variant", default="auto", choices=["auto", "direct", "combine"],
                     help="auto = direct on one GPU, combine (hot-key pre-combining) when items are sharded over several")
     ap.add_argument("--pull-limit", type=int, default=0)
     ap.add_argument("--lr", type=float, default=0.01)

@@ -29,7 +29,7 @@ from ...ops import philox
 from ...ops.table import ShardedTable, new_flow, read_flow
 from .vector import FactorIsNotANumberException
 
-VARIANTS = {"direct": 0, "staged": 1, "combine": 2}
+VARIANTS = {"direct": 0, "combine": 2}     # (C ABI value 1 is reserved and runs the direct kernel)
 REPLICATE_BELOW_BYTES = 16 << 20
 # "auto": the direct kernel on one GPU (HBM-bound, the sort would only cost time); the combining
 # kernel when items are sharded over several GPUs (NVLink-bound: measured 8.4 vs 4.0 G ratings/s on

@@ -136,12 +136,13 @@ typedef struct FpsMfParams {
   float   lambda;          /* L2 regularisation, reference = 0                                    */
   int32_t pull_limit;      /* 0 = unlimited; else max unanswered pulls per worker                 */
   int32_t local_shard;     /* this worker's index (its user rows, and "remote" accounting)        */
-  int32_t variant;         /* 0 = direct (warp-per-rating, register path)
-                              1 = staged (TMA bulk copies of rows into shared memory + mbarrier)
-                              2 = direct + hot-key pre-combine in shared memory                   */
-  int32_t unroll;          /* ratings a sub-warp keeps in flight: 0 = default (2), 1, 2 or 4       */
-  int32_t blocks_per_sm;   /* persistent grid = SMs * this; 0 = default (6)                       */
-  int32_t reserved;
+  int32_t variant;         /* 0 = direct (sub-warp per rating, rows in registers)
+                              1 = reserved (runs the direct kernel)
+                              2 = combine: ratings sorted by item, one pull + one combined push
+                                  per run of equal items inside a 32-record slice (mf_staged.cu)   */
+  int32_t unroll;          /* ratings a sub-warp keeps in flight: 0 = default (1), 1, 2 or 4       */
+  int32_t blocks_per_sm;   /* cap of the grid = SMs * this; 0 = default (64, i.e. not persistent)  */
+  int32_t reserved;        /* tuning: 6 = the unroll-1 build without the 32-register launch bound  */
 } FpsMfParams;
 
 /* One fused pull-compute-push pass over n ratings: for each (user, item, r): v = pull(item) from
