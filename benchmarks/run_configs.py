@@ -262,13 +262,42 @@ def config7(ctx):
     return res
 
 
+def config8(ctx):
+    """Streaming ring (persistent consumer kernel; the host feeds a device-resident ring through the copy engine): config-2 shapes
+    (rank 64, ML-20M-sized tables), records pushed by the host in 1M-record feeds."""
+    import time
+    from fps_b200.models.mf.device import DeviceMF
+    from fps_b200.models.mf.stream import OnlineStream
+    if ctx.world_size > 1:
+        return {"config": 8, "skipped": "single-GPU streaming benchmark"}
+    nu, ni, dim, n, feed = 138_493, 26_744, 64, 16_000_000, 1_000_000
+    mf = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=0, seed=2, ctx=ctx, variant="direct")
+    g = torch.Generator().manual_seed(8)
+    u = torch.randint(0, nu, (n,), generator=g, dtype=torch.int32).numpy()
+    i = (torch.rand(n, generator=g) ** 3 * ni).int().numpy()
+    r = torch.rand(n, generator=g).numpy()
+    st = OnlineStream(mf, capacity=1 << 22, iteration_wait_ms=500, max_lifetime_ms=120_000)
+    st.feed(u[:feed], i[:feed], r[:feed])          # starts the kernel; warm-up
+    t0 = time.time()
+    for k in range(feed, n, feed):
+        st.feed(u[k:k + feed], i[k:k + feed], r[k:k + feed])
+    while st._retired() < n:
+        time.sleep(0.0005)
+    dt = time.time() - t0
+    reason = st.join()
+    s = mf.stats()
+    return {"config": 8, "what": "online MF rank 64 through the persistent ring consumer (host-fed device ring, copy-engine DMA)",
+            "records": n - feed, "seconds": dt, "records_per_sec": (n - feed) / dt, "exit_reason": reason,
+            "ring_done": s["ring_done"], "relaunches": st.relaunches, "nan_count": s["nan_count"]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="1,2,3,4,6")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "configs.jsonl"))
     a = ap.parse_args()
     ctx = init_context()
-    fns = {1: config1, 2: config2, 3: config3, 4: config4, 6: config6, 7: config7}
+    fns = {1: config1, 2: config2, 3: config3, 4: config4, 6: config6, 7: config7, 8: config8}
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     for c in [int(x) for x in a.configs.split(",")]:
         try:

@@ -119,7 +119,18 @@ k_mf_stream(const __grid_constant__ FpsTableView items, const __grid_constant__ 
       const int k = k0 + grp;
       MfRec<VPL> rec;
       const long long slot = (long long)((base + k) % capacity);
-      mf_load<LANES, VPL, LAZY>(rec, items, users, ring_u, ring_i, ring_r, slot, k < cnt, p.local_shard, c);
+      // ring slots are rewritten by the copy engine while this kernel runs: read them at L2 (.cg), never
+      // through the non-coherent / L1 path a `const __restrict__` load may take
+      MfIds ids;
+      ids.active = k < cnt;
+      ids.u = ids.i = 0;
+      ids.r = 0.f;
+      if (ids.active) {
+        asm volatile("ld.global.cg.s32 %0, [%1];" : "=r"(ids.u) : "l"(ring_u + slot));
+        asm volatile("ld.global.cg.s32 %0, [%1];" : "=r"(ids.i) : "l"(ring_i + slot));
+        asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(ids.r) : "l"(ring_r + slot));
+      }
+      mf_load_ids<LANES, VPL, LAZY>(rec, items, users, ids, p.local_shard, c);
       mf_update<LANES, VPL, LAZY>(rec, items, p, c);
     }
     if (p.pull_limit > 0) flow_release(flow, cnt);

@@ -3,39 +3,28 @@
 Parity: ``PSOnlineMatrixFactorizationWorker.scala:22-90`` driven by
 ``FlinkParameterServer.transform(..., iterationWaitTime)`` (``M/FlinkParameterServer.scala:331-335``):
 records arrive continuously, the job ends after the feedback edge has been idle for
-``iteration_wait_time`` ms (0 = run until stopped).  Here the ring, its tail and the stop flag
-are in mapped pinned host memory (the producer is a host thread - "the data source"), the
-consumer is ``fps_mf_online_stream``: CTAs claim chunks with an atomic on the device-side
-head, idle time is measured with ``%globaltimer`` on the device, and the kernel leaves by
-itself - no host round trip decides termination.  ``max_lifetime_ms`` is a hard cap so a lost
+``iteration_wait_time`` ms (0 = run until stopped).  Here the producer is a host thread ("the data
+source") and the consumer is ``fps_mf_online_stream``: CTAs claim chunks with an atomic on the
+device-side head, idle time is measured with ``%globaltimer`` on the device, and the kernel leaves
+by itself - no host round trip decides termination.  ``max_lifetime_ms`` is a hard cap so a lost
 producer can never wedge the GPU.
+
+The ring, its tail and the stop flag live in *device* memory and are written by the copy engine:
+``feed()`` enqueues the payload copies and then the 8-byte tail on one copy stream (in-order DMA =
+the payload is visible before the tail that announces it) while the kernel keeps running on its own
+stream.  The first version kept the ring in mapped pinned host memory and let the kernel read it
+over PCIe: measured 0.24 M records/s - zero-copy reads of 4-byte fields run one transaction at a
+time on this platform (2.9 MB/s), 30 000x below what the same kernel does on device-resident data.
 """
 from __future__ import annotations
 
 import ctypes as C
 import time
-from typing import Optional
 
 import numpy as np
 
 from ...ops import _native as N
 from ...ops.table import read_flow
-
-
-class _Mapped:
-    def __init__(self, nbytes: int):
-        h, d = C.c_void_p(), C.c_void_p()
-        N.check(N.lib().fps_host_alloc_mapped(C.byref(h), C.byref(d), nbytes), "fps_host_alloc_mapped")
-        self.h, self.d, self.nbytes = h.value, d.value, nbytes
-
-    def array(self, dtype, count: int, offset: int = 0) -> np.ndarray:
-        ct = np.ctypeslib.as_ctypes_type(np.dtype(dtype))
-        return np.ctypeslib.as_array((ct * count).from_address(self.h + offset))
-
-    def free(self) -> None:
-        if self.h:
-            N.lib().fps_host_free(self.h)
-            self.h = 0
 
 
 class OnlineStream:
@@ -46,18 +35,16 @@ class OnlineStream:
         self.capacity = int(capacity)
         self.iteration_wait_ms = int(iteration_wait_ms)
         self.max_lifetime_ms = int(max_lifetime_ms)
-        self._ring = _Mapped(self.capacity * 12)
-        self._ctl = _Mapped(64)
-        self.ring_u = self._ring.array(np.int32, self.capacity, 0)
-        self.ring_i = self._ring.array(np.int32, self.capacity, self.capacity * 4)
-        self.ring_r = self._ring.array(np.float32, self.capacity, self.capacity * 8)
-        self.tail = self._ctl.array(np.uint64, 1, 0)
-        self.stop = self._ctl.array(np.int32, 1, 32)
-        self.tail[0] = 0
-        self.stop[0] = 0
+        self.ring_u = torch.zeros(self.capacity, device="cuda", dtype=torch.int32)
+        self.ring_i = torch.zeros(self.capacity, device="cuda", dtype=torch.int32)
+        self.ring_r = torch.zeros(self.capacity, device="cuda", dtype=torch.float32)
+        self._ctl = torch.zeros(8, device="cuda", dtype=torch.int64)      # [0] tail, [4] stop (as int32)
+        self._tail_host = torch.zeros(1, dtype=torch.int64).pin_memory()
+        self._stop_host = torch.ones(1, dtype=torch.int64).pin_memory()
         self._kernel_stream = torch.cuda.Stream()
         self._copy_stream = torch.cuda.Stream()
         self._done_host = torch.zeros(N.FLOW_BYTES, dtype=torch.uint8).pin_memory()
+        self._staging = None
         self._fed = 0
         self._started = False
         self._exit_seen = 0
@@ -76,10 +63,11 @@ class OnlineStream:
         else:
             mf.flow.zero_()
         torch.cuda.synchronize()
+        ctl = self._ctl.data_ptr()
         with torch.cuda.stream(self._kernel_stream):
             N.check(N.lib().fps_mf_online_stream(
-                mf.items.view_ref(), mf.users.view_ref(), self._ring.d, self._ring.d + self.capacity * 4,
-                self._ring.d + self.capacity * 8, self.capacity, self._ctl.d, self._ctl.d + 32,
+                mf.items.view_ref(), mf.users.view_ref(), self.ring_u.data_ptr(), self.ring_i.data_ptr(),
+                self.ring_r.data_ptr(), self.capacity, ctl, ctl + 32,
                 C.byref(mf.params), self.iteration_wait_ms, self.max_lifetime_ms, N.ptr(mf.flow),
                 self._kernel_stream.cuda_stream), "fps_mf_online_stream")
         self._started = True
@@ -93,16 +81,26 @@ class OnlineStream:
         self._exit_seen = int(f.exit_reason)
         return int(f.ring_done)
 
+    def _stage(self, n: int):
+        """Pinned staging for one feed (grow-only): pageable sources would make the copies synchronous."""
+        import torch
+        if self._staging is None or self._staging[0].numel() < n:
+            self._staging = (torch.empty(n, dtype=torch.int32).pin_memory(),
+                             torch.empty(n, dtype=torch.int32).pin_memory(),
+                             torch.empty(n, dtype=torch.float32).pin_memory())
+        return self._staging
+
     def feed(self, users, items, ratings, timeout_s: float = 30.0) -> None:
         """Append records (CPU tensors / arrays).  Blocks while the ring is full (back-pressure).
         The consumer kernel is launched by the first call: the device-side idle clock must not run
         while the producer is still getting ready (a consumer started earlier could time out before
         the first record arrives and leave the ring unread)."""
+        import torch
         if not self._started:
             self.start()
-        u = np.asarray(users, dtype=np.int32)
-        i = np.asarray(items, dtype=np.int32)
-        r = np.asarray(ratings, dtype=np.float32)
+        u = np.ascontiguousarray(users, dtype=np.int32)
+        i = np.ascontiguousarray(items, dtype=np.int32)
+        r = np.ascontiguousarray(ratings, dtype=np.float32)
         n, pos = len(u), 0
         deadline = time.time() + timeout_s
         while pos < n:
@@ -124,27 +122,35 @@ class OnlineStream:
             take = min(free, n - pos)
             start = self._fed % self.capacity
             first = min(take, self.capacity - start)
-            for ring, src in ((self.ring_u, u), (self.ring_i, i), (self.ring_r, r)):
-                ring[start:start + first] = src[pos:pos + first]
-                if take > first:
-                    ring[0:take - first] = src[pos + first:pos + take]
+            su, si, sr = self._stage(take)
+            self._copy_stream.synchronize()          # the previous feed's copies have left the staging buffers
+            su[:take].copy_(torch.from_numpy(u[pos:pos + take]))
+            si[:take].copy_(torch.from_numpy(i[pos:pos + take]))
+            sr[:take].copy_(torch.from_numpy(r[pos:pos + take]))
             self._fed += take
+            self._tail_host[0] = self._fed
+            with torch.cuda.stream(self._copy_stream):
+                for ring, src in ((self.ring_u, su), (self.ring_i, si), (self.ring_r, sr)):
+                    ring[start:start + first].copy_(src[:first], non_blocking=True)
+                    if take > first:
+                        ring[0:take - first].copy_(src[first:take], non_blocking=True)
+                # same stream, after the payload: the tail that announces it
+                self._ctl[0:1].copy_(self._tail_host, non_blocking=True)
             pos += take
-            self.tail[0] = self._fed          # publish after the payload (x86 store order)
 
     def request_stop(self) -> None:
-        self.stop[0] = 1
+        import torch
+        with torch.cuda.stream(self._copy_stream):
+            self._ctl[4:5].copy_(self._stop_host, non_blocking=True)
 
     def join(self) -> int:
         """Wait for the kernel to leave; returns its exit reason (1 idle, 2 stop, 3 lifetime)."""
         if not self._started:
             return 0
+        self._copy_stream.synchronize()
         self._kernel_stream.synchronize()
         flow = read_flow(self.mf.flow)
         if flow["exit_reason"] == 1 and flow["ring_done"] < self._fed:      # left just before the last feed
             self.start(resume=True)
             self._kernel_stream.synchronize()
-        reason = read_flow(self.mf.flow)["exit_reason"]
-        self._ring.free()
-        self._ctl.free()
-        return reason
+        return read_flow(self.mf.flow)["exit_reason"]

@@ -246,3 +246,25 @@ def test_streaming_kernel_idle_timeout_and_results(native):
     assert s["records"] == n and s["ring_done"] == n
     assert s["max_in_flight"] <= 1600
     assert mf.rmse(u.cuda(), i.cuda(), r.cuda()) < before
+
+
+def test_streaming_consumer_is_rearmed_after_a_producer_gap(native):
+    """A producer pause longer than iteration_wait_ms ends the consumer kernel (idle timeout); the next
+    feed() re-arms it with ring_head / ring_done kept, so nothing is lost or processed twice."""
+    import time
+    from fps_b200.models.mf.device import DeviceMF
+    from fps_b200.models.mf.stream import OnlineStream
+    mf = DeviceMF(2000, 1000, 16, 0.0, 0.2, 0.05, pull_limit=0)
+    g = torch.Generator().manual_seed(4)
+    n = 30_000
+    u = torch.randint(0, 2000, (n,), generator=g, dtype=torch.int32)
+    i = torch.randint(0, 1000, (n,), generator=g, dtype=torch.int32)
+    r = torch.rand(n, generator=g)
+    st = OnlineStream(mf, capacity=1 << 13, iteration_wait_ms=100, max_lifetime_ms=20_000)
+    st.feed(u[:10_000], i[:10_000], r[:10_000])
+    time.sleep(0.6)                                  # > iteration_wait_ms: the kernel leaves
+    st.feed(u[10_000:], i[10_000:], r[10_000:])      # 20 000 records through an 8 192-slot ring
+    reason = st.join()
+    s = mf.stats()
+    assert st.relaunches >= 1
+    assert reason == 1 and s["records"] == n and s["ring_done"] == n and s["nan_count"] == 0
