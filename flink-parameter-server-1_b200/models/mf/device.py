@@ -304,11 +304,38 @@ def ps_online_mf_device(src, num_factors: int = 10, range_min: float = -0.01, ra
     u_all, i_all, r_all = _ratings_to_tensors(ratings, ctx.rank, ctx.world_size)
     gen = torch.Generator(device="cuda").manual_seed(seed * 31 + ctx.rank)
     seen = torch.zeros(n_items, dtype=torch.bool, device="cuda")
-    stream = None
     if streaming:
+        # The producer of a stream is the host: negatives are drawn with numpy and the records go straight
+        # into the ring.  (Besides being the natural place, it keeps the GPU free of producer work - a
+        # torch.randint on a CUDA generator was measured to wait for the resident consumer kernel to leave,
+        # scripts/stream_concurrency_diag.py: 1.5 s = one idle timeout per call.)
         from .stream import OnlineStream
         stream = OnlineStream(mf, capacity=max(1 << 16, 2 * batch_size * (1 + negative_sample_rate)),
                               iteration_wait_ms=iteration_wait_time, max_lifetime_ms=600_000)
+        rng = np.random.default_rng(seed * 31 + ctx.rank)
+        u_np, i_np, r_np = u_all.cpu().numpy(), i_all.cpu().numpy(), r_all.cpu().numpy()
+        seen_np = np.zeros(n_items, dtype=bool)
+        for s in range(0, len(u_np), batch_size):
+            u, i, r = u_np[s:s + batch_size], i_np[s:s + batch_size], r_np[s:s + batch_size]
+            pool = np.flatnonzero(seen_np).astype(np.int32)
+            seen_np[i] = True
+            if negative_sample_rate > 0 and pool.size > 1:
+                k = negative_sample_rate
+                neg_i = pool[rng.integers(0, pool.size, size=(len(u), k))]
+                keep = (neg_i != i[:, None]).ravel()
+                nu = np.repeat(u, k)[keep]
+                ni = neg_i.ravel()[keep]
+                u = np.concatenate([nu, u])
+                i = np.concatenate([ni, i])
+                r = np.concatenate([np.zeros(len(nu), np.float32), r])
+            stream.feed(u, i, r)
+        stream.join()
+        torch.cuda.synchronize()
+        ctx.barrier()
+        mf.stats()
+        out = mf.dump()
+        return (out, mf) if return_model else out
+    stream = None
     for s in range(0, u_all.numel(), batch_size):
         u, i, r = u_all[s:s + batch_size], i_all[s:s + batch_size], r_all[s:s + batch_size]
         pool = torch.nonzero(seen).flatten().int()

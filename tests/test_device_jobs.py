@@ -90,7 +90,7 @@ def test_online_mf_device_job_with_negative_sampling(streaming):
         stream.append(Rating(u, (u % 8) * 25 + rnd.randrange(25), 1.0, t))
     out, mf = ps_online_mf_device(stream, num_factors=8, range_min=-0.1, range_max=0.1, learning_rate=0.2,
                                   negative_sample_rate=3, batch_size=500, streaming=streaming,
-                                  iteration_wait_time=3000, return_model=True)   # > any host gap between feeds
+                                  iteration_wait_time=500, return_model=True)
     s = mf.stats()
     assert s["records"] > len(stream) and s["nan_count"] == 0       # negatives were trained too
     assert s["max_in_flight"] <= 1600
