@@ -108,21 +108,29 @@ def config2(ctx):
     from fps_b200.models.mf.device import DeviceMF
     nu, ni, dim, B = 138_493, 26_744, 64, 1 << 20
     W, rank = ctx.world_size, ctx.rank
-    mf = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=0, seed=2, ctx=ctx)
+    # lr 0.002: with 1M-rating launches per GPU on 26.7K items a hot item takes thousands of concurrent steps
+    # from stale reads; at lr 0.01 that diverges on 2+ GPUs (nan_count > 0 - and a diverged run looks fast
+    # because non-finite updates are skipped), so the learning rate is the one that trains at every N
+    lr = float(os.environ.get("FPS_CONFIG2_LR", "0.002"))
+    mf = DeviceMF(nu, ni, dim, -0.01, 0.01, lr, pull_limit=0, seed=2, ctx=ctx,
+                  variant=os.environ.get("FPS_CONFIG2_VARIANT", "auto"))    # FPS_MF_REPLICATE_ITEMS=1: replicated item table
     g = torch.Generator().manual_seed(2 + rank)
     batches = []
     for _ in range(4):
         u = (torch.randint(0, (nu + W - 1) // W, (B,), generator=g) * W + rank).clamp_(max=nu - 1)
         u = u - ((u - rank) % W)
-        batches.append((u.int().cuda(), zipf_items(B, ni, g).int().cuda(), (torch.rand(B, generator=g) * 4 + 1).cuda()))
+        batches.append((u.int().cuda(), zipf_items(B, ni, g).int().cuda(), (torch.rand(B, generator=g) * 0.8 + 0.2).cuda()))   # stars / 5: the 1..5 scale diverges at lr 0.01 with 1M-rating launches
     k = [0]
 
     def step():
         mf.step(*batches[k[0] % 4])
         k[0] += 1
     ms = timed(step, 3, 20)
+    st = mf.stats(check_nan=False)      # a diverged model would skip its updates and look fast: report it
     return {"config": 2, "what": "online MF rank 64, ML-20M-shaped stream", "n_gpus": W, "variant": mf.variant,
-            "batch_per_gpu": B, "ms_per_step": ms, "ratings_per_sec": B * W / ms * 1e3}
+            "batch_per_gpu": B, "ms_per_step": ms, "ratings_per_sec": B * W / ms * 1e3,
+            "learning_rate": lr, "nan_count": st["nan_count"], "mse": st["loss_sum"] / max(st["records"], 1),
+            "items_table": "replicated" if mf.items.replicated else "sharded"}
 
 
 def _csr_batch(n_ex, n_feat, nnz, g, device):

@@ -198,7 +198,8 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
   if (repl) {
     FPS_REQUIRE(items->delta_rows != nullptr && !items->lazy && !users->lazy, FPS_E_UNSUPPORTED,
                 "fps_mf_sgd_step: a replicated item table must be eager and use deferred pushes (delta_rows)");
-    FPS_REQUIRE(params->variant == 0, FPS_E_UNSUPPORTED, "fps_mf_sgd_step: replicated items run the direct variant");
+    FPS_REQUIRE(params->variant == 0 || params->variant == 2, FPS_E_UNSUPPORTED,
+                "fps_mf_sgd_step: replicated items run the direct or the combine variant");
   }
   if (params->variant == 1) {
     return fps_mf_sgd_staged(items, users, d_user_ids, d_item_ids, d_ratings, n, params, d_flow, st);

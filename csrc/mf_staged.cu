@@ -58,19 +58,24 @@ struct Carry {
   bool remote;
 };
 
-template <int LANES, int VPL>
-__device__ __forceinline__ void carry_flush(Carry<LANES, VPL>& cy, int nvec) {
+// REPL: the item table is replicated with deferred pushes - the combined delta also goes to the local
+// delta array (fps_table_flush_delta forwards it to the other replicas after the launch).
+template <int LANES, int VPL, bool REPL>
+__device__ __forceinline__ void carry_flush(Carry<LANES, VPL>& cy, int nvec, const FpsTableView& items) {
   if (cy.item < 0) return;
   const int lane = threadIdx.x % LANES;
 #pragma unroll
   for (int q = 0; q < VPL; ++q) {
     const int b = lane + q * LANES;
-    if (b < nvec) red_add4(cy.row + b * 4, cy.acc[q]);
+    if (b < nvec) {
+      red_add4(cy.row + b * 4, cy.acc[q]);
+      if (REPL) red_add4(items.delta_rows + (cy.row - items.rows[0]) + b * 4, cy.acc[q]);
+    }
   }
   cy.item = -1;
 }
 
-template <int LANES, int VPL, int UNROLL>
+template <int LANES, int VPL, int UNROLL, bool REPL = false>
 __global__ void __launch_bounds__(MF_THREADS, (VPL == 1 ? (UNROLL == 1 ? 4 : UNROLL == 2 ? 3 : 2) : 1))
 k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
                  const int* __restrict__ suid, const int* __restrict__ siid, const float* __restrict__ srating,
@@ -177,7 +182,7 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
 #pragma unroll
     for (int q = 0; q < UNROLL; ++q) {
       if (fresh[q]) {                   // sub-warp-uniform
-        carry_flush<LANES, VPL>(cy, nvec);
+        carry_flush<LANES, VPL, REPL>(cy, nvec, items);
         cy.item = cur[q].i;
         cy.row = vrow[q];
         cy.remote = rem[q];
@@ -227,7 +232,7 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
       if (lane == 0) c.loss += e * e;
     }
     if (phase == ipc - 1) {
-      carry_flush<LANES, VPL>(cy, nvec);      // slice boundary: bounded staleness
+      carry_flush<LANES, VPL, REPL>(cy, nvec, items);      // slice boundary: bounded staleness
       if (p.pull_limit > 0) flow_release(flow, cnt);
     }
 #pragma unroll
@@ -235,7 +240,7 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
     here = ahead;
     advance(ahead);
   }
-  carry_flush<LANES, VPL>(cy, nvec);
+  carry_flush<LANES, VPL, REPL>(cy, nvec, items);
   // rows actually pulled / pushed (after combining) are reported separately from records
   {
     unsigned int t = pulls;
@@ -327,10 +332,12 @@ int fps_mf_sgd_combine(const FpsTableView* items, const FpsTableView* users, con
   // records in flight per sub-warp: 1 is best when the rows are in local HBM (bandwidth-bound), more
   // when they come over NVLink (latency-bound: ~3x the load latency at the same occupancy)
   const int unroll = params->unroll;
+  const bool repl = items->n_replicas > 1;
 #define LAUNCH_U(L, V, U) k_mf_sgd_combine<L, V, U><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, su, keys, sr, n, *params, chunk, chunk_mul, flow)
 #define LAUNCH(L, V)                                   \
   do {                                                 \
-    if (V == 1 && unroll == 2) LAUNCH_U(L, V, 2);      \
+    if (repl) k_mf_sgd_combine<L, V, 1, true><<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, su, keys, sr, n, *params, chunk, chunk_mul, flow); \
+    else if (V == 1 && unroll == 2) LAUNCH_U(L, V, 2); \
     else if (V == 1 && unroll == 4) LAUNCH_U(L, V, 4); \
     else LAUNCH_U(L, V, 1);                            \
   } while (0)

@@ -19,6 +19,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from typing import Iterable, Optional
 
 import numpy as np
@@ -49,7 +50,13 @@ class DeviceMF:
         self.ctx = ctx or get_context()
         self.n_users, self.n_items, self.num_factors = n_users, n_items, num_factors
         if replicate_items is None:
-            replicate_items = (self.ctx.distributed and not lazy and variant in ("auto", "direct")
+            # opt-in (FPS_MF_REPLICATE_ITEMS=1 or the argument): with deferred pushes every GPU's deltas of a
+            # whole launch land on the others at once, i.e. hot rows take N steps from the same stale value.
+            # SGD tolerates that at gentle learning rates but it is a different staleness profile from the
+            # sharded table (whose pushes land immediately): measured stable on 2 GPUs with the direct
+            # kernel (config 2), divergent with the combine kernel, whose pushes are whole-run deltas.
+            replicate_items = (os.environ.get("FPS_MF_REPLICATE_ITEMS", "0") == "1" and self.ctx.distributed
+                               and not lazy
                                and n_items * ((num_factors + 3) // 4 * 4) * 4 <= REPLICATE_BELOW_BYTES)
         if replicate_items and lazy:
             raise ValueError("a replicated item table must be eager (lazy=False)")
@@ -57,10 +64,8 @@ class DeviceMF:
                                   init_range=(range_min, range_max), seed=seed,
                                   stream_tag=philox.STREAM_ITEM, lazy=lazy, ctx=self.ctx,
                                   replicated=bool(replicate_items))
-        if self.items.replicated:
-            if not self.items.deferred:
-                raise ValueError("replicated MF items need deferred pushes (unset FPS_REPLICA_PUSH=immediate)")
-            variant = "direct"
+        if self.items.replicated and not self.items.deferred:
+            raise ValueError("replicated MF items need deferred pushes (unset FPS_REPLICA_PUSH=immediate)")
         self.users = ShardedTable(n_users, num_factors, n_shards=n_shards, partition="hash",
                                   init_range=(range_min, range_max), seed=seed,
                                   stream_tag=philox.STREAM_USER, lazy=lazy, ctx=self.ctx,
@@ -69,10 +74,18 @@ class DeviceMF:
         self.params.lr, self.params.lambda_ = learning_rate, lambda_
         self.params.pull_limit = int(pull_limit)
         self.params.local_shard = 0 if self.items.replicated else (self.ctx.rank if self.ctx.distributed else -1)
-        if variant == "auto":
-            # (under a pull limiter the direct kernel: a combine sub-warp holds its credits while it walks
-            # its slice serially - measured 109 ms vs ~10 ms per 4M ratings at limit 1600)
-            variant = "combine" if (self.ctx.distributed and not lazy and pull_limit <= 0) else "direct"
+        # "auto" picks per step (see _variant_for): the combine kernel whenever combining pays -
+        #   * items sharded over several GPUs: every combined row is NVLink traffic saved;
+        #   * a batch much larger than the item table (>= 4 ratings per item on average and >= 256K ratings,
+        #     so the sort is amortised): otherwise the hot rows' atomics serialise (measured, rank 64,
+        #     26.7K items, 1M-rating launches: 0.222 ms combine vs 0.387 ms direct);
+        # never for lazy tables (the combine kernel has no life-cycle path) nor under a pull limiter (a
+        # combine sub-warp holds its credits while it walks its slice serially: 109 ms vs ~10 ms per 4M
+        # ratings at limit 1600).
+        self._auto = variant == "auto"
+        self._combine_ok = not lazy and pull_limit <= 0 and not self.items.replicated
+        if self._auto:
+            variant = "combine" if (self._combine_ok and self.ctx.distributed and not self.items.replicated) else "direct"
         self.variant = variant
         self.params.variant = VARIANTS[variant]
         self.flow = new_flow()
@@ -85,6 +98,11 @@ class DeviceMF:
         """One fused pass over a batch already on the device (int32, int32, fp32).  With several
         ranks every user id in the batch must satisfy ``user % world == rank``."""
         n = users.numel()
+        if self._auto and self._combine_ok:
+            dense = n >= 4 * self.n_items and n >= (1 << 18)
+            sharded = self.ctx.distributed and not self.items.replicated
+            self.variant = "combine" if (dense or sharded) else "direct"
+            self.params.variant = VARIANTS[self.variant]
         N.check(N.lib().fps_mf_sgd_step(self.items.view_ref(), self.users.view_ref(), N.ptr(users),
                                         N.ptr(items), N.ptr(ratings), n, C.byref(self.params),
                                         N.ptr(self.flow), N.current_stream()), "fps_mf_sgd_step")

@@ -79,7 +79,7 @@ def main():
 
     # 3a. the same job with the (12.8 MB) item table replicated on every GPU: local pulls, deferred delta exchange
     if world > 1:
-        mfr = DeviceMF(n_users, n_items, dim, 0.0, 0.2, 0.05, pull_limit=1600, seed=1, ctx=ctx)
+        mfr = DeviceMF(n_users, n_items, dim, 0.0, 0.2, 0.05, pull_limit=1600, seed=1, ctx=ctx, replicate_items=True)
         for _ in range(15):
             mfr.step(users, items, ratings)
         torch.cuda.synchronize()
