@@ -154,7 +154,11 @@ def config3(ctx):
     pa.params.pull_limit = 10_000
     ms_lim = timed(lambda: pa.step(indptr, idx, val, lab), 2, 5)
     s = pa.stats()
-    return {"config": 3, "what": "binary PA-I, RCV1-shaped (47K features, 75 nnz)", "n_gpus": ctx.world_size,
+    cpu = None
+    if ctx.rank == 0:
+        from fps_b200.parallel import cpu_baseline
+        cpu = cpu_baseline.bench_pa_binary(F, nnz, 1 << 15, workers=4, shards=4, variant="pa_i", pull_limit=10_000)
+    return {"config": 3, "cpu_restatement": cpu, "what": "binary PA-I, RCV1-shaped (47K features, 75 nnz)", "n_gpus": ctx.world_size,
             "examples_per_gpu": B, "ms_per_step": ms, "examples_per_sec": B * ctx.world_size / ms * 1e3,
             "pull_rows_per_sec": B * nnz * ctx.world_size / ms * 1e3,
             "table": ("replicated, deferred delta exchange" if pa.table.deferred else

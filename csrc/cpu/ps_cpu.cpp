@@ -9,6 +9,7 @@
 //     sends Push(item, delta), the shard adds it (SimplePSLogic.scala:16-25);
 //   * unanswered pulls per worker never exceed pull_limit (WorkerLogic.scala:176-225);
 //   * fp64 like the reference.
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cmath>
@@ -191,6 +192,159 @@ double fps_cpu_mf_run(int W, int S, int dim, int64_t n_per_worker, const int32_t
   double tot = 0.0;
   for (double x : sse) tot += x;
   if (out_sse) *out_sse = tot;
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// Binary passive-aggressive (PassiveAggressiveParameterServer.scala:283-338 with RangePSLogicWithClose):
+// per example one Pull per active feature, the shard answers with the weight, the worker assembles the
+// nnz answers (per-channel FIFO order), computes margin / tau (PA, PA-I, PA-II) and sends one Push per
+// feature.  The limiter counts features, like the reference.  Arrays are [W] blocks: indptr
+// [W][n_per_worker + 1] (offsets local to the worker's block of indices / values, which hold
+// nnz_per_worker entries each), labels [W][n_per_worker] (+1 / -1).  weights [S][div] fp64, range
+// partitioned: owner = id / div.  Returns elapsed seconds; *out_loss = summed hinge loss,
+// *out_mistakes = examples whose prediction (with the pulled weights) had the wrong sign.
+double fps_cpu_pa_binary_run(int W, int S, int64_t n_per_worker, int64_t nnz_per_worker, const int64_t* indptr,
+                             const int32_t* indices, const float* values, const int32_t* labels, double* weights,
+                             int64_t div, int variant, double C, int pull_limit, double* out_loss,
+                             int64_t* out_mistakes) {
+  const uint64_t slot = 64;
+  const uint64_t cap = pow2_at_least((uint64_t)2 * pull_limit + 4);
+  std::vector<Ring> req((size_t)W * S), ans((size_t)S * W);
+  for (auto& r : req) r.init(cap, slot);
+  for (auto& r : ans) r.init(cap, slot);
+  std::atomic<int> workers_done{0};
+  std::vector<double> loss(W, 0.0);
+  std::vector<int64_t> wrong(W, 0);
+  auto t0 = std::chrono::steady_clock::now();
+
+  auto shard_fn = [&](int s) {
+    double* table = weights + (size_t)s * div;
+    while (true) {
+      bool any = false;
+      for (int w = 0; w < W; ++w) {
+        Ring& in = req[(size_t)w * S + s];
+        for (int burst = 0; burst < 64; ++burst) {
+          char* p = in.try_front();
+          if (!p) break;
+          Msg* m = (Msg*)p;
+          double* cell = table + ((int64_t)m->id - (int64_t)s * div);
+          if (m->type == 0) {
+            Ring& out = ans[(size_t)s * W + w];
+            char* q;
+            while (!(q = out.try_reserve())) std::this_thread::yield();
+            Msg* a = (Msg*)q;
+            a->type = 1;
+            a->id = m->id;
+            a->row[0] = *cell;
+            out.commit();
+          } else {
+            *cell += m->row[0];
+          }
+          in.pop();
+          any = true;
+        }
+      }
+      if (!any) {
+        if (workers_done.load(std::memory_order_acquire) == W) {
+          bool empty = true;
+          for (int w = 0; w < W; ++w) empty = empty && req[(size_t)w * S + s].try_front() == nullptr;
+          if (empty) break;
+        }
+        std::this_thread::yield();
+      }
+    }
+  };
+
+  auto worker_fn = [&](int w) {
+    const int64_t* ip = indptr + (size_t)w * (n_per_worker + 1);
+    const int32_t* idx = indices + (size_t)w * nnz_per_worker;
+    const float* val = values + (size_t)w * nnz_per_worker;
+    const int32_t* lab = labels + (size_t)w * n_per_worker;
+    std::vector<double> got((size_t)nnz_per_worker, 0.0);       // pulled weight per (example, feature) position
+    std::vector<int32_t> missing((size_t)n_per_worker, 0);      // answers an example still waits for
+    // per-shard FIFO of nnz positions whose pull is outstanding (channel order == answer order)
+    std::vector<std::vector<int64_t>> pend(S);
+    std::vector<size_t> pend_head(S, 0);
+    std::vector<int64_t> owner_example((size_t)nnz_per_worker);
+    int64_t next_ex = 0, next_pos = 0, in_flight = 0, done_ex = 0;
+    double local_loss = 0.0;
+    int64_t local_wrong = 0;
+    while (done_ex < n_per_worker) {
+      // ---- answers: assemble; a complete example computes and pushes
+      for (int s = 0; s < S; ++s) {
+        Ring& in = ans[(size_t)s * W + w];
+        char* p;
+        while ((p = in.try_front())) {
+          Msg* a = (Msg*)p;
+          const int64_t pos = pend[s][pend_head[s]++];
+          got[pos] = a->row[0];
+          in.pop();
+          --in_flight;
+          const int64_t e = owner_example[pos];
+          if (--missing[e] == 0) {
+            double m = 0.0, n2 = 0.0;
+            for (int64_t k = ip[e]; k < ip[e + 1]; ++k) {
+              m += (double)val[k] * got[k];
+              n2 += (double)val[k] * (double)val[k];
+            }
+            const double y = lab[e] > 0 ? 1.0 : -1.0;
+            if ((m > 0.0) != (y > 0.0)) ++local_wrong;
+            const double l = std::max(0.0, 1.0 - y * m);
+            local_loss += l;
+            double tau = 0.0;
+            if (n2 > 0.0) tau = variant == 0 ? l / n2 : variant == 1 ? std::min(C, l / n2) : l / (n2 + 1.0 / (2.0 * C));
+            if (tau != 0.0) {
+              for (int64_t k = ip[e]; k < ip[e + 1]; ++k) {
+                const int so = (int)((int64_t)idx[k] / div);
+                Ring& out = req[(size_t)w * S + so];
+                char* q;
+                while (!(q = out.try_reserve())) std::this_thread::yield();
+                Msg* msg = (Msg*)q;
+                msg->type = 1;
+                msg->id = idx[k];
+                msg->row[0] = tau * y * (double)val[k];
+                out.commit();
+              }
+            }
+            ++done_ex;
+          }
+        }
+      }
+      // ---- pulls, feature by feature, while credits last
+      while (next_ex < n_per_worker && in_flight < pull_limit) {
+        if (next_pos == ip[next_ex]) {
+          missing[next_ex] = (int32_t)(ip[next_ex + 1] - ip[next_ex]);
+          if (missing[next_ex] == 0) { ++done_ex; ++next_ex; continue; }
+        }
+        const int so = (int)((int64_t)idx[next_pos] / div);
+        Ring& out = req[(size_t)w * S + so];
+        char* q = out.try_reserve();
+        if (!q) break;
+        Msg* msg = (Msg*)q;
+        msg->type = 0;
+        msg->id = idx[next_pos];
+        out.commit();
+        pend[so].push_back(next_pos);
+        owner_example[next_pos] = next_ex;
+        ++in_flight;
+        if (++next_pos == ip[next_ex + 1]) ++next_ex;
+      }
+    }
+    loss[w] = local_loss;
+    wrong[w] = local_wrong;
+    workers_done.fetch_add(1, std::memory_order_release);
+  };
+
+  std::vector<std::thread> th;
+  for (int s = 0; s < S; ++s) th.emplace_back(shard_fn, s);
+  for (int w = 0; w < W; ++w) th.emplace_back(worker_fn, w);
+  for (auto& t : th) t.join();
+  auto t1 = std::chrono::steady_clock::now();
+  double tl = 0.0;
+  int64_t tw = 0;
+  for (int w = 0; w < W; ++w) { tl += loss[w]; tw += wrong[w]; }
+  if (out_loss) *out_loss = tl;
+  if (out_mistakes) *out_mistakes = tw;
   return std::chrono::duration<double>(t1 - t0).count();
 }
 

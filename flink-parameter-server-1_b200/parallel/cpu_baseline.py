@@ -31,6 +31,10 @@ def lib():
         L.fps_cpu_mf_run.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_double, C.c_int,
                                      C.POINTER(C.c_double)]
+        L.fps_cpu_pa_binary_run.restype = C.c_double
+        L.fps_cpu_pa_binary_run.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_int,
+                                            C.POINTER(C.c_double), C.POINTER(C.c_int64)]
         L.fps_cpu_fill_uniform.restype = None
         L.fps_cpu_fill_uniform.argtypes = [C.c_void_p, C.c_int64, C.c_double, C.c_double, C.c_uint64]
         _lib = L
@@ -53,6 +57,48 @@ def run_mf(users, items, ratings, user_table, item_table, lr: float, pull_limit:
                                 user_table.ctypes.data, user_table.shape[1], item_table.ctypes.data, I,
                                 float(lr), int(pull_limit), C.byref(sse))
     return secs, sse.value
+
+
+def run_pa_binary(indptr, indices, values, labels, weights, variant: str = "pa", C_: float = 1.0,
+                  pull_limit: int = 10_000):
+    """Binary passive-aggressive through the C++ PS loop (``PassiveAggressiveParameterServer.scala:283-338``
+    semantics: one pull and one push per active feature, limiter counted in features, range-partitioned
+    weights).  ``indptr`` ``[W, n + 1]`` (offsets local to each worker's block), ``indices`` / ``values``
+    ``[W, nnz]``, ``labels`` ``[W, n]`` (+1 / -1), ``weights`` ``[S, div]`` fp64 updated in place
+    (feature ``f`` lives at ``weights[f // div, f % div]``).  Returns ``(seconds, hinge loss sum, mistakes)``."""
+    indptr = np.ascontiguousarray(indptr, dtype=np.int64)
+    indices = np.ascontiguousarray(indices, dtype=np.int32)
+    values = np.ascontiguousarray(values, dtype=np.float32)
+    labels = np.ascontiguousarray(labels, dtype=np.int32)
+    W, n1 = indptr.shape
+    S, div = weights.shape
+    assert indices.shape == values.shape and indices.shape[0] == W and labels.shape == (W, n1 - 1)
+    assert weights.flags.c_contiguous and weights.dtype == np.float64
+    loss, wrong = C.c_double(0.0), C.c_int64(0)
+    secs = lib().fps_cpu_pa_binary_run(W, S, n1 - 1, indices.shape[1], indptr.ctypes.data, indices.ctypes.data,
+                                       values.ctypes.data, labels.ctypes.data, weights.ctypes.data, div,
+                                       {"pa": 0, "pa_i": 1, "pa_ii": 2}[variant], float(C_), int(pull_limit),
+                                       C.byref(loss), C.byref(wrong))
+    return secs, loss.value, wrong.value
+
+
+def bench_pa_binary(n_features: int = 47_236, nnz: int = 75, examples: int = 1 << 17, workers: int = 4,
+                    shards: int = 4, variant: str = "pa_i", pull_limit: int = 10_000, seed: int = 0) -> dict:
+    """BASELINE config 3 on the CPU restatement (same shapes as ``benchmarks/run_configs.py`` config 3)."""
+    rng = np.random.default_rng(seed)
+    n = examples // workers
+    div = (n_features + shards - 1) // shards
+    idx = np.sort(rng.integers(0, n_features, size=(workers, n, nnz), dtype=np.int32), axis=2).reshape(workers, -1)
+    val = rng.standard_normal((workers, n * nnz)).astype(np.float32)
+    lab = (rng.integers(0, 2, size=(workers, n)) * 2 - 1).astype(np.int32)
+    indptr = np.tile(np.arange(0, (n + 1) * nnz, nnz, dtype=np.int64), (workers, 1))
+    w = np.zeros((shards, div), dtype=np.float64)
+    run_pa_binary(indptr[:, : n // 8 + 1], idx[:, : (n // 8) * nnz], val[:, : (n // 8) * nnz], lab[:, : n // 8], w,
+                  variant, 1.0, pull_limit)                                         # warm-up on a slice
+    secs, loss, wrong = run_pa_binary(indptr, idx, val, lab, w, variant, 1.0, pull_limit)
+    return {"impl": "cpu", "note": "C++ CPU restatement of the PS loop (not Flink), fp64", "workers": workers,
+            "shards": shards, "examples": n * workers, "seconds": secs, "examples_per_sec": n * workers / secs,
+            "feature_pulls_per_sec": n * workers * nnz / secs, "mean_hinge_loss": loss / (n * workers)}
 
 
 def bench_mf(n_users: int, n_items: int, dim: int, batch: int, steps: int, warmup: int, workers: int,

@@ -1,6 +1,7 @@
 """BL2: the C++ CPU parameter server computes the same SGD as a serial numpy loop when run with
 one worker, and stays sane (finite, loss decreasing) with several threads."""
 import numpy as np
+import pytest
 
 from fps_b200.parallel import cpu_baseline
 
@@ -47,3 +48,42 @@ def test_multi_threaded_run_learns():
     assert np.isfinite(U).all() and np.isfinite(V).all() and sse2 < sse1
     res = cpu_baseline.bench_mf(2000, 1000, 16, 8000, steps=2, warmup=1, workers=2, shards=2)
     assert res["ratings_per_sec"] > 0
+
+
+@pytest.mark.parametrize("variant", ["pa", "pa_i", "pa_ii"])
+def test_cpu_pa_binary_equals_serial_rule_at_pull_limit_one(variant):
+    """BL2 for passive-aggressive: with one worker and pull limit 1 the threaded PS loop is the serial
+    algorithm (an example's pushes are on the channel before the next example's first pull)."""
+    rng = np.random.default_rng(1)
+    F, n, nnz, Cc = 50, 200, 6, 0.5
+    idx = np.stack([np.sort(rng.choice(F, nnz, replace=False)) for _ in range(n)]).astype(np.int32)
+    val = rng.standard_normal((n, nnz)).astype(np.float32)
+    lab = np.where((val * rng.standard_normal(F)[idx]).sum(1) > 0, 1, -1).astype(np.int32)
+    indptr = np.arange(0, (n + 1) * nnz, nnz, dtype=np.int64)[None]
+    w = np.zeros((2, 25))                                     # two range-partitioned shards
+    _secs, loss, wrong = cpu_baseline.run_pa_binary(indptr, idx.reshape(1, -1), val.reshape(1, -1), lab[None], w,
+                                                    variant, Cc, 1)
+    ref, want_loss, want_wrong = np.zeros(F), 0.0, 0
+    for e in range(n):
+        x = val[e].astype(np.float64)
+        m, y = float(x @ ref[idx[e]]), float(lab[e])
+        l, n2 = max(0.0, 1.0 - y * m), float(x @ x)
+        want_loss += l
+        want_wrong += (m > 0) != (y > 0)
+        tau = {"pa": l / n2, "pa_i": min(Cc, l / n2), "pa_ii": l / (n2 + 1 / (2 * Cc))}[variant]
+        ref[idx[e]] += tau * y * x
+    assert np.allclose(w.reshape(-1), ref) and abs(loss - want_loss) < 1e-9 and wrong == want_wrong
+
+
+def test_cpu_pa_binary_multi_worker_learns_and_respects_limit():
+    rng = np.random.default_rng(2)
+    F, W, n, nnz = 400, 3, 600, 10
+    truth = rng.standard_normal(F)
+    idx = np.sort(rng.integers(0, F, size=(W, n, nnz), dtype=np.int32), axis=2)
+    val = rng.standard_normal((W, n, nnz)).astype(np.float32)
+    lab = np.where((val * truth[idx]).sum(2) > 0, 1, -1).astype(np.int32)
+    indptr = np.tile(np.arange(0, (n + 1) * nnz, nnz, dtype=np.int64), (W, 1))
+    w = np.zeros((4, 100))
+    _s, _loss, wrong_first = cpu_baseline.run_pa_binary(indptr, idx.reshape(W, -1), val.reshape(W, -1), lab, w, "pa_i", 1.0, 50)
+    _s, _loss, wrong_again = cpu_baseline.run_pa_binary(indptr, idx.reshape(W, -1), val.reshape(W, -1), lab, w, "pa_i", 1.0, 50)
+    assert wrong_again < 0.5 * wrong_first                       # second pass over the same data: far fewer mistakes
