@@ -106,7 +106,7 @@ def config1(ctx):
 def config2(ctx):
     """Online MF rank 64, ML-20M-shaped stream, micro-batches of 1M ratings per GPU."""
     from fps_b200.models.mf.device import DeviceMF
-    nu, ni, dim, B = 138_493, 26_744, 64, 1 << 20
+    nu, ni, dim, B = 138_493, 26_744, 64, int(os.environ.get("FPS_CONFIG2_BATCH", 1 << 20))
     W, rank = ctx.world_size, ctx.rank
     # lr 0.002: with 1M-rating launches per GPU on 26.7K items a hot item takes thousands of concurrent steps
     # from stale reads; at lr 0.01 that diverges on 2+ GPUs (nan_count > 0 - and a diverged run looks fast
