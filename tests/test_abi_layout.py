@@ -44,3 +44,31 @@ def test_ctypes_structs_match_the_c_header(tmp_path):
         for field, _ in cls._fields_:
             assert got[(name, field)] == getattr(cls, field).offset, (name, field)
     assert N.FLOW_BYTES == got[("FpsFlow", "sizeof")]
+
+
+def _header_prototypes():
+    import re
+    text = open(os.path.join(ROOT, "include", "fps_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\b(?:int|size_t|const char\*)\s+(fps_\w+)\s*\(([^;{}]*)\)\s*;", text):
+        args = m.group(2).strip()
+        protos[m.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    return protos
+
+
+def test_every_declared_entry_point_is_exported_with_the_bound_arity():
+    """Header prototype <-> exported symbol <-> ctypes argtypes (loads the library; needs no GPU)."""
+    if not N.available():
+        pytest.skip("libfps_b200.so has not been built")
+    try:
+        L = N.lib()
+    except OSError as e:                      # e.g. no CUDA runtime on the machine
+        pytest.skip(f"cannot load the library here: {e}")
+    protos = _header_prototypes()
+    assert len(protos) >= 30
+    for name, n_args in protos.items():
+        fn = getattr(L, name, None)
+        assert fn is not None, f"{name} is declared in fps_b200.h but not exported"
+        if fn.argtypes is not None:
+            assert len(fn.argtypes) == n_args, (name, len(fn.argtypes), n_args)
