@@ -204,7 +204,9 @@ def main():
     if a.impl == "ours":
         st = model.stats(check_nan=False)
         mse = st["loss_sum"] / max(st["records"], 1)
-        extra = {"nan_count": st["nan_count"], "bad_ids": st["bad_ids"], "mse": mse,
+        # a diverged model makes the kernel skip its (non-finite) updates and look fast: say so in the line
+        extra = {"nan_count": st["nan_count"], "training_valid": st["nan_count"] == 0 and st["bad_ids"] == 0,
+                 "bad_ids": st["bad_ids"], "mse": mse,
                  "remote_pull_fraction": (st["remote_pulls"] / max(st["pulls"], 1)) if world > 1 else 0.0}
     else:
         extra = {"mse": float(model.loss_sum.item()) / max(model.records, 1)}
