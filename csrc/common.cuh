@@ -42,8 +42,6 @@ void fps_set_error(const char* fmt, ...);
 
 int fps_num_sms();   // cached per device
 int fps_check_view(const FpsTableView* v, const char* who);
-int fps_mf_sgd_staged(const FpsTableView*, const FpsTableView*, const int32_t*, const int32_t*,
-                      const float*, int64_t, const FpsMfParams*, FpsFlow*, cudaStream_t);
 int fps_mf_sgd_combine(const FpsTableView*, const FpsTableView*, const int32_t*, const int32_t*,
                        const float*, int64_t, const FpsMfParams*, FpsFlow*, cudaStream_t);
 

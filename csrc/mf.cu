@@ -201,9 +201,8 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
     FPS_REQUIRE(params->variant == 0 || params->variant == 2, FPS_E_UNSUPPORTED,
                 "fps_mf_sgd_step: replicated items run the direct or the combine variant");
   }
-  if (params->variant == 1) {
-    return fps_mf_sgd_staged(items, users, d_user_ids, d_item_ids, d_ratings, n, params, d_flow, st);
-  }
+  FPS_REQUIRE(params->variant == 0 || params->variant == 2, FPS_E_INVALID,
+              "fps_mf_sgd_step: variant must be 0 (direct) or 2 (combine); the tile path has its own entry points");
   if (params->variant == 2) {
     return fps_mf_sgd_combine(items, users, d_user_ids, d_item_ids, d_ratings, n, params, d_flow, st);
   }

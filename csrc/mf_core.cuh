@@ -11,7 +11,9 @@ struct MfCounters {
   unsigned int records, remote, nan, bad;
   __device__ __forceinline__ void clear() { loss = 0.f; records = remote = nan = bad = 0; }
   // block-reduce, then one set of atomics per CTA
-  __device__ __forceinline__ void flush(FpsFlow* flow) {
+  // rows_are_records: the direct kernels pull and push one row per record; the combining kernels count
+  // their (fewer) rows themselves
+  __device__ __forceinline__ void flush(FpsFlow* flow, bool rows_are_records = true) {
     __shared__ float s_loss[MF_THREADS / 32];
     __shared__ unsigned int s_cnt[MF_THREADS / 32][4];
     float l = loss;
@@ -38,8 +40,10 @@ struct MfCounters {
       if (A) {
         atomicAdd(&flow->loss_sum, L);
         atomicAdd((unsigned long long*)&flow->records, A);
-        atomicAdd((unsigned long long*)&flow->pulls, A);
-        atomicAdd((unsigned long long*)&flow->pushes, A - C);
+        if (rows_are_records) {
+          atomicAdd((unsigned long long*)&flow->pulls, A);
+          atomicAdd((unsigned long long*)&flow->pushes, A - C);
+        }
       }
       if (B) {
         atomicAdd((unsigned long long*)&flow->remote_pulls, B);

@@ -246,9 +246,13 @@ k_mf_sgd_combine(const __grid_constant__ FpsTableView items, const __grid_consta
     unsigned int t = pulls;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-    if ((threadIdx.x & 31) == 0 && t) atomicAdd((unsigned long long*)&flow->reserved[0], (unsigned long long)t);
+    if ((threadIdx.x & 31) == 0 && t) {
+      atomicAdd((unsigned long long*)&flow->reserved[0], (unsigned long long)t);
+      atomicAdd((unsigned long long*)&flow->pulls, (unsigned long long)t);     // rows, not records
+      atomicAdd((unsigned long long*)&flow->pushes, (unsigned long long)t);    // one combined push per pulled run
+    }
   }
-  c.flush(flow);
+  c.flush(flow, /*rows_are_records=*/false);
 }
 
 int ensure_scratch(size_t need, void** out) {
@@ -356,13 +360,4 @@ int fps_mf_sgd_combine(const FpsTableView* items, const FpsTableView* users, con
 #undef LAUNCH_U
   FPS_LAUNCH_CHECK();
   return 0;
-}
-
-// variant value 1 is reserved (an early plan staged rows through shared memory with bulk copies; the
-// register path of the direct kernel measured at 92 % of the copy bandwidth, so it was never built).
-int fps_mf_sgd_staged(const FpsTableView* items, const FpsTableView* users, const int32_t* u, const int32_t* i,
-                      const float* r, int64_t n, const FpsMfParams* p, FpsFlow* flow, cudaStream_t st) {
-  FpsMfParams q = *p;
-  q.variant = 0;
-  return fps_mf_sgd_step(items, users, u, i, r, n, &q, flow, (void*)st);
 }

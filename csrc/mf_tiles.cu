@@ -1,0 +1,713 @@
+// MF variant "tiles": hot-key pre-combining in shared memory, pulled rows staged by the TMA engine,
+// no library kernel anywhere on the path (north star items 2 and 3).
+//
+// Step = two phases.
+//
+//   fps_mf_bucket     groups the step's ratings by (item mod NB) with a counting sort of our own
+//                     (k_bucket_count -> k_bucket_scan -> k_bucket_scatter): all records of one item
+//                     end up in the same ~1K-record neighbourhood of a packed 16-byte record array.
+//                     It only depends on the step's inputs, so the caller may run it on another
+//                     stream while the previous step's kernel is still busy (DeviceMF does).
+//   fps_mf_sgd_tiles  one CTA per tile of TILE consecutive packed records: load the tile into shared
+//                     memory, bitonic-sort it by item there, then every (sub-)warp walks a contiguous
+//                     segment of the sorted tile carrying (item, pulled row, accumulated delta) in
+//                     registers: a run of equal items costs ONE pull and one combined push per
+//                     TL_RUN_FLUSH records instead of one of each per record.
+//
+// For rows of up to 512 bytes handled by a whole warp (rank 125..128, the headline shape) the rows
+// are not loaded through registers: each warp runs a private producer/consumer pipeline in which the
+// TMA engine (plain cp.async.bulk, no multicast -> SASS UBLKCP) copies the next RU user rows and the
+// rows of the next RI item runs into a shared-memory ring, completion signalled on mbarriers.  That
+// is ~3 KB in flight per warp without spending a register on it, against 1 KB for the register path
+// - which is what a pull that crosses NVLink (about 3x the latency of local HBM) needs.  The peer
+// rows are read by the copy engine of the *requesting* SM straight from the owner's HBM; the delta
+// goes back as a 16-byte red.add per lane as in the other variants.
+//
+// Pull limiter: credits are handed out hierarchically.  A CTA takes its whole allowance from the
+// worker's pool (FpsFlow.in_flight) once, when it starts, and gives it back when it leaves; inside
+// the CTA the allowance is enforced by construction (a walker never has more item rows outstanding
+// than its share: the carried row plus its ring slots).  No CTA spins on the shared word in steady
+// state, and the grid is sized so that the allowances of all resident CTAs fit the limit.
+#include "common.cuh"
+#include "flow.cuh"
+#include "mf_core.cuh"
+
+namespace {
+
+constexpr int TL_THREADS = 256;
+constexpr int TL_MAX_TILE = 2048;
+constexpr int TL_MAX_BUCKETS = 8192;
+constexpr int TL_RUN_FLUSH = 32;   // records of one run after which the combined delta is pushed
+constexpr int TL_RU = 4;           // user rows in flight per warp (staged path)
+constexpr int TL_RI = 2;           // item rows in flight per warp (staged path)
+constexpr size_t TL_HDR_BYTES = 2 * TL_MAX_BUCKETS * sizeof(int);   // counts + cursors
+
+struct __align__(16) TileRec {
+  int user, item;
+  float rating;
+  int pad;
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tl_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void tl_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tl_mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+  }
+}
+// global -> shared bulk copy executed by the TMA engine (no multicast); completes `bytes` on `bar`
+__device__ __forceinline__ void tl_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_addr(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// phase 1: counting sort by (item & mask) into packed records
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_bucket_count(const int* __restrict__ iid, long long n, int nb, int* __restrict__ counts) {
+  extern __shared__ int s_hist[];
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) s_hist[b] = 0;
+  __syncthreads();
+  const long long per = (n + gridDim.x - 1) / gridDim.x;
+  const long long lo = per * blockIdx.x, hi = min(n, lo + per);
+  for (long long k = lo + threadIdx.x; k < hi; k += blockDim.x) atomicAdd(&s_hist[iid[k] & (nb - 1)], 1);
+  __syncthreads();
+  for (int b = threadIdx.x; b < nb; b += blockDim.x)
+    if (s_hist[b]) atomicAdd(&counts[b], s_hist[b]);
+}
+
+// exclusive scan of counts[nb] into cursors[nb]; clears counts for the next step (one CTA)
+__global__ void __launch_bounds__(1024)
+k_bucket_scan(int* __restrict__ counts, int* __restrict__ cursors, int nb) {
+  __shared__ int s_warp[32];
+  const int per = (nb + 1023) / 1024;
+  const int b0 = threadIdx.x * per;
+  int local[TL_MAX_BUCKETS / 1024];
+  int sum = 0;
+#pragma unroll
+  for (int q = 0; q < TL_MAX_BUCKETS / 1024; ++q) {
+    local[q] = (q < per && b0 + q < nb) ? counts[b0 + q] : 0;
+    sum += local[q];
+  }
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((threadIdx.x & 31) >= o) incl += t;
+  }
+  if ((threadIdx.x & 31) == 31) s_warp[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    int w = s_warp[threadIdx.x];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, w, o);
+      if (threadIdx.x >= o) w += t;
+    }
+    s_warp[threadIdx.x] = w;
+  }
+  __syncthreads();
+  int run = incl - sum + ((threadIdx.x >> 5) ? s_warp[(threadIdx.x >> 5) - 1] : 0);
+#pragma unroll
+  for (int q = 0; q < TL_MAX_BUCKETS / 1024; ++q) {
+    if (q < per && b0 + q < nb) {
+      cursors[b0 + q] = run;
+      counts[b0 + q] = 0;
+      run += local[q];
+    }
+  }
+}
+
+// every CTA owns one contiguous range of the input: count its records per bucket in shared memory,
+// claim one output range per non-empty bucket with a single global atomic, then place the records
+__global__ void __launch_bounds__(256)
+k_bucket_scatter(const int* __restrict__ uid, const int* __restrict__ iid, const float* __restrict__ rating,
+                 long long n, int nb, int* __restrict__ cursors, TileRec* __restrict__ out) {
+  extern __shared__ int s_mem[];
+  int* s_cnt = s_mem;          // [nb] records of this CTA per bucket, then running rank
+  int* s_base = s_mem + nb;    // [nb] first output slot of this CTA in the bucket
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) s_cnt[b] = 0;
+  __syncthreads();
+  const long long per = (n + gridDim.x - 1) / gridDim.x;
+  const long long lo = per * blockIdx.x, hi = min(n, lo + per);
+  for (long long k = lo + threadIdx.x; k < hi; k += blockDim.x) atomicAdd(&s_cnt[iid[k] & (nb - 1)], 1);
+  __syncthreads();
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) {
+    const int c = s_cnt[b];
+    s_base[b] = c ? atomicAdd(&cursors[b], c) : 0;
+    s_cnt[b] = 0;
+  }
+  __syncthreads();
+  for (long long k = lo + threadIdx.x; k < hi; k += blockDim.x) {
+    TileRec r;
+    r.item = iid[k];
+    r.user = uid[k];
+    r.rating = rating ? rating[k] : 0.f;
+    r.pad = 0;
+    const int b = r.item & (nb - 1);
+    const int pos = s_base[b] + atomicAdd(&s_cnt[b], 1);
+    out[pos] = r;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// phase 2: per-tile shared-memory sort + run-carrying SGD
+// ---------------------------------------------------------------------------------------------
+struct TileCounters {
+  float loss;
+  unsigned int records, pulls, pushes, rpulls, rpushes, nan, bad;
+  __device__ __forceinline__ void clear() { loss = 0.f; records = pulls = pushes = rpulls = rpushes = nan = bad = 0; }
+  __device__ __forceinline__ void flush(FpsFlow* flow) {
+    __shared__ float s_loss[TL_THREADS / 32];
+    __shared__ unsigned int s_c[TL_THREADS / 32][7];
+    float l = loss;
+    unsigned int v[7] = {records, pulls, pushes, rpulls, rpushes, nan, bad};
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l += __shfl_xor_sync(0xffffffffu, l, o);
+#pragma unroll
+      for (int q = 0; q < 7; ++q) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+    }
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) {
+      s_loss[w] = l;
+#pragma unroll
+      for (int q = 0; q < 7; ++q) s_c[w][q] = v[q];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double L = 0.0;
+      unsigned long long t[7] = {0, 0, 0, 0, 0, 0, 0};
+      for (int i = 0; i < TL_THREADS / 32; ++i) {
+        L += s_loss[i];
+        for (int q = 0; q < 7; ++q) t[q] += s_c[i][q];
+      }
+      if (t[0]) {
+        atomicAdd(&flow->loss_sum, L);
+        atomicAdd((unsigned long long*)&flow->records, t[0]);
+      }
+      if (t[1]) {
+        atomicAdd((unsigned long long*)&flow->pulls, t[1]);
+        atomicAdd((unsigned long long*)&flow->reserved[0], t[1]);     // "combined_rows" of the older variant
+      }
+      if (t[2]) atomicAdd((unsigned long long*)&flow->pushes, t[2]);
+      if (t[3]) atomicAdd((unsigned long long*)&flow->remote_pulls, t[3]);
+      if (t[4]) atomicAdd((unsigned long long*)&flow->remote_pushes, t[4]);
+      if (t[5]) atomicAdd((unsigned long long*)&flow->nan_count, t[5]);
+      if (t[6]) atomicAdd((unsigned long long*)&flow->bad_ids, t[6]);
+    }
+  }
+};
+
+// Load tile `tile` into shared memory, drop records with ids outside the tables (counted as bad),
+// sort the rest by item.  Returns the number of valid records; s_key[k] = item << 32 | slot in s_rec.
+__device__ __forceinline__ int tile_load_sort(const FpsTableView& items, const FpsTableView& users,
+                                              const TileRec* __restrict__ recs, long long n, long long tile,
+                                              int tile_sz, TileRec* s_rec, unsigned long long* s_key,
+                                              TileCounters& c) {
+  const long long base = tile * tile_sz;
+  const int cnt = (int)min((long long)tile_sz, n - base);
+  int sort_n = 32;
+  while (sort_n < cnt) sort_n <<= 1;
+  for (int k = threadIdx.x; k < sort_n; k += TL_THREADS) {
+    unsigned long long key = ~0ull;
+    if (k < cnt) {
+      const TileRec r = recs[base + k];
+      s_rec[k] = r;
+      const RowRef ir = locate(items, r.item), ur = locate(users, r.user);
+      if (in_table(items, r.item, ir) && in_table(users, r.user, ur) && users.rows[ur.owner] != nullptr)
+        key = ((unsigned long long)(unsigned int)r.item << 32) | (unsigned int)k;
+      else
+        ++c.bad;
+    }
+    s_key[k] = key;
+  }
+  __syncthreads();
+  // bitonic sort, ascending
+  for (int size = 2; size <= sort_n; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = threadIdx.x; t < (sort_n >> 1); t += TL_THREADS) {
+        const int i = 2 * t - (t & (stride - 1));
+        const int j = i + stride;
+        const unsigned long long a = s_key[i], b = s_key[j];
+        const bool up = (i & size) == 0;
+        if ((a > b) == up) {
+          s_key[i] = b;
+          s_key[j] = a;
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // valid records sort before the ~0 keys: binary search for the first invalid key
+  int lo = 0, hi = cnt;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if ((unsigned int)(s_key[mid] >> 32) == 0xffffffffu) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+
+template <int LANES, int VPL>
+struct TCarry {
+  int item;
+  int run_len;
+  float* row;
+  float4 v[VPL];
+  float4 acc[VPL];
+  bool remote;
+};
+
+template <int LANES, int VPL>
+__device__ __forceinline__ void tcarry_push(TCarry<LANES, VPL>& cy, int nvec, TileCounters& c) {
+  const int lane = threadIdx.x % LANES;
+#pragma unroll
+  for (int q = 0; q < VPL; ++q) {
+    const int b = lane + q * LANES;
+    if (b < nvec) red_add4(cy.row + b * 4, cy.acc[q]);
+    cy.acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  cy.run_len = 0;
+  if (lane == 0) {
+    ++c.pushes;
+    if (cy.remote) ++c.rpushes;
+  }
+}
+
+// the SGD step of one record against the carried item row; `us` = user row as loaded
+template <int LANES, int VPL>
+__device__ __forceinline__ void tile_sgd(TCarry<LANES, VPL>& cy, const float4 (&us)[VPL], float* urow, float r,
+                                         bool active, int nvec, const FpsMfParams& p, TileCounters& c) {
+  const int lane = threadIdx.x % LANES;
+  float dot = 0.f;
+#pragma unroll
+  for (int q = 0; q < VPL; ++q) dot += dot4(us[q], cy.v[q]);
+  dot = group_sum<LANES>(dot);
+  if (!active) return;
+  if (lane == 0) ++c.records;
+  const float e = r - dot;
+  if (!isfinite(e)) {
+    if (lane == 0) ++c.nan;
+    return;
+  }
+  const float g = p.lr * e, decay = p.lr * p.lambda;
+#pragma unroll
+  for (int q = 0; q < VPL; ++q) {
+    const int b = lane + q * LANES;
+    if (b < nvec) {
+      const float4 u = us[q], w = cy.v[q];
+      float4 un, dv;
+      un.x = u.x + fmaf(g, w.x, -decay * u.x);
+      un.y = u.y + fmaf(g, w.y, -decay * u.y);
+      un.z = u.z + fmaf(g, w.z, -decay * u.z);
+      un.w = u.w + fmaf(g, w.w, -decay * u.w);
+      st_row4(urow + b * 4, un);
+      dv.x = fmaf(g, u.x, -decay * w.x);
+      dv.y = fmaf(g, u.y, -decay * w.y);
+      dv.z = fmaf(g, u.z, -decay * w.z);
+      dv.w = fmaf(g, u.w, -decay * w.w);
+      cy.acc[q].x += dv.x; cy.acc[q].y += dv.y; cy.acc[q].z += dv.z; cy.acc[q].w += dv.w;
+      cy.v[q].x += dv.x; cy.v[q].y += dv.y; cy.v[q].z += dv.z; cy.v[q].w += dv.w;   // serial SGD inside a run
+    }
+  }
+  if (lane == 0) c.loss += e * e;
+  if (++cy.run_len >= TL_RUN_FLUSH) tcarry_push<LANES, VPL>(cy, nvec, c);
+}
+
+// ---- register path: any rank, LANES lanes per record -----------------------------------------
+template <int LANES, int VPL>
+__global__ void __launch_bounds__(TL_THREADS, (VPL == 1 ? 3 : 1))
+k_mf_tiles_reg(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
+               const TileRec* __restrict__ recs, long long n, const FpsMfParams p, int tile_sz,
+               long long n_tiles, long long tile_mul, int active_groups, int cta_credits, FpsFlow* flow) {
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  TileRec* s_rec = reinterpret_cast<TileRec*>(s_raw);
+  unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_raw + (size_t)tile_sz * sizeof(TileRec));
+  constexpr int GPB = TL_THREADS / LANES;
+  const int grp = threadIdx.x / LANES, lane = threadIdx.x % LANES;
+  const int nvec = items.stride >> 2;
+  const int groups = active_groups > 0 && active_groups < GPB ? active_groups : GPB;   // limiter: fewer walkers
+  TileCounters c;
+  c.clear();
+  if (p.pull_limit > 0) flow_acquire(flow, cta_credits, p.pull_limit);
+  for (long long lin = blockIdx.x; lin < n_tiles; lin += gridDim.x) {
+    const long long tile = (lin * tile_mul) % n_tiles;
+    const int valid = tile_load_sort(items, users, recs, n, tile, tile_sz, s_rec, s_key, c);
+    const int seg = (valid + groups - 1) / groups;
+    const int b0 = min(valid, grp * seg), b1 = grp < groups ? min(valid, b0 + seg) : b0;
+    TCarry<LANES, VPL> cy;
+    cy.item = -1;
+    cy.run_len = 0;
+    cy.row = nullptr;
+    cy.remote = false;
+#pragma unroll
+    for (int q = 0; q < VPL; ++q) cy.acc[q] = cy.v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    // user row of the next record is loaded one iteration ahead (register double buffer)
+    float4 nxt_us[VPL];
+    float* nxt_urow = nullptr;
+    int nxt_user = -1;
+    auto load_user = [&](int k, float4 (&dst)[VPL], float*& urow, int& user) {
+      urow = nullptr;
+      user = -1;
+#pragma unroll
+      for (int q = 0; q < VPL; ++q) dst[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (k < b1) {
+        const TileRec r = s_rec[(unsigned int)s_key[k]];
+        const RowRef ur = locate(users, r.user);
+        urow = users.rows[ur.owner] + ur.slot * users.stride;
+        user = r.user;
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+          const int b = lane + q * LANES;
+          if (b < nvec) dst[q] = ld_row4(urow + b * 4);
+        }
+      }
+    };
+    load_user(b0, nxt_us, nxt_urow, nxt_user);
+    for (int j = 0; j < seg; ++j) {          // block-uniform trip count: shuffles inside
+      const int k = b0 + j;
+      const bool active = k < b1;
+      float4 us[VPL];
+      float* urow = nxt_urow;
+      const int user = nxt_user;
+#pragma unroll
+      for (int q = 0; q < VPL; ++q) us[q] = nxt_us[q];
+      float r = 0.f;
+      if (active) {
+        const unsigned long long key = s_key[k];
+        const int item = (int)(key >> 32);
+        r = s_rec[(unsigned int)key].rating;
+        if (item != cy.item) {                 // sub-warp-uniform
+          if (cy.item >= 0 && cy.run_len > 0) tcarry_push<LANES, VPL>(cy, nvec, c);
+          const RowRef ir = locate(items, item);
+          cy.item = item;
+          cy.row = items.rows[ir.owner] + ir.slot * items.stride;
+          cy.remote = ir.owner != p.local_shard;
+          cy.run_len = 0;
+#pragma unroll
+          for (int q = 0; q < VPL; ++q) {
+            const int b = lane + q * LANES;
+            cy.v[q] = b < nvec ? ld_row4(cy.row + b * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            cy.acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          if (lane == 0) {
+            ++c.pulls;
+            if (cy.remote) ++c.rpulls;
+          }
+        }
+      }
+      load_user(k + 1, nxt_us, nxt_urow, nxt_user);
+      tile_sgd<LANES, VPL>(cy, us, urow, r, active, nvec, p, c);
+      // the row prefetched for the next record was read before this record's store: reload on a clash
+      if (active && nxt_user == user && nxt_urow != nullptr) {
+#pragma unroll
+        for (int q = 0; q < VPL; ++q) {
+          const int b = lane + q * LANES;
+          if (b < nvec) nxt_us[q] = ld_row4(nxt_urow + b * 4);
+        }
+      }
+    }
+    if (cy.item >= 0 && cy.run_len > 0) tcarry_push<LANES, VPL>(cy, nvec, c);
+    __syncthreads();    // the next tile overwrites s_rec / s_key
+  }
+  if (p.pull_limit > 0) flow_release(flow, cta_credits);
+  c.flush(flow);
+}
+
+// ---- TMA-staged path: one warp per segment, rows of <= 512 bytes -------------------------------
+struct WarpRing {
+  float rows[(TL_RU + TL_RI) * 128];     // RU user slots then RI item slots, 512 B each
+  uint64_t bar[TL_RU + TL_RI];
+  float* gptr[TL_RU + TL_RI];            // global address of the row held in each slot
+};
+
+__global__ void __launch_bounds__(TL_THREADS, 4)
+k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
+               const TileRec* __restrict__ recs, long long n, const FpsMfParams p, int tile_sz,
+               long long n_tiles, long long tile_mul, int item_depth, int active_warps, int cta_credits,
+               FpsFlow* flow) {
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  TileRec* s_rec = reinterpret_cast<TileRec*>(s_raw);
+  unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_raw + (size_t)tile_sz * sizeof(TileRec));
+  WarpRing* rings = reinterpret_cast<WarpRing*>(s_raw + (size_t)tile_sz * (sizeof(TileRec) + 8));
+  constexpr int NW = TL_THREADS / 32;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nvec = items.stride >> 2;
+  const uint32_t row_bytes = (uint32_t)items.stride * 4u;
+  WarpRing& ring = rings[w];
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < TL_RU + TL_RI; ++s) tl_mbar_init(&ring.bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  TileCounters c;
+  c.clear();
+  if (p.pull_limit > 0) flow_acquire(flow, cta_credits, p.pull_limit);
+  __syncthreads();
+  uint32_t phase = 0;                     // bit s = parity the next wait on slot s expects
+  item_depth = item_depth < 0 ? 0 : (item_depth > TL_RI ? TL_RI : item_depth);
+  const int RI = item_depth < 1 ? 1 : item_depth;     // item ring slots in use
+  const int walkers = active_warps > 0 && active_warps < NW ? active_warps : NW;   // limiter: fewer walkers
+  for (long long lin = blockIdx.x; lin < n_tiles; lin += gridDim.x) {
+    const long long tile = (lin * tile_mul) % n_tiles;
+    const int valid = tile_load_sort(items, users, recs, n, tile, tile_sz, s_rec, s_key, c);
+    const int seg = (valid + walkers - 1) / walkers;
+    const int b0 = min(valid, w * seg), b1 = w < walkers ? min(valid, b0 + seg) : b0;
+    const int len = b1 - b0;
+    // ---- producer side ----------------------------------------------------------------------
+    auto issue_user = [&](int j) {         // record j of the segment -> user slot j % RU
+      if (j < len && lane == 0) {
+        const TileRec r = s_rec[(unsigned int)s_key[b0 + j]];
+        const RowRef ur = locate(users, r.user);
+        float* g = users.rows[ur.owner] + ur.slot * users.stride;
+        const int s = j % TL_RU;
+        ring.gptr[s] = g;
+        tl_mbar_expect_tx(&ring.bar[s], row_bytes);
+        tl_bulk_g2s(&ring.rows[s * 128], g, row_bytes, &ring.bar[s]);
+      }
+    };
+    int pi = 0, runs_issued = 0, runs_consumed = 0, p_item = -1;
+    auto pump_items = [&](int cap) {       // keep up to `cap` item rows of upcoming runs in flight
+      while (runs_issued - runs_consumed < cap && pi < len) {
+        const int item = (int)(s_key[b0 + pi] >> 32);
+        if (item != p_item) {
+          p_item = item;
+          if (lane == 0) {
+            const RowRef ir = locate(items, item);
+            float* g = items.rows[ir.owner] + ir.slot * items.stride;
+            const int s = TL_RU + runs_issued % RI;
+            ring.gptr[s] = g;
+            tl_mbar_expect_tx(&ring.bar[s], row_bytes);
+            tl_bulk_g2s(&ring.rows[s * 128], g, row_bytes, &ring.bar[s]);
+          }
+          ++runs_issued;
+        }
+        ++pi;
+      }
+    };
+#pragma unroll
+    for (int j = 0; j < TL_RU; ++j) issue_user(j);
+    pump_items(item_depth);
+    // ---- consumer side ----------------------------------------------------------------------
+    TCarry<32, 1> cy;
+    cy.item = -1;
+    cy.run_len = 0;
+    cy.row = nullptr;
+    cy.remote = false;
+    cy.acc[0] = cy.v[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    int recent[TL_RU];                     // users of the last RU records (their stores may be newer than a prefetch)
+#pragma unroll
+    for (int q = 0; q < TL_RU; ++q) recent[q] = -1;
+    for (int j = 0; j < len; ++j) {
+      const unsigned long long key = s_key[b0 + j];
+      const int item = (int)(key >> 32);
+      const TileRec r = s_rec[(unsigned int)key];
+      // user row
+      const int su = j % TL_RU;
+      tl_mbar_wait(&ring.bar[su], (phase >> su) & 1u);
+      phase ^= 1u << su;
+      float* urow = ring.gptr[su];
+      float4 us[1];
+      us[0] = lane < nvec ? *reinterpret_cast<const float4*>(&ring.rows[su * 128 + lane * 4])
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
+      bool clash = false;
+#pragma unroll
+      for (int q = 0; q < TL_RU; ++q) clash |= recent[q] == r.user;
+      if (clash && lane < nvec) us[0] = ld_row4(urow + lane * 4);
+#pragma unroll
+      for (int q = TL_RU - 1; q > 0; --q) recent[q] = recent[q - 1];
+      recent[0] = r.user;
+      __syncwarp();
+      issue_user(j + TL_RU);
+      // item row
+      if (item != cy.item) {
+        if (cy.item >= 0 && cy.run_len > 0) tcarry_push<32, 1>(cy, nvec, c);
+        if (runs_issued == runs_consumed) pump_items(1);     // depth 0 (tight limiter): fetch on demand
+        const int si = TL_RU + runs_consumed % RI;
+        tl_mbar_wait(&ring.bar[si], (phase >> si) & 1u);
+        phase ^= 1u << si;
+        cy.item = item;
+        cy.row = ring.gptr[si];
+        cy.v[0] = lane < nvec ? *reinterpret_cast<const float4*>(&ring.rows[si * 128 + lane * 4])
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+        cy.acc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+        cy.run_len = 0;
+        const RowRef ir = locate(items, item);
+        cy.remote = ir.owner != p.local_shard;
+        if (lane == 0) {
+          ++c.pulls;
+          if (cy.remote) ++c.rpulls;
+        }
+        __syncwarp();
+        ++runs_consumed;
+        pump_items(item_depth);
+      }
+      tile_sgd<32, 1>(cy, us, urow, r.rating, true, nvec, p, c);
+    }
+    if (cy.item >= 0 && cy.run_len > 0) tcarry_push<32, 1>(cy, nvec, c);
+    __syncthreads();
+  }
+  if (p.pull_limit > 0) flow_release(flow, cta_credits);
+  c.flush(flow);
+}
+
+int n_buckets_for(long long n) {
+  int nb = 1;
+  while (nb < TL_MAX_BUCKETS && (long long)nb * 1024 < n) nb <<= 1;
+  return nb;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t fps_mf_tiles_scratch_bytes(int64_t n) {
+  return TL_HDR_BYTES + (size_t)(n > 0 ? n : 0) * sizeof(TileRec) + 256;
+}
+
+int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const float* d_ratings, int64_t n,
+                  void* d_scratch, size_t scratch_bytes, void* stream) {
+  FPS_REQUIRE(d_scratch != nullptr && scratch_bytes >= fps_mf_tiles_scratch_bytes(n), FPS_E_INVALID,
+              "fps_mf_bucket: scratch of %zu bytes is smaller than fps_mf_tiles_scratch_bytes(%lld)", scratch_bytes,
+              (long long)n);
+  FPS_REQUIRE(n <= 0x7fffffffll, FPS_E_TOO_LARGE, "fps_mf_bucket: at most 2^31-1 ratings per step");
+  if (n <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  int* counts = (int*)d_scratch;
+  int* cursors = counts + TL_MAX_BUCKETS;
+  TileRec* out = (TileRec*)((unsigned char*)d_scratch + TL_HDR_BYTES);
+  const int nb = n_buckets_for(n);
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  FPS_CUDA(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+    FPS_CUDA(cudaFuncSetAttribute(k_bucket_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  2 * TL_MAX_BUCKETS * (int)sizeof(int)));
+    attr_done[dev] = true;
+  }
+  FPS_CUDA(cudaMemsetAsync(counts, 0, (size_t)nb * sizeof(int), st));
+  long long blocks = (n + 4095) / 4096;
+  const long long cap = (long long)fps_num_sms() * 4;
+  if (blocks > cap) blocks = cap;
+  k_bucket_count<<<(int)blocks, 256, nb * sizeof(int), st>>>(d_item_ids, n, nb, counts);
+  k_bucket_scan<<<1, 1024, 0, st>>>(counts, cursors, nb);
+  k_bucket_scatter<<<(int)blocks, 256, 2 * nb * sizeof(int), st>>>(d_user_ids, d_item_ids, d_ratings, n, nb, cursors, out);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, const void* d_scratch, int64_t n,
+                     const FpsMfParams* params, FpsFlow* d_flow, void* stream) {
+  if (int e = fps_check_view(items, "fps_mf_sgd_tiles")) return e;
+  if (int e = fps_check_view(users, "fps_mf_sgd_tiles")) return e;
+  FPS_REQUIRE(params != nullptr && d_flow != nullptr && d_scratch != nullptr, FPS_E_INVALID,
+              "fps_mf_sgd_tiles: params, flow and scratch are required");
+  FPS_REQUIRE(items->stride == users->stride && items->dim == users->dim, FPS_E_INVALID,
+              "fps_mf_sgd_tiles: item and user tables must have the same dim/stride");
+  FPS_REQUIRE(!items->lazy && !users->lazy && items->n_replicas <= 1 && items->stride % 4 == 0 && items->stride <= 512,
+              FPS_E_UNSUPPORTED, "fps_mf_sgd_tiles: eager, sharded (not replicated) tables of rank <= 512 only");
+  if (n <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const TileRec* recs = (const TileRec*)((const unsigned char*)d_scratch + TL_HDR_BYTES);
+  const int nvec = items->stride / 4;
+  int lanes = 1;
+  while (lanes < nvec && lanes < 32) lanes <<= 1;
+  const int vpl = (nvec + lanes - 1) / lanes;
+  const int gpb = TL_THREADS / lanes;
+  // params->reserved selects the tile size (512 / 1024 / 2048; 0 = 1024); params->unroll = 1 forces
+  // the register path for shapes the staged path would take
+  int tile_sz = params->reserved == 512 ? 512 : params->reserved == 2048 ? 2048 : 1024;
+  if (n < tile_sz) {
+    tile_sz = 32;
+    while (tile_sz < n) tile_sz <<= 1;
+  }
+  const long long n_tiles = (n + tile_sz - 1) / tile_sz;
+  long long tile_mul = (long long)((double)n_tiles * 0.6180339887) | 1;
+  auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };
+  while (tile_mul > 1 && gcd(tile_mul, n_tiles) != 1) tile_mul -= 2;
+  if (tile_mul < 1) tile_mul = 1;
+  const int sms = fps_num_sms();
+  const bool staged = lanes == 32 && vpl == 1 && params->unroll != 1;
+  long long blocks = n_tiles;
+  // Limiter: the limit is split into per-CTA allowances.  Spread them as widely as possible (one
+  // item row outstanding per walker first, then deeper rings) - the same number of credits moves
+  // more bytes from 148 SMs than from a few.  A walker's outstanding pulls = the carried row (in
+  // compute, its push not yet issued) + the item rows its ring prefetches.
+  const int walkers_full = staged ? TL_THREADS / 32 : gpb;   // (sub-)warps per CTA that pull
+  int active_groups = 0, item_depth = TL_RI, cta_credits = 0;
+  if (params->pull_limit > 0) {
+    const long long limit = params->pull_limit;
+    const long long resident = (long long)sms * (staged ? 4 : 3);
+    int walkers = walkers_full, depth = 1;
+    if (limit < walkers_full) {                       // fewer credits than walkers in one CTA
+      active_groups = walkers = (int)limit;
+      blocks = 1;
+    } else {
+      long long ctas = limit / walkers;               // one outstanding row per walker
+      if (ctas > resident) ctas = resident;
+      if (staged) {
+        depth = (int)(limit / (ctas * walkers));
+        if (depth > TL_RI + 1) depth = TL_RI + 1;
+      }
+      if (blocks > ctas) blocks = ctas;
+    }
+    item_depth = depth - 1;
+    cta_credits = walkers * depth;
+  }
+  const size_t smem_base = (size_t)tile_sz * (sizeof(TileRec) + 8);
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  FPS_CUDA(cudaGetDevice(&dev));
+#define SET_ATTR(K) FPS_CUDA(cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                                  (int)((size_t)TL_MAX_TILE * (sizeof(TileRec) + 8) + (TL_THREADS / 32) * sizeof(WarpRing))))
+  if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+    SET_ATTR(k_mf_tiles_tma);
+    SET_ATTR((k_mf_tiles_reg<1, 1>));
+    SET_ATTR((k_mf_tiles_reg<2, 1>));
+    SET_ATTR((k_mf_tiles_reg<4, 1>));
+    SET_ATTR((k_mf_tiles_reg<8, 1>));
+    SET_ATTR((k_mf_tiles_reg<16, 1>));
+    SET_ATTR((k_mf_tiles_reg<32, 1>));
+    SET_ATTR((k_mf_tiles_reg<32, 2>));
+    SET_ATTR((k_mf_tiles_reg<32, 4>));
+    attr_done[dev] = true;
+  }
+#undef SET_ATTR
+  if (staged) {
+    const size_t smem = smem_base + (TL_THREADS / 32) * sizeof(WarpRing);
+    k_mf_tiles_tma<<<(int)blocks, TL_THREADS, smem, st>>>(*items, *users, recs, n, *params, tile_sz, n_tiles, tile_mul,
+                                                          item_depth, active_groups, cta_credits, d_flow);
+  } else {
+#define LAUNCH(L, V) k_mf_tiles_reg<L, V><<<(int)blocks, TL_THREADS, smem_base, st>>>(*items, *users, recs, n, *params, tile_sz, n_tiles, tile_mul, active_groups, cta_credits, d_flow)
+    if (vpl == 1) {
+      switch (lanes) {
+        case 1: LAUNCH(1, 1); break;
+        case 2: LAUNCH(2, 1); break;
+        case 4: LAUNCH(4, 1); break;
+        case 8: LAUNCH(8, 1); break;
+        case 16: LAUNCH(16, 1); break;
+        default: LAUNCH(32, 1); break;
+      }
+    } else if (vpl == 2) { LAUNCH(32, 2); }
+    else { LAUNCH(32, 4); }
+#undef LAUNCH
+  }
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

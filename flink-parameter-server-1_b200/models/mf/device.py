@@ -28,13 +28,17 @@ from ...entities import Left, Right
 from ...ops import _native as N
 from ...ops import philox
 from ...ops.table import ShardedTable, new_flow, read_flow
+from ...utils.observability import nvtx_range
 from .vector import FactorIsNotANumberException
 
-VARIANTS = {"direct": 0, "combine": 2}     # (C ABI value 1 is reserved and runs the direct kernel)
+# direct  : one (sub-)warp per rating, rows in registers (csrc/mf.cu)
+# tiles   : own counting sort by item bucket + per-CTA shared-memory sort, run-carrying SGD, rows staged
+#           by the TMA engine (csrc/mf_tiles.cu) - the hot-key pre-combining path
+# combine : the round-1 pre-combining path (cub radix sort + register-carried runs, csrc/mf_staged.cu);
+#           kept for A/B comparisons only
+VARIANTS = {"direct": 0, "combine": 2, "tiles": 3}
 REPLICATE_BELOW_BYTES = 16 << 20
-# "auto": the direct kernel on one GPU (HBM-bound, the sort would only cost time); the combining
-# kernel when items are sharded over several GPUs (NVLink-bound: measured 8.4 vs 4.0 G ratings/s on
-# 8 GPUs with MovieLens-shaped popularity, 6.7 vs 5.7 with uniform items).
+# "auto": see DeviceMF._variant_for.
 
 
 class DeviceMF:
@@ -83,30 +87,108 @@ class DeviceMF:
         # combine sub-warp holds its credits while it walks its slice serially: 109 ms vs ~10 ms per 4M
         # ratings at limit 1600).
         self._auto = variant == "auto"
+        self._tiles_ok = not lazy and not self.items.replicated and self.items.stride <= 512
         self._combine_ok = not lazy and pull_limit <= 0 and not self.items.replicated
+        if variant == "tiles" and not self._tiles_ok:
+            raise ValueError("variant='tiles' needs eager, sharded (not replicated) tables of rank <= 512")
+        if variant == "combine" and not self._combine_ok:
+            variant = "direct"
+        self._prefer_tiles = os.environ.get("FPS_MF_PREFER_TILES", "0") == "1"
         if self._auto:
-            variant = "combine" if (self._combine_ok and self.ctx.distributed and not self.items.replicated) else "direct"
+            variant = "tiles" if (self._tiles_ok and (self.ctx.distributed or self._prefer_tiles)) else "direct"
         self.variant = variant
-        self.params.variant = VARIANTS[variant]
+        self.params.variant = VARIANTS[variant] if variant != "tiles" else 0
         self.flow = new_flow()
         self._copy_stream = None
         self._staging = None
+        self._tile_slots = None
+        self._tile_stream = None
+        self._tile_slot = 0
         self.launches = 0
+        self.kernel_launches = 0          # kernels of ours launched by step() so far
+
+    def _variant_for(self, n: int) -> str:
+        """``auto``: the tile path whenever combining pays -
+          * items sharded over several GPUs: every combined row is NVLink traffic saved;
+          * a batch much larger than the item table (>= 4 ratings per item on average and >= 256K
+            ratings): otherwise the hot rows' atomics serialise;
+        else the direct kernel.  Lazy and replicated tables always run the direct kernel."""
+        if not self._tiles_ok:
+            return "direct"
+        dense = n >= 4 * self.n_items and n >= (1 << 18)
+        return "tiles" if (dense or self.ctx.distributed or self._prefer_tiles) else "direct"
+
+    # -- tile path plumbing -----------------------------------------------------------------------
+    def _tile_scratch(self, n: int):
+        """Two caller-owned scratch buffers (never allocated inside a step once they are large
+        enough) and a side stream on which the bucketing of a step can run."""
+        import torch
+        need = int(N.lib().fps_mf_tiles_scratch_bytes(n))
+        if self._tile_slots is None or self._tile_slots[0]["bytes"] < need:
+            torch.cuda.synchronize()
+            grow = need + need // 4
+            self._tile_slots = [{"buf": torch.empty(grow, device="cuda", dtype=torch.uint8), "bytes": grow,
+                                 "ready": torch.cuda.Event(), "free": torch.cuda.Event(), "used": False}
+                                for _ in range(2)]
+            if self._tile_stream is None:
+                self._tile_stream = torch.cuda.Stream(priority=-1)
+        s = self._tile_slots[self._tile_slot]
+        self._tile_slot ^= 1
+        return s
+
+    def _bucket(self, users, items, ratings, n: int, ready_event=None, on_stream=None):
+        """Phase 1 of a tile step.  ``ready_event`` (a ``torch.cuda.Event`` after which the inputs are
+        valid) lets it run on the side stream while the previous step's kernel is still busy; without
+        it the inputs are taken to be ordered after everything already queued on the current stream,
+        previous step included."""
+        import torch
+        s = self._tile_scratch(n)
+        main = torch.cuda.current_stream()
+        side = on_stream or (self._tile_stream if ready_event is not None else main)
+        if side is not main:
+            if ready_event is not None:
+                side.wait_event(ready_event)
+            if s["used"]:
+                side.wait_event(s["free"])           # the kernel that last read this scratch has finished
+        N.check(N.lib().fps_mf_bucket(N.ptr(users), N.ptr(items), N.ptr(ratings), n, s["buf"].data_ptr(),
+                                      s["bytes"], side.cuda_stream), "fps_mf_bucket")
+        if side is not main:
+            s["ready"].record(side)
+            main.wait_event(s["ready"])
+        self.kernel_launches += 3
+        return s
+
+    def _run_tiles(self, s, n: int) -> None:
+        import torch
+        N.check(N.lib().fps_mf_sgd_tiles(self.items.view_ref(), self.users.view_ref(), s["buf"].data_ptr(), n,
+                                         C.byref(self.params), N.ptr(self.flow), N.current_stream()),
+                "fps_mf_sgd_tiles")
+        s["free"].record(torch.cuda.current_stream())
+        s["used"] = True
+        self.kernel_launches += 1
 
     # -- training ------------------------------------------------------------------------------
-    def step(self, users, items, ratings) -> None:
+    def step(self, users, items, ratings, ready_event=None) -> None:
         """One fused pass over a batch already on the device (int32, int32, fp32).  With several
-        ranks every user id in the batch must satisfy ``user % world == rank``."""
+        ranks every user id in the batch must satisfy ``user % world == rank``.
+        ``ready_event``: optional ``torch.cuda.Event`` after which the three tensors are valid; with it
+        the tile path groups this batch on a side stream while the previous step is still running."""
         n = users.numel()
-        if self._auto and self._combine_ok:
-            dense = n >= 4 * self.n_items and n >= (1 << 18)
-            sharded = self.ctx.distributed and not self.items.replicated
-            self.variant = "combine" if (dense or sharded) else "direct"
-            self.params.variant = VARIANTS[self.variant]
-        N.check(N.lib().fps_mf_sgd_step(self.items.view_ref(), self.users.view_ref(), N.ptr(users),
-                                        N.ptr(items), N.ptr(ratings), n, C.byref(self.params),
-                                        N.ptr(self.flow), N.current_stream()), "fps_mf_sgd_step")
-        self.items.flush_deltas()                # replicated items: this launch's summed deltas -> the other replicas
+        if n == 0:
+            return
+        with nvtx_range("fps.mf.step"):
+            if self._auto:
+                self.variant = self._variant_for(n)
+            if self.variant == "tiles":
+                s = self._bucket(users, items, ratings, n, ready_event)
+                self._run_tiles(s, n)
+            else:
+                self.params.variant = VARIANTS[self.variant]
+                N.check(N.lib().fps_mf_sgd_step(self.items.view_ref(), self.users.view_ref(), N.ptr(users),
+                                                N.ptr(items), N.ptr(ratings), n, C.byref(self.params),
+                                                N.ptr(self.flow), N.current_stream()), "fps_mf_sgd_step")
+                self.kernel_launches += 3 if self.variant == "combine" else 1
+            self.items.flush_deltas()            # replicated items: this launch's summed deltas -> the other replicas
         self.launches += 1
 
     def _ensure_staging(self, n: int):
@@ -151,8 +233,17 @@ class DeviceMF:
             st["i"][:n].copy_(items_h, non_blocking=True)
             st["r"][:n].copy_(ratings_h, non_blocking=True)
             st["copied"].record(self._copy_stream)
-        main.wait_event(st["copied"])
-        self.step(st["u"][:n], st["i"][:n], st["r"][:n])
+        if self._auto:
+            self.variant = self._variant_for(n)
+        if self.variant == "tiles":
+            # the grouping of this batch runs on the copy stream right behind its H2D copies, i.e. while
+            # the previous step's kernel is still busy on the main stream
+            s = self._bucket(st["u"][:n], st["i"][:n], st["r"][:n], n, on_stream=self._copy_stream)
+            self._run_tiles(s, n)
+            self.launches += 1
+        else:
+            main.wait_event(st["copied"])
+            self.step(st["u"][:n], st["i"][:n], st["r"][:n])
         view = self.flow[N.FLOW_LOSS_OFFSET:N.FLOW_LOSS_OFFSET + 16].view(torch.float64)
         st["loss"].copy_(view, non_blocking=True)
         st["done"].record(main)

@@ -138,6 +138,9 @@ def lib() -> C.CDLL:
         "fps_table_dump_shard": (C.c_int, [P(FpsTableView), C.c_int, i64, i64, vp, vp, i64, vp, vp]),
         "fps_mf_sgd_step": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, vp, i64, P(FpsMfParams), vp, vp]),
         "fps_mf_predict": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, i64, vp, vp]),
+        "fps_mf_tiles_scratch_bytes": (C.c_size_t, [i64]),
+        "fps_mf_bucket": (C.c_int, [vp, vp, vp, i64, vp, C.c_size_t, vp]),
+        "fps_mf_sgd_tiles": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, i64, P(FpsMfParams), vp, vp]),
         "fps_mf_online_stream": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, vp, u64, vp, vp,
                                            P(FpsMfParams), C.c_uint32, C.c_uint32, vp, vp]),
         "fps_pa_step": (C.c_int, [P(FpsTableView), vp, vp, vp, vp, i64, P(FpsPaParams), vp, vp, vp]),
@@ -151,6 +154,7 @@ def lib() -> C.CDLL:
         "fps_topk_pack_items": (C.c_int, [vp, i32, i64, i32, vp, vp]),
         "fps_lemp_topk_packed": (C.c_int, [vp, i32, i64, vp, vp, vp, i64, i32, i32, i32, vp, C.c_size_t,
                                            vp, vp, vp, vp]),
+        "fps_lemp_topk_static": (C.c_int, [vp, i32, i64, vp, i32, vp, vp, i64, i32, i32, i32, vp, vp, vp, vp]),
         "fps_topk_simt": (C.c_int, [vp, i32, i64, vp, i32, vp, i64, i32, i32, vp, C.c_size_t, vp, vp, vp]),
         "fps_topk_merge": (C.c_int, [vp, vp, i32, i64, i32, i32, vp, i32, vp, vp, vp]),
     }

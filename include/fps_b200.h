@@ -136,10 +136,10 @@ typedef struct FpsMfParams {
   float   lambda;          /* L2 regularisation, reference = 0                                    */
   int32_t pull_limit;      /* 0 = unlimited; else max unanswered pulls per worker                 */
   int32_t local_shard;     /* this worker's index (its user rows, and "remote" accounting)        */
-  int32_t variant;         /* 0 = direct (sub-warp per rating, rows in registers)
-                              1 = reserved (runs the direct kernel)
-                              2 = combine: ratings sorted by item, one pull + one combined push
-                                  per run of equal items inside a 32-record slice (mf_staged.cu)   */
+  int32_t variant;         /* fps_mf_sgd_step: 0 = direct (sub-warp per rating, rows in registers)
+                              2 = combine (round-1 path kept for comparison): cub radix sort by item,
+                                  one pull + one combined push per run inside a 32-record slice
+                              (the tile path, fps_mf_bucket + fps_mf_sgd_tiles, ignores this field)   */
   int32_t unroll;          /* ratings a sub-warp keeps in flight: 0 = default (1), 1, 2 or 4       */
   int32_t blocks_per_sm;   /* cap of the grid = SMs * this; 0 = default (64, i.e. not persistent)  */
   int32_t reserved;        /* tuning: 6 = the unroll-1 build without the 32-register launch bound  */
@@ -163,6 +163,26 @@ int fps_mf_online_stream(const FpsTableView* items, const FpsTableView* users,
                          const volatile int32_t* stop, const FpsMfParams* params,
                          uint32_t iteration_wait_ms, uint32_t max_lifetime_ms, FpsFlow* d_flow,
                          void* stream);
+
+/* Variant "tiles" (csrc/mf_tiles.cu): hot-key pre-combining in shared memory with TMA-staged rows,
+ * in two calls so that the first can overlap the previous step.
+ *   fps_mf_bucket     groups the n ratings by (item mod NB) into packed records in caller-owned
+ *                     scratch (fps_mf_tiles_scratch_bytes(n) bytes) with three small kernels of our
+ *                     own (count / scan / scatter); depends on the inputs only.
+ *   fps_mf_sgd_tiles  one CTA per tile of bucketed records: shared-memory sort by item, then every
+ *                     warp walks a sorted segment carrying (item, row, combined delta); rows of up to
+ *                     512 bytes arrive through per-warp cp.async.bulk rings.  Same update rule as
+ *                     fps_mf_sgd_step; one pull per run of equal items, one push per <= 32 records of it.
+ *                     Eager, sharded tables of rank <= 512 (else FPS_E_UNSUPPORTED).  params->reserved =
+ *                     tile size (512 / 1024 / 2048, 0 = 1024); params->unroll = 1 forces the register
+ *                     path.  Pull limiter: every CTA takes its allowance from FpsFlow.in_flight once.
+ * Replaces X1 / X2 of M/FlinkParameterServer.scala:265-317 and SimplePSLogic.scala:16-25 like
+ * fps_mf_sgd_step, with far fewer messages for popular items.                                      */
+size_t fps_mf_tiles_scratch_bytes(int64_t n);
+int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const float* d_ratings, int64_t n,
+                  void* d_scratch, size_t scratch_bytes, void* stream);
+int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, const void* d_scratch, int64_t n,
+                     const FpsMfParams* params, FpsFlow* d_flow, void* stream);
 
 /* Replicated table with deferred pushes: add the locally accumulated deltas to every other replica
  * (red.add.v4 per peer, all-zero 16-byte chunks are skipped) and clear them.  Run it on the stream of

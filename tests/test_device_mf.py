@@ -268,3 +268,126 @@ def test_streaming_consumer_is_rearmed_after_a_producer_gap(native):
     s = mf.stats()
     assert st.relaunches >= 1
     assert reason == 1 and s["records"] == n and s["ring_done"] == n and s["nan_count"] == 0
+
+
+# ---- tile variant: own bucketing + shared-memory sort / pre-combine + TMA-staged rows ---------------
+@pytest.mark.parametrize("dim,shards", [(10, 1), (16, 3), (64, 2), (100, 1), (128, 2), (128, 3), (200, 1)])
+def test_tiles_variant_equals_oracle_on_conflict_free_schedule(native, dim, shards):
+    """Register path (dim < 125 or > 128) and the cp.async.bulk ring path (dim 100 / 128) against the
+    serial fp64 rule; inside a wave every item is distinct, so item order is a valid serial order."""
+    from fps_b200.models.mf.device import DeviceMF, conflict_free_waves
+    rng = np.random.default_rng(dim + shards)
+    nu, ni, n = 400, 150, 3000
+    u = rng.integers(0, nu, n).astype(np.int32)
+    i = rng.integers(0, ni, n).astype(np.int32)
+    r = rng.random(n).astype(np.float32)
+    mf = DeviceMF(nu, ni, dim, 0.0, 0.3, 0.05, lambda_=0.01, n_shards=shards, seed=5, variant="tiles")
+    U0 = mf.users.expected_init(np.arange(nu))
+    V0 = mf.items.expected_init(np.arange(ni))
+    du, di, dr = (torch.from_numpy(x).cuda() for x in (u, i, r))
+    ou, oi, orr = [], [], []
+    for wu, wi, wv in conflict_free_waves(du, di, dr):
+        mf.step(wu, wi, wv)
+        order = torch.argsort(wi, stable=True)
+        ou += wu[order].tolist(); oi += wi[order].tolist(); orr += wv[order].tolist()
+    torch.cuda.synchronize()
+    U, V = serial_sgd_oracle(ou, oi, orr, U0, V0, 0.05, 0.01)
+    s = mf.stats()
+    assert s["records"] == n and s["bad_ids"] == 0
+    assert s["pulls"] == n and s["pushes"] == n          # every run has length one here
+    np.testing.assert_allclose(mf.items.gather(torch.arange(ni)).cpu().numpy(), V, rtol=2e-4, atol=2e-5)
+    np.testing.assert_allclose(mf.users.gather(torch.arange(nu)).cpu().numpy(), U, rtol=2e-4, atol=2e-5)
+
+
+@pytest.mark.parametrize("dim", [64, 128])
+def test_tiles_single_walker_is_the_serial_rule_even_with_repeated_users(native, dim):
+    """pull_limit=1 leaves one walker: the whole batch is one serial pass in item order.  Five users
+    repeat all the time, so every prefetched user row is stale by the time it is used - the reload on
+    a clash must make the result equal to the serial rule anyway; runs of equal items are carried."""
+    from fps_b200.models.mf.device import DeviceMF
+    rng = np.random.default_rng(dim)
+    nu, ni, n = 5, 300, 900
+    u = rng.integers(0, nu, n).astype(np.int32)
+    i = np.repeat(rng.permutation(ni).astype(np.int32), 3)           # every item three times, adjacent
+    r = rng.random(n).astype(np.float32)
+    # equal items keep their input order only if the bucketing happens to; make the three records of an
+    # item identical in (user, rating) so that any order among them is the same serial schedule
+    u = np.repeat(u[::3], 3); r = np.repeat(r[::3], 3)
+    mf = DeviceMF(nu, ni, dim, 0.0, 0.3, 0.05, lambda_=0.01, n_shards=1, seed=7, variant="tiles", pull_limit=1)
+    U0 = mf.users.expected_init(np.arange(nu))
+    V0 = mf.items.expected_init(np.arange(ni))
+    mf.step(*(torch.from_numpy(x).cuda() for x in (u, i, r)))
+    torch.cuda.synchronize()
+    order = np.argsort(i, kind="stable")
+    U, V = serial_sgd_oracle(u[order], i[order], r[order], U0, V0, 0.05, 0.01)
+    s = mf.stats()
+    assert s["records"] == n and s["pulls"] == ni and s["max_in_flight"] == 1 and s["in_flight"] == 0
+    np.testing.assert_allclose(mf.items.gather(torch.arange(ni)).cpu().numpy(), V, rtol=5e-4, atol=5e-5)
+    np.testing.assert_allclose(mf.users.gather(torch.arange(nu)).cpu().numpy(), U, rtol=5e-4, atol=5e-5)
+
+
+@pytest.mark.parametrize("dim,shards", [(16, 1), (64, 3), (128, 2)])
+def test_tiles_variant_combines_hot_keys_and_learns_like_direct(native, dim, shards):
+    from fps_b200.models.mf.device import DeviceMF
+    g = torch.Generator().manual_seed(3)
+    m = 200_000
+    uu = torch.randint(0, 20_000, (m,), generator=g, dtype=torch.int32).cuda()
+    ii = (torch.rand(m, generator=g) ** 3 * 5_000).int().cuda()
+    rr = (0.5 + 0.3 * torch.sin(uu.float()) * torch.cos(ii.float())).cuda()
+    ev = torch.cuda.Event()
+    ev.record()
+    res = {}
+    for variant, limit in (("direct", 0), ("tiles", 0), ("tiles", 1600), ("tiles", 100_000)):
+        m2 = DeviceMF(20_000, 5_000, dim, 0.0, 0.5 / dim ** 0.5, 0.01, n_shards=shards, seed=9, variant=variant,
+                      pull_limit=limit)
+        for k in range(8):
+            m2.step(uu, ii, rr, ready_event=ev if k % 2 else None)      # both orderings of the bucketing
+        torch.cuda.synchronize()
+        st = m2.stats(check_nan=False)
+        res[(variant, limit)] = (m2.rmse(uu, ii, rr), st)
+        assert st["nan_count"] == 0 and st["records"] == 8 * m and st["bad_ids"] == 0, (variant, limit, st)
+        if limit:
+            assert 0 < st["max_in_flight"] <= limit and st["in_flight"] == 0, st
+    t = res[("tiles", 0)][1]
+    assert t["pulls"] < 0.8 * 8 * m and t["pushes"] < 0.8 * 8 * m          # hot keys really were combined
+    assert t["pulls"] == t["combined_rows"]
+    for key, (rmse, _) in res.items():
+        assert abs(rmse - res[("direct", 0)][0]) < 0.05 and rmse < 0.4, res
+
+
+def test_tiles_variant_counts_bad_ids_and_handles_odd_sizes(native):
+    from fps_b200.models.mf.device import DeviceMF
+    mf = DeviceMF(50, 40, 128, 0.0, 0.1, 0.01, variant="tiles")
+    for n in (1, 31, 33, 1025, 2500):
+        g = torch.Generator().manual_seed(n)
+        u = torch.randint(0, 50, (n,), generator=g, dtype=torch.int32)
+        i = torch.randint(0, 40, (n,), generator=g, dtype=torch.int32)
+        u[0] = 50          # outside the user table
+        if n > 1:
+            i[1] = -3      # outside the item table
+        mf.reset_stats()
+        mf.step(u.cuda(), i.cuda(), torch.rand(n, generator=g).cuda())
+        torch.cuda.synchronize()
+        s = mf.stats()
+        assert s["bad_ids"] == min(n, 2) and s["records"] == n - min(n, 2), (n, s)
+    assert torch.isfinite(mf.items.gather(torch.arange(40))).all()
+
+
+def test_step_from_host_pipelines_the_tile_path(native):
+    from fps_b200.models.mf.device import DeviceMF
+    g = torch.Generator().manual_seed(5)
+    n = 50_000
+    batches = []
+    for _ in range(3):
+        u = torch.randint(0, 3000, (n,), generator=g, dtype=torch.int32).pin_memory()
+        i = torch.randint(0, 2000, (n,), generator=g, dtype=torch.int32).pin_memory()
+        r = torch.rand(n, generator=g).pin_memory()
+        batches.append((u, i, r))
+    mf = DeviceMF(3000, 2000, 128, 0.0, 0.1, 0.02, variant="tiles")
+    first = None
+    for k in range(12):
+        mf.step_from_host(*batches[k % 3])
+    last = mf.flush_host_steps()
+    s = mf.stats()
+    assert s["records"] == 12 * n and s["nan_count"] == 0
+    assert 0 < last < 0.5
