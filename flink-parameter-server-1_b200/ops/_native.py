@@ -132,6 +132,8 @@ def lib() -> C.CDLL:
         "fps_host_alloc_mapped": (C.c_int, [P(vp), P(vp), C.c_size_t]),
         "fps_host_free": (C.c_int, [vp]),
         "fps_p2p_probe": (C.c_int, [vp, vp, C.c_size_t, C.c_int, C.c_int, P(f32), vp]),
+        "fps_p2p_probe_random": (C.c_int, [vp, i64, C.c_int, i64, C.c_int, C.c_int, C.c_int, C.c_int, P(f32), vp]),
+        "fps_p2p_probe_mixed": (C.c_int, [vp, vp, i64, i64, C.c_int, C.c_int, P(f32), vp]),
         "fps_table_init_shard": (C.c_int, [P(FpsTableView), C.c_int, i64, vp]),
         "fps_table_gather": (C.c_int, [P(FpsTableView), vp, i64, vp, C.c_int, vp, vp]),
         "fps_table_scatter": (C.c_int, [P(FpsTableView), vp, i64, vp, C.c_int, C.c_int, vp, vp]),

@@ -10,7 +10,8 @@ and the two partitioners (hash ``M/FlinkParameterServer.scala:126-134``; range
   * ``lazy=True`` keeps the reference's life-cycle (untouched / first-pulled / first-pushed) in
     one state byte per row; ``lazy=False`` materialises ``init(id)`` eagerly (the benchmark mode);
   * with ``world_size > 1`` shard ``r`` lives on rank ``r`` and every rank maps all shards
-    through CUDA IPC, so kernels dereference peer rows directly over NVLink.
+    through VMM symmetric memory (or CUDA IPC with ``peer_mapping="ipc"``), so kernels dereference
+    peer rows directly over NVLink.
 """
 from __future__ import annotations
 

@@ -10,7 +10,7 @@ Parity:
     without recursion.
 
 The device engine implements the same bound with a credit counter in device memory
-(``csrc/flow_control.cuh``); ``pull_limit`` means the same thing in both engines:
+(``csrc/flow.cuh``, per-CTA allowances in ``csrc/mf_tiles.cu``); ``pull_limit`` means the same thing in both engines:
 *the number of unanswered pulls per worker instance never exceeds the limit*.
 """
 from __future__ import annotations

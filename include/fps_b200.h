@@ -38,7 +38,8 @@ enum { FPS_PART_HASH = 0, FPS_PART_RANGE = 1 };
 enum { FPS_ROW_UNTOUCHED = 0, FPS_ROW_PULLED = 1, FPS_ROW_PUSHED = 2 };
 
 /* A sharded fp32 table as seen from one GPU: rows[s] is shard s' base pointer mapped into this
- * process (its own cudaMalloc for the local shard, a cudaIpc mapping for a peer's).            */
+ * process (its own allocation for the local shard; a peer's shard through a VMM symmetric-memory mapping,
+ * or a cudaIpc mapping with peer_mapping="ipc").            */
 typedef struct FpsTableView {
   float*    rows[FPS_MAX_SHARDS];
   uint8_t*  state[FPS_MAX_SHARDS];   /* NULL everywhere = eager table                            */
@@ -110,6 +111,16 @@ int fps_host_free(void* h_ptr);
  * into dst.  Returns elapsed ms of `iters` launches via *ms.                                       */
 int fps_p2p_probe(float* d_dst, const float* d_src, size_t bytes, int mode, int iters, float* ms,
                   void* stream);
+
+/* Random-row probes (the PS access pattern, unlike the streaming probe above): n_rows rows of row_floats
+ * floats at random offsets within span_rows rows of d_table (local or peer-mapped); mode as above;
+ * `unroll` rows in flight per warp, blocks_per_sm CTAs per SM.  The mixed probe interleaves peer loads,
+ * peer red.adds, local loads and local stores as selected by the bits of `flags` (1, 2, 4, 8; 128 = all
+ * four on one row index) - the mix the fused MF kernel issues.  Elapsed ms of `iters` launches in *ms.  */
+int fps_p2p_probe_random(float* d_table, int64_t span_rows, int row_floats, int64_t n_rows, int mode,
+                         int unroll, int blocks_per_sm, int iters, float* ms, void* stream);
+int fps_p2p_probe_mixed(float* d_remote, float* d_local, int64_t span_rows, int64_t n_rows, int flags,
+                        int iters, float* ms, void* stream);
 
 /* ---- table: init (N9), load (N10), dump (N11) ------------------------------------------------ */
 /* Fill local shard `shard` with init(id) for every slot (eager tables) - RangedRandomFactorInitializer

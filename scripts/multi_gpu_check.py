@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Multi-GPU correctness + P2P probe (launch with torchrun, one rank per GPU):
-  * every rank addresses every peer's shard through CUDA IPC (pull = P2P loads),
+  * every rank addresses every peer's shard through its VMM / IPC mapping (pull = P2P loads),
   * remote pushes land (red.add over NVLink),
   * the fused MF kernel trains with items sharded over all GPUs,
   * NVLink rooflines for the three access types (load / store / red.add) -> gpurun_out/p2p_probe.json

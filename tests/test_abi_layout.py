@@ -70,5 +70,5 @@ def test_every_declared_entry_point_is_exported_with_the_bound_arity():
     for name, n_args in protos.items():
         fn = getattr(L, name, None)
         assert fn is not None, f"{name} is declared in fps_b200.h but not exported"
-        if fn.argtypes is not None:
-            assert len(fn.argtypes) == n_args, (name, len(fn.argtypes), n_args)
+        assert fn.argtypes is not None, f"{name} is declared in fps_b200.h but has no ctypes signature in ops/_native.py"
+        assert len(fn.argtypes) == n_args, (name, len(fn.argtypes), n_args)
