@@ -157,6 +157,16 @@ __device__ __forceinline__ void red_add4(float* p, float4 v) {
                "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
 }
+// Push-and-refresh: the add returns the row as it was, so `old + v` is the row as everybody sees it
+// now, own delta included - one round trip instead of a push followed by a pull that might overtake it.
+__device__ __forceinline__ float4 atom_add4(float* p, float4 v) {
+  float4 o;
+  asm volatile("atom.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4], {%5,%6,%7,%8};"
+               : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
+               : "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+  return o;
+}
 __device__ __forceinline__ void red_add1(float* p, float v) {
   asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
 }

@@ -9,25 +9,33 @@
 // all threads of the block call these; contains __syncthreads
 __device__ __forceinline__ void flow_acquire(FpsFlow* flow, int n, int limit) {
   if (threadIdx.x == 0) {
-    unsigned long long stalls = 0;
-    // CAS, not add-then-undo: speculative adds from hundreds of waiting CTAs would keep the
-    // counter above the limit forever (livelock) when the limit is small.
-    int cur = *(volatile int*)&flow->in_flight;
-    while (true) {
-      if (cur + n <= limit) {
-        const int seen = atomicCAS(&flow->in_flight, cur, cur + n);
-        if (seen == cur) {
-          atomicMax(&flow->max_in_flight, cur + n);
-          break;
+    // Fast path: one optimistic add.  The hosts size their grids so that the allowances of all CTAs
+    // that can be resident fit the limit, so it all but always succeeds (no retry, one round trip).
+    const int old = atomicAdd(&flow->in_flight, n);
+    if (old + n <= limit) {
+      atomicMax(&flow->max_in_flight, old + n);
+    } else {
+      // Somebody else holds the credits (another launch on the same flow block): undo, then wait with
+      // CAS - not add-then-undo in a loop, which livelocks when many CTAs wait at a small limit.
+      atomicSub(&flow->in_flight, n);
+      unsigned long long stalls = 0;
+      int cur = *(volatile int*)&flow->in_flight;
+      while (true) {
+        if (cur + n <= limit) {
+          const int seen = atomicCAS(&flow->in_flight, cur, cur + n);
+          if (seen == cur) {
+            atomicMax(&flow->max_in_flight, cur + n);
+            break;
+          }
+          cur = seen;
+          continue;
         }
-        cur = seen;
-        continue;
+        ++stalls;
+        __nanosleep(100 + (blockIdx.x & 63) * 4);
+        cur = *(volatile int*)&flow->in_flight;
       }
-      ++stalls;
-      __nanosleep(100 + (blockIdx.x & 63) * 4);
-      cur = *(volatile int*)&flow->in_flight;
+      atomicAdd((unsigned long long*)&flow->limiter_stalls, stalls + 1);
     }
-    if (stalls) atomicAdd((unsigned long long*)&flow->limiter_stalls, stalls);
   }
   __syncthreads();
 }

@@ -12,14 +12,18 @@ template <int LANES, int VPL, bool LAZY, int UNROLL, int MINB = 1, bool REPL = f
 __global__ void __launch_bounds__(MF_THREADS, MINB)
 k_mf_sgd(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
          const int* __restrict__ uid, const int* __restrict__ iid, const float* __restrict__ rating,
-         long long n, const FpsMfParams p, int chunk, FpsFlow* flow) {
+         long long n, const FpsMfParams p, int chunk, int cta_credits, FpsFlow* flow) {
   constexpr int GPB = MF_THREADS / LANES;   // ratings in flight per block pass
   const int grp = threadIdx.x / LANES;
   MfCounters c;
   c.clear();
+  // Pull limiter: the CTA takes its allowance (the pulls one pass of it can have outstanding) from the
+  // worker's pool once and keeps it for its lifetime; the host sizes the grid so that all allowances
+  // fit the limit.  (The first version acquired per 256-record chunk: every CTA of a 148-SM grid spun
+  // on one word, 7x slower at limit 1600.)
+  if (p.pull_limit > 0) flow_acquire(flow, cta_credits, p.pull_limit);
   for (long long base = (long long)blockIdx.x * chunk; base < n; base += (long long)gridDim.x * chunk) {
     const int cnt = (int)min((long long)chunk, n - base);
-    if (p.pull_limit > 0) flow_acquire(flow, cnt, p.pull_limit);
     for (int k0 = 0; k0 < cnt; k0 += GPB * UNROLL) {   // warp-uniform trip count (shuffles inside)
       const int k = k0 + grp * UNROLL;
       MfRec<VPL> rec[UNROLL];
@@ -29,8 +33,8 @@ k_mf_sgd(const __grid_constant__ FpsTableView items, const __grid_constant__ Fps
 #pragma unroll
       for (int q = 0; q < UNROLL; ++q) mf_update<LANES, VPL, LAZY, REPL>(rec[q], items, p, c);
     }
-    if (p.pull_limit > 0) flow_release(flow, cnt);
   }
+  if (p.pull_limit > 0) flow_release(flow, cta_credits);
   c.flush(flow);
 }
 
@@ -64,13 +68,14 @@ __global__ void __launch_bounds__(MF_THREADS)
 k_mf_stream(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
             const int* ring_u, const int* ring_i, const float* ring_r, unsigned long long capacity,
             const volatile unsigned long long* tail, const volatile int* stop, const FpsMfParams p,
-            int chunk, unsigned long long wait_ns, unsigned long long life_ns, FpsFlow* flow) {
+            int chunk, int cta_credits, unsigned long long wait_ns, unsigned long long life_ns, FpsFlow* flow) {
   constexpr int GPB = MF_THREADS / LANES;
   const int grp = threadIdx.x / LANES;
   __shared__ unsigned long long s_base;
   __shared__ int s_cnt;
   MfCounters c;
   c.clear();
+  if (p.pull_limit > 0) flow_acquire(flow, cta_credits, p.pull_limit);   // per-CTA allowance, see k_mf_sgd
   const unsigned long long t_start = globaltimer_ns();
   while (true) {
     if (threadIdx.x == 0) {
@@ -114,7 +119,6 @@ k_mf_stream(const __grid_constant__ FpsTableView items, const __grid_constant__ 
       if (threadIdx.x == 0) atomicMax(&flow->exit_reason, -cnt);
       break;
     }
-    if (p.pull_limit > 0) flow_acquire(flow, cnt, p.pull_limit);
     for (int k0 = 0; k0 < cnt; k0 += GPB) {
       const int k = k0 + grp;
       MfRec<VPL> rec;
@@ -133,7 +137,6 @@ k_mf_stream(const __grid_constant__ FpsTableView items, const __grid_constant__ 
       mf_load_ids<LANES, VPL, LAZY>(rec, items, users, ids, p.local_shard, c);
       mf_update<LANES, VPL, LAZY>(rec, items, p, c);
     }
-    if (p.pull_limit > 0) flow_release(flow, cnt);
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence();
@@ -141,6 +144,7 @@ k_mf_stream(const __grid_constant__ FpsTableView items, const __grid_constant__ 
       *(volatile unsigned long long*)&flow->last_activity_ns = globaltimer_ns();
     }
   }
+  if (p.pull_limit > 0) flow_release(flow, cta_credits);
   c.flush(flow);
 }
 
@@ -214,15 +218,21 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
   const int bps = params->blocks_per_sm > 0 ? params->blocks_per_sm : 64;
   const long long cap = (long long)fps_num_sms() * bps;
   if (blocks > cap) blocks = cap;
-  if (params->pull_limit > 0) {
-    // With a limiter only ~pull_limit / chunk CTAs can hold credits at a time; launching thousands
-    // more just makes them fight over the counter (measured: 102 ms instead of ~10 ms per 4M
-    // ratings at limit 1600).  Twice that many keeps the limiter engaged without the stampede.
-    const long long useful = 2 * ((long long)params->pull_limit / chunk > 0 ? (long long)params->pull_limit / chunk : 1);
-    if (blocks > useful) blocks = useful;
-  }
   const int unroll = params->unroll;   // 0 = default
-#define MF_ARGS <<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, d_flow)
+  int cta_credits = 0;
+  if (params->pull_limit > 0) {
+    // one pass of a CTA has (sub-warps x ratings per sub-warp) pulls outstanding, or the whole chunk if
+    // that is smaller; the grid holds as many CTAs as allowances fit the limit
+    const Shape sh = shape_for(items->stride);
+    const int per_pass = (MF_THREADS / sh.lanes) * (unroll == 2 || unroll == 4 ? unroll : (sh.vpl == 2 ? 2 : 1));
+    cta_credits = per_pass < chunk ? per_pass : chunk;
+    // at most SMs x 8 CTAs (the tightest launch bound) are resident and hold credits at a time; only if
+    // even those do not fit is the grid cut down to a persistent one
+    const long long resident = (long long)fps_num_sms() * 8;
+    const long long fit = params->pull_limit / cta_credits > 0 ? params->pull_limit / cta_credits : 1;
+    if (fit < resident && blocks > fit) blocks = fit;
+  }
+#define MF_ARGS <<<(int)blocks, MF_THREADS, 0, st>>>(*items, *users, d_user_ids, d_item_ids, d_ratings, n, *params, chunk, cta_credits, d_flow)
   // Default for eager tables up to rank 128: one rating per sub-warp, 32 registers, 8 CTAs/SM (64
   // resident warps).  Measured on B200 (4.19M ratings, rank 128): 1.37 ms vs 1.55 ms for the
   // 2-ratings-per-sub-warp build at 56 registers - thread-level parallelism hides the row-load
@@ -274,12 +284,20 @@ int fps_mf_online_stream(const FpsTableView* items, const FpsTableView* users, c
   int chunk = 64;
   if (params->pull_limit > 0 && params->pull_limit < chunk) chunk = params->pull_limit;
   // one resident wave only: every CTA of a polling kernel must be co-resident
-  const int blocks = fps_num_sms() * 2;
+  int blocks = fps_num_sms() * 2;
+  int cta_credits = 0;
+  if (params->pull_limit > 0) {
+    const Shape sh = shape_for(items->stride);
+    const int per_pass = MF_THREADS / sh.lanes;
+    cta_credits = per_pass < chunk ? per_pass : chunk;
+    const int fit = params->pull_limit / cta_credits > 0 ? params->pull_limit / cta_credits : 1;
+    if (blocks > fit) blocks = fit;
+  }
   const unsigned long long wait_ns = (unsigned long long)iteration_wait_ms * 1000000ull;
   const unsigned long long life_ns = (unsigned long long)max_lifetime_ms * 1000000ull;
 #define FN(L, V, Z)                                                                                   \
-  if (Z) k_mf_stream<L, V, true><<<blocks, MF_THREADS, 0, st>>>(*items, *users, ring_users, ring_items, ring_ratings, ring_capacity, (const volatile unsigned long long*)tail, stop, *params, chunk, wait_ns, life_ns, d_flow); \
-  else k_mf_stream<L, V, false><<<blocks, MF_THREADS, 0, st>>>(*items, *users, ring_users, ring_items, ring_ratings, ring_capacity, (const volatile unsigned long long*)tail, stop, *params, chunk, wait_ns, life_ns, d_flow)
+  if (Z) k_mf_stream<L, V, true><<<blocks, MF_THREADS, 0, st>>>(*items, *users, ring_users, ring_items, ring_ratings, ring_capacity, (const volatile unsigned long long*)tail, stop, *params, chunk, cta_credits, wait_ns, life_ns, d_flow); \
+  else k_mf_stream<L, V, false><<<blocks, MF_THREADS, 0, st>>>(*items, *users, ring_users, ring_items, ring_ratings, ring_capacity, (const volatile unsigned long long*)tail, stop, *params, chunk, cta_credits, wait_ns, life_ns, d_flow)
   MF_DISPATCH(FN);
 #undef FN
   FPS_LAUNCH_CHECK();

@@ -8,6 +8,11 @@
 //                     end up in the same ~1K-record neighbourhood of a packed 16-byte record array.
 //                     It only depends on the step's inputs, so the caller may run it on another
 //                     stream while the previous step's kernel is still busy (DeviceMF does).
+//                     Buckets are small (~256 records); a tile is ~3/4 of the tile size worth of
+//                     consecutive records whose ends are moved back to a bucket boundary when one is
+//                     near (k_tile_bounds), so that an item's records are not cut in two by a tile
+//                     edge (a cut costs a second pull and push of the same row: +8.6 % rows measured
+//                     with bucket-sized tiles cut at fixed offsets).
 //   fps_mf_sgd_tiles  one CTA per tile of TILE consecutive packed records: load the tile into shared
 //                     memory, bitonic-sort it by item there, then every (sub-)warp walks a contiguous
 //                     segment of the sorted tile carrying (item, pulled row, accumulated delta) in
@@ -36,11 +41,18 @@ namespace {
 
 constexpr int TL_THREADS = 256;
 constexpr int TL_MAX_TILE = 2048;
-constexpr int TL_MAX_BUCKETS = 8192;
+constexpr int TL_MAX_BUCKETS = 16384;
+constexpr int TL_BUCKET_TARGET = 256;   // average records per bucket
 constexpr int TL_RUN_FLUSH = 32;   // records of one run after which the combined delta is pushed
 constexpr int TL_RU = 4;           // user rows in flight per warp (staged path)
 constexpr int TL_RI = 2;           // item rows in flight per warp (staged path)
-constexpr size_t TL_HDR_BYTES = 2 * TL_MAX_BUCKETS * sizeof(int);   // counts + cursors
+constexpr size_t TL_HDR_BYTES = 2 * TL_MAX_BUCKETS * sizeof(int);   // counts + cursors (= bucket ends after the scatter)
+constexpr int TL_MIN_NOMINAL = 384;      // nominal records per tile at the smallest tile size (512 * 3 / 4)
+
+// scratch layout: [counts | cursors][tile_start: n / TL_MIN_NOMINAL + 2 ints, padded][records]
+__host__ __device__ inline size_t tl_bounds_bytes(long long n) {
+  return (((size_t)(n / TL_MIN_NOMINAL + 2) * sizeof(int)) + 255) & ~(size_t)255;
+}
 
 struct __align__(16) TileRec {
   int user, item;
@@ -77,7 +89,7 @@ __device__ __forceinline__ void tl_bulk_g2s(void* smem_dst, const void* gmem_src
 // ---------------------------------------------------------------------------------------------
 // phase 1: counting sort by (item & mask) into packed records
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 k_bucket_count(const int* __restrict__ iid, long long n, int nb, int* __restrict__ counts) {
   extern __shared__ int s_hist[];
   for (int b = threadIdx.x; b < nb; b += blockDim.x) s_hist[b] = 0;
@@ -96,7 +108,7 @@ k_bucket_scan(int* __restrict__ counts, int* __restrict__ cursors, int nb) {
   __shared__ int s_warp[32];
   const int per = (nb + 1023) / 1024;
   const int b0 = threadIdx.x * per;
-  int local[TL_MAX_BUCKETS / 1024];
+  int local[TL_MAX_BUCKETS / 1024];      // 16
   int sum = 0;
 #pragma unroll
   for (int q = 0; q < TL_MAX_BUCKETS / 1024; ++q) {
@@ -134,7 +146,7 @@ k_bucket_scan(int* __restrict__ counts, int* __restrict__ cursors, int nb) {
 
 // every CTA owns one contiguous range of the input: count its records per bucket in shared memory,
 // claim one output range per non-empty bucket with a single global atomic, then place the records
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 k_bucket_scatter(const int* __restrict__ uid, const int* __restrict__ iid, const float* __restrict__ rating,
                  long long n, int nb, int* __restrict__ cursors, TileRec* __restrict__ out) {
   extern __shared__ int s_mem[];
@@ -162,6 +174,29 @@ k_bucket_scatter(const int* __restrict__ uid, const int* __restrict__ iid, const
     const int pos = s_base[b] + atomicAdd(&s_cnt[b], 1);
     out[pos] = r;
   }
+}
+
+// Tile t nominally starts at record t * nominal; if a bucket boundary lies at most `snap` records
+// before that point the tile starts there instead (no small bucket is ever cut; a bucket larger than
+// `snap` - a hot item - is cut at the nominal points).  Tiles are at most nominal + snap records.
+// `ends` = the cursors after the scatter = the end offset of every bucket.
+__global__ void __launch_bounds__(256)
+k_tile_bounds(const int* __restrict__ ends, int nb, long long n, int nominal, int snap, int n_tiles,
+              int* __restrict__ tile_start) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t > n_tiles) return;
+  const long long p = min(n, (long long)t * nominal);
+  int s = (int)p;
+  if (p > 0 && p < n) {
+    int lo = 0, hi = nb;                    // number of buckets whose end is <= p
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (ends[mid] <= p) lo = mid + 1; else hi = mid;
+    }
+    const int b = lo > 0 ? ends[lo - 1] : 0;
+    if (p - b <= snap) s = b;
+  }
+  tile_start[t] = s;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -216,11 +251,11 @@ struct TileCounters {
 // Load tile `tile` into shared memory, drop records with ids outside the tables (counted as bad),
 // sort the rest by item.  Returns the number of valid records; s_key[k] = item << 32 | slot in s_rec.
 __device__ __forceinline__ int tile_load_sort(const FpsTableView& items, const FpsTableView& users,
-                                              const TileRec* __restrict__ recs, long long n, long long tile,
-                                              int tile_sz, TileRec* s_rec, unsigned long long* s_key,
+                                              const TileRec* __restrict__ recs, const int* __restrict__ tile_start,
+                                              long long tile, TileRec* s_rec, unsigned long long* s_key,
                                               TileCounters& c) {
-  const long long base = tile * tile_sz;
-  const int cnt = (int)min((long long)tile_sz, n - base);
+  const long long base = tile_start[tile];
+  const int cnt = tile_start[tile + 1] - (int)base;
   int sort_n = 32;
   while (sort_n < cnt) sort_n <<= 1;
   for (int k = threadIdx.x; k < sort_n; k += TL_THREADS) {
@@ -262,6 +297,33 @@ __device__ __forceinline__ int tile_load_sort(const FpsTableView& items, const F
   return lo;
 }
 
+// Where the walkers' segments of a sorted tile may begin.  Cut points are the run boundaries plus,
+// inside a run longer than TL_SERIAL, every TL_SERIAL-th record of it: a run is walked serially by ONE
+// walker (exact serial SGD on the carried row, one pull) unless it is so long that this would leave
+// the rest of the CTA idle.  Returns the first cut point >= p.  Without this a hot item's run was
+// split over every (sub-)warp of the CTA, all starting from the same stale row - the sum of their
+// deltas overshoots by the number of walkers (diverged at rank 16, 64 sub-warps per CTA).
+constexpr int TL_SERIAL = 128;
+__device__ __forceinline__ int tile_cut(const unsigned long long* s_key, int valid, int p) {
+  if (p <= 0) return 0;
+  if (p >= valid) return valid;
+  const unsigned int item = (unsigned int)(s_key[p] >> 32);
+  if ((unsigned int)(s_key[p - 1] >> 32) != item) return p;
+  int lo = 0, hi = p;                       // first record of the run that contains p
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if ((unsigned int)(s_key[mid] >> 32) < item) lo = mid + 1; else hi = mid;
+  }
+  const int start = lo;
+  lo = p; hi = valid;                       // first record after the run
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if ((unsigned int)(s_key[mid] >> 32) <= item) lo = mid + 1; else hi = mid;
+  }
+  const int next_cut = start + ((p - start + TL_SERIAL - 1) / TL_SERIAL) * TL_SERIAL;
+  return min(lo, next_cut);
+}
+
 template <int LANES, int VPL>
 struct TCarry {
   int item;
@@ -285,6 +347,30 @@ __device__ __forceinline__ void tcarry_push(TCarry<LANES, VPL>& cy, int nvec, Ti
   if (lane == 0) {
     ++c.pushes;
     if (cy.remote) ++c.rpushes;
+  }
+}
+
+// Long run: publish the delta gathered so far AND refresh the carried row in one round trip (the
+// add returns the previous value), so walkers on the same hot item feed back into each other every
+// TL_RUN_FLUSH records - without it the sum of many walkers' deltas, all computed from the same
+// stale row, overshoots (diverged on a 6 %-hot item at rank 16).
+template <int LANES, int VPL>
+__device__ __forceinline__ void tcarry_exchange(TCarry<LANES, VPL>& cy, int nvec, TileCounters& c) {
+  const int lane = threadIdx.x % LANES;
+#pragma unroll
+  for (int q = 0; q < VPL; ++q) {
+    const int b = lane + q * LANES;
+    if (b < nvec) {
+      const float4 o = atom_add4(cy.row + b * 4, cy.acc[q]);
+      cy.v[q].x = o.x + cy.acc[q].x; cy.v[q].y = o.y + cy.acc[q].y;
+      cy.v[q].z = o.z + cy.acc[q].z; cy.v[q].w = o.w + cy.acc[q].w;
+    }
+    cy.acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  cy.run_len = 0;
+  if (lane == 0) {
+    ++c.pushes; ++c.pulls;
+    if (cy.remote) { ++c.rpushes; ++c.rpulls; }
   }
 }
 
@@ -325,14 +411,14 @@ __device__ __forceinline__ void tile_sgd(TCarry<LANES, VPL>& cy, const float4 (&
     }
   }
   if (lane == 0) c.loss += e * e;
-  if (++cy.run_len >= TL_RUN_FLUSH) tcarry_push<LANES, VPL>(cy, nvec, c);
+  if (++cy.run_len >= TL_RUN_FLUSH) tcarry_exchange<LANES, VPL>(cy, nvec, c);
 }
 
 // ---- register path: any rank, LANES lanes per record -----------------------------------------
 template <int LANES, int VPL>
 __global__ void __launch_bounds__(TL_THREADS, (VPL == 1 ? 3 : 1))
 k_mf_tiles_reg(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
-               const TileRec* __restrict__ recs, long long n, const FpsMfParams p, int tile_sz,
+               const TileRec* __restrict__ recs, const int* __restrict__ tile_start, const FpsMfParams p, int tile_sz,
                long long n_tiles, long long tile_mul, int active_groups, int cta_credits, FpsFlow* flow) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   TileRec* s_rec = reinterpret_cast<TileRec*>(s_raw);
@@ -346,9 +432,17 @@ k_mf_tiles_reg(const __grid_constant__ FpsTableView items, const __grid_constant
   if (p.pull_limit > 0) flow_acquire(flow, cta_credits, p.pull_limit);
   for (long long lin = blockIdx.x; lin < n_tiles; lin += gridDim.x) {
     const long long tile = (lin * tile_mul) % n_tiles;
-    const int valid = tile_load_sort(items, users, recs, n, tile, tile_sz, s_rec, s_key, c);
-    const int seg = (valid + groups - 1) / groups;
-    const int b0 = min(valid, grp * seg), b1 = grp < groups ? min(valid, b0 + seg) : b0;
+    const int valid = tile_load_sort(items, users, recs, tile_start, tile, s_rec, s_key, c);
+    const int nominal = (valid + groups - 1) / groups;
+    const int b0 = grp < groups ? tile_cut(s_key, valid, grp * nominal) : valid;
+    const int b1 = grp < groups ? tile_cut(s_key, valid, (grp + 1) * nominal) : valid;
+    // block-uniform trip count (shuffles inside the loop): the longest segment of the CTA
+    __shared__ int s_seg;
+    if (threadIdx.x == 0) s_seg = 0;
+    __syncthreads();
+    if (lane == 0 && b1 > b0) atomicMax(&s_seg, b1 - b0);
+    __syncthreads();
+    const int seg = s_seg;
     TCarry<LANES, VPL> cy;
     cy.item = -1;
     cy.run_len = 0;
@@ -437,7 +531,7 @@ struct WarpRing {
 
 __global__ void __launch_bounds__(TL_THREADS, 4)
 k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
-               const TileRec* __restrict__ recs, long long n, const FpsMfParams p, int tile_sz,
+               const TileRec* __restrict__ recs, const int* __restrict__ tile_start, const FpsMfParams p, int tile_sz,
                long long n_tiles, long long tile_mul, int item_depth, int active_warps, int cta_credits,
                FpsFlow* flow) {
   extern __shared__ __align__(16) unsigned char s_raw[];
@@ -464,9 +558,10 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
   const int walkers = active_warps > 0 && active_warps < NW ? active_warps : NW;   // limiter: fewer walkers
   for (long long lin = blockIdx.x; lin < n_tiles; lin += gridDim.x) {
     const long long tile = (lin * tile_mul) % n_tiles;
-    const int valid = tile_load_sort(items, users, recs, n, tile, tile_sz, s_rec, s_key, c);
-    const int seg = (valid + walkers - 1) / walkers;
-    const int b0 = min(valid, w * seg), b1 = w < walkers ? min(valid, b0 + seg) : b0;
+    const int valid = tile_load_sort(items, users, recs, tile_start, tile, s_rec, s_key, c);
+    const int nominal = (valid + walkers - 1) / walkers;
+    const int b0 = w < walkers ? tile_cut(s_key, valid, w * nominal) : valid;
+    const int b1 = w < walkers ? tile_cut(s_key, valid, (w + 1) * nominal) : valid;
     const int len = b1 - b0;
     // ---- producer side ----------------------------------------------------------------------
     auto issue_user = [&](int j) {         // record j of the segment -> user slot j % RU
@@ -567,7 +662,7 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
 
 int n_buckets_for(long long n) {
   int nb = 1;
-  while (nb < TL_MAX_BUCKETS && (long long)nb * 1024 < n) nb <<= 1;
+  while (nb < TL_MAX_BUCKETS && (long long)nb * TL_BUCKET_TARGET < n) nb <<= 1;
   return nb;
 }
 
@@ -576,7 +671,7 @@ int n_buckets_for(long long n) {
 extern "C" {
 
 size_t fps_mf_tiles_scratch_bytes(int64_t n) {
-  return TL_HDR_BYTES + (size_t)(n > 0 ? n : 0) * sizeof(TileRec) + 256;
+  return TL_HDR_BYTES + tl_bounds_bytes(n > 0 ? n : 0) + (size_t)(n > 0 ? n : 0) * sizeof(TileRec) + 256;
 }
 
 int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const float* d_ratings, int64_t n,
@@ -589,7 +684,7 @@ int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const fl
   cudaStream_t st = (cudaStream_t)stream;
   int* counts = (int*)d_scratch;
   int* cursors = counts + TL_MAX_BUCKETS;
-  TileRec* out = (TileRec*)((unsigned char*)d_scratch + TL_HDR_BYTES);
+  TileRec* out = (TileRec*)((unsigned char*)d_scratch + TL_HDR_BYTES + tl_bounds_bytes(n));
   const int nb = n_buckets_for(n);
   static bool attr_done[64] = {false};
   int dev = 0;
@@ -597,20 +692,25 @@ int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const fl
   if (dev >= 0 && dev < 64 && !attr_done[dev]) {
     FPS_CUDA(cudaFuncSetAttribute(k_bucket_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   2 * TL_MAX_BUCKETS * (int)sizeof(int)));
+    FPS_CUDA(cudaFuncSetAttribute(k_bucket_count, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  TL_MAX_BUCKETS * (int)sizeof(int)));
     attr_done[dev] = true;
   }
   FPS_CUDA(cudaMemsetAsync(counts, 0, (size_t)nb * sizeof(int), st));
-  long long blocks = (n + 4095) / 4096;
-  const long long cap = (long long)fps_num_sms() * 4;
+  // one CTA per SM at most: every CTA walks all nb bins of its shared-memory histogram three times,
+  // which only pays when it also owns a long range of records
+  long long blocks = (n + 16383) / 16384;
+  const long long cap = (long long)fps_num_sms();
   if (blocks > cap) blocks = cap;
-  k_bucket_count<<<(int)blocks, 256, nb * sizeof(int), st>>>(d_item_ids, n, nb, counts);
+  const int threads = n >= 65536 ? 1024 : 256;
+  k_bucket_count<<<(int)blocks, threads, nb * sizeof(int), st>>>(d_item_ids, n, nb, counts);
   k_bucket_scan<<<1, 1024, 0, st>>>(counts, cursors, nb);
-  k_bucket_scatter<<<(int)blocks, 256, 2 * nb * sizeof(int), st>>>(d_user_ids, d_item_ids, d_ratings, n, nb, cursors, out);
+  k_bucket_scatter<<<(int)blocks, threads, 2 * nb * sizeof(int), st>>>(d_user_ids, d_item_ids, d_ratings, n, nb, cursors, out);
   FPS_LAUNCH_CHECK();
   return 0;
 }
 
-int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, const void* d_scratch, int64_t n,
+int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, void* d_scratch, int64_t n,
                      const FpsMfParams* params, FpsFlow* d_flow, void* stream) {
   if (int e = fps_check_view(items, "fps_mf_sgd_tiles")) return e;
   if (int e = fps_check_view(users, "fps_mf_sgd_tiles")) return e;
@@ -622,7 +722,9 @@ int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, const
               FPS_E_UNSUPPORTED, "fps_mf_sgd_tiles: eager, sharded (not replicated) tables of rank <= 512 only");
   if (n <= 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
-  const TileRec* recs = (const TileRec*)((const unsigned char*)d_scratch + TL_HDR_BYTES);
+  const int* ends = (const int*)d_scratch + TL_MAX_BUCKETS;
+  int* tile_start = (int*)((unsigned char*)d_scratch + TL_HDR_BYTES);
+  const TileRec* recs = (const TileRec*)((const unsigned char*)d_scratch + TL_HDR_BYTES + tl_bounds_bytes(n));
   const int nvec = items->stride / 4;
   int lanes = 1;
   while (lanes < nvec && lanes < 32) lanes <<= 1;
@@ -630,12 +732,11 @@ int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, const
   const int gpb = TL_THREADS / lanes;
   // params->reserved selects the tile size (512 / 1024 / 2048; 0 = 1024); params->unroll = 1 forces
   // the register path for shapes the staged path would take
-  int tile_sz = params->reserved == 512 ? 512 : params->reserved == 2048 ? 2048 : 1024;
-  if (n < tile_sz) {
-    tile_sz = 32;
-    while (tile_sz < n) tile_sz <<= 1;
-  }
-  const long long n_tiles = (n + tile_sz - 1) / tile_sz;
+  const int tile_sz = params->reserved == 512 ? 512 : params->reserved == 2048 ? 2048 : 1024;
+  const int nominal = tile_sz / 4 * 3, snap = tile_sz / 4;
+  const long long n_tiles = (n + nominal - 1) / nominal;
+  k_tile_bounds<<<(int)((n_tiles + 1 + 255) / 256), 256, 0, st>>>(ends, n_buckets_for(n), n, nominal, snap, (int)n_tiles,
+                                                               tile_start);
   long long tile_mul = (long long)((double)n_tiles * 0.6180339887) | 1;
   auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };
   while (tile_mul > 1 && gcd(tile_mul, n_tiles) != 1) tile_mul -= 2;
@@ -648,22 +749,21 @@ int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, const
   // more bytes from 148 SMs than from a few.  A walker's outstanding pulls = the carried row (in
   // compute, its push not yet issued) + the item rows its ring prefetches.
   const int walkers_full = staged ? TL_THREADS / 32 : gpb;   // (sub-)warps per CTA that pull
+  const int depth_max = staged ? TL_RI + 1 : 1;
   int active_groups = 0, item_depth = TL_RI, cta_credits = 0;
   if (params->pull_limit > 0) {
     const long long limit = params->pull_limit;
-    const long long resident = (long long)sms * (staged ? 4 : 3);
+    const long long resident = (long long)sms * (2048 / TL_THREADS);   // most CTAs the hardware can keep resident
     int walkers = walkers_full, depth = 1;
     if (limit < walkers_full) {                       // fewer credits than walkers in one CTA
       active_groups = walkers = (int)limit;
       blocks = 1;
     } else {
-      long long ctas = limit / walkers;               // one outstanding row per walker
-      if (ctas > resident) ctas = resident;
-      if (staged) {
-        depth = (int)(limit / (ctas * walkers));
-        if (depth > TL_RI + 1) depth = TL_RI + 1;
-      }
-      if (blocks > ctas) blocks = ctas;
+      for (depth = depth_max; depth > 1 && resident * walkers * depth > limit; --depth) {}
+      if (resident * walkers * depth > limit) {       // not even one row per walker fits: fewer, persistent CTAs
+        const long long ctas = limit / walkers;
+        if (blocks > ctas) blocks = ctas;
+      }                                               // else: the full grid - only `resident` CTAs hold credits at a time
     }
     item_depth = depth - 1;
     cta_credits = walkers * depth;
@@ -689,10 +789,10 @@ int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, const
 #undef SET_ATTR
   if (staged) {
     const size_t smem = smem_base + (TL_THREADS / 32) * sizeof(WarpRing);
-    k_mf_tiles_tma<<<(int)blocks, TL_THREADS, smem, st>>>(*items, *users, recs, n, *params, tile_sz, n_tiles, tile_mul,
+    k_mf_tiles_tma<<<(int)blocks, TL_THREADS, smem, st>>>(*items, *users, recs, tile_start, *params, tile_sz, n_tiles, tile_mul,
                                                           item_depth, active_groups, cta_credits, d_flow);
   } else {
-#define LAUNCH(L, V) k_mf_tiles_reg<L, V><<<(int)blocks, TL_THREADS, smem_base, st>>>(*items, *users, recs, n, *params, tile_sz, n_tiles, tile_mul, active_groups, cta_credits, d_flow)
+#define LAUNCH(L, V) k_mf_tiles_reg<L, V><<<(int)blocks, TL_THREADS, smem_base, st>>>(*items, *users, recs, tile_start, *params, tile_sz, n_tiles, tile_mul, active_groups, cta_credits, d_flow)
     if (vpl == 1) {
       switch (lanes) {
         case 1: LAUNCH(1, 1); break;

@@ -192,7 +192,7 @@ int fps_mf_online_stream(const FpsTableView* items, const FpsTableView* users,
 size_t fps_mf_tiles_scratch_bytes(int64_t n);
 int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const float* d_ratings, int64_t n,
                   void* d_scratch, size_t scratch_bytes, void* stream);
-int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, const void* d_scratch, int64_t n,
+int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, void* d_scratch, int64_t n,
                      const FpsMfParams* params, FpsFlow* d_flow, void* stream);
 
 /* Replicated table with deferred pushes: add the locally accumulated deltas to every other replica

@@ -77,6 +77,26 @@ def main():
     ok &= ok4
     print(f"[rank {rank}] all ranks read identical item rows: {ok4}", flush=True)
 
+    # 3c. rank 128 = the TMA-staged tile path reading PEER rows with cp.async.bulk: one conflict-free step
+    #     whose items all live on the next rank, replayed in fp64 from rows gathered before it
+    mt = DeviceMF(40_000, 40_000, 128, 0.0, 0.2, 0.05, seed=3, ctx=ctx, replicate_items=False, variant="tiles")
+    k = torch.arange(3000, device="cuda", dtype=torch.int64)
+    pu, pi = k * world + rank, k * world + (rank + 1) % world
+    pr = torch.full((3000,), 0.5, device="cuda")
+    ctx.barrier()
+    U0, V0 = mt.users.gather(pu).double(), mt.items.gather(pi).double()
+    torch.cuda.synchronize(); ctx.barrier()
+    mt.step(pu.int(), pi.int(), pr)
+    torch.cuda.synchronize(); ctx.barrier()
+    U1, V1 = mt.users.gather(pu).double(), mt.items.gather(pi).double()
+    e = (0.5 - (U0 * V0).sum(1))[:, None]
+    err = max(float((U0 + 0.05 * e * V0 - U1).abs().max()), float((V0 + 0.05 * e * U0 - V1).abs().max()))
+    st = mt.stats()
+    ok3c = err < 1e-6 and st["records"] == 3000 and (world == 1 or st["remote_pulls"] == 3000) and mt.variant == "tiles"
+    ok &= ok3c
+    print(f"[rank {rank}] tile path (TMA rings over peer rows), fp64 replay max err {err:.2e}, remote pulls "
+          f"{st['remote_pulls']}: {ok3c}", flush=True)
+
     # 3a. the same job with the (12.8 MB) item table replicated on every GPU: local pulls, deferred delta exchange
     if world > 1:
         mfr = DeviceMF(n_users, n_items, dim, 0.0, 0.2, 0.05, pull_limit=1600, seed=1, ctx=ctx, replicate_items=True)
