@@ -133,6 +133,7 @@ k_mf_stream(const __grid_constant__ FpsTableView items, const __grid_constant__ 
         asm volatile("ld.global.cg.s32 %0, [%1];" : "=r"(ids.u) : "l"(ring_u + slot));
         asm volatile("ld.global.cg.s32 %0, [%1];" : "=r"(ids.i) : "l"(ring_i + slot));
         asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(ids.r) : "l"(ring_r + slot));
+        ids.active = ids.u != FPS_SKIP_ID;
       }
       mf_load_ids<LANES, VPL, LAZY>(rec, items, users, ids, p.local_shard, c);
       mf_update<LANES, VPL, LAZY>(rec, items, p, c);

@@ -84,6 +84,7 @@ __device__ __forceinline__ MfIds mf_fetch_ids(const int* __restrict__ uid, const
     d.u = uid[idx];
     d.i = iid[idx];
     d.r = rating ? rating[idx] : 0.f;
+    d.active = d.u != FPS_SKIP_ID;       // an unused negative-sample slot
   }
   return d;
 }

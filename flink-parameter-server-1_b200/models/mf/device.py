@@ -87,7 +87,8 @@ class DeviceMF:
         # combine sub-warp holds its credits while it walks its slice serially: 109 ms vs ~10 ms per 4M
         # ratings at limit 1600).
         self._auto = variant == "auto"
-        self._tiles_ok = not lazy and not self.items.replicated and self.items.stride <= 512
+        self._tiles_ok = (not lazy and not self.items.replicated and self.items.stride <= 512
+                          and max(self.items.rows_per_shard, self.users.rows_per_shard) < (1 << 28))
         self._combine_ok = not lazy and pull_limit <= 0 and not self.items.replicated
         if variant == "tiles" and not self._tiles_ok:
             raise ValueError("variant='tiles' needs eager, sharded (not replicated) tables of rank <= 512")
@@ -322,6 +323,57 @@ class DeviceMF:
         self.ctx.barrier()
 
 
+class NegativeSampler:
+    """Device-resident negative sampler of one worker (``csrc/sampler.cu``): per-user ring of the
+    last ``user_memory`` items, pool of the items seen so far, Philox rejection draws.
+
+    Parity: the ingest half of ``PSOnlineMatrixFactorizationWorker.onRecv`` (``:59-89``) and of
+    ``PSOfflineMatrixFactorizationWorker.onRecv`` (``:64-95``).  ``expand`` turns a batch of positives
+    into ``n * (rate + 1)`` records - per positive its negatives (rating 0) then the positive itself -
+    with unused slots marked ``SKIP_ID`` (the SGD kernels pass over them)."""
+
+    def __init__(self, mf: "DeviceMF", negative_sample_rate: int, user_memory: int = 128, seed: int = 0):
+        import torch
+        if negative_sample_rate < 0 or user_memory <= 0:
+            raise ValueError("negative_sample_rate >= 0 and user_memory > 0")
+        self.mf, self.rate, self.user_memory = mf, int(negative_sample_rate), int(user_memory)
+        users = mf.users
+        distributed = mf.ctx.distributed
+        n_rings = users.rows_per_shard if distributed else users.n_shards * users.rows_per_shard
+        z = lambda n, dt: torch.zeros(max(int(n), 1), device="cuda", dtype=dt)   # noqa: E731
+        self._seen = z(n_rings * self.user_memory, torch.int32)
+        self._seen_count = z(n_rings, torch.int32)
+        self._bitmap = z((mf.n_items + 31) // 32, torch.int32)
+        self._pool = z(mf.n_items, torch.int32)
+        self._pool_count = z(1, torch.int32)
+        st = N.FpsNegSampler()
+        st.seen, st.seen_count = self._seen.data_ptr(), self._seen_count.data_ptr()
+        st.item_bitmap, st.item_pool = self._bitmap.data_ptr(), self._pool.data_ptr()
+        st.pool_count = self._pool_count.data_ptr()
+        st.n_items, st.seed = mf.n_items, (seed * 0x9E3779B97F4A7C15 + 0x1234567) & (2 ** 64 - 1)
+        st.user_memory, st.rate = self.user_memory, self.rate
+        st.local_shard = mf.ctx.rank if distributed else -1
+        self._state = st
+        self._tag = 0
+
+    def expand(self, users, items, ratings):
+        """``(users, items, ratings)`` int32 / int32 / fp32 on the device -> the expanded batch."""
+        import torch
+        n = users.numel()
+        m = n * (self.rate + 1)
+        ou = torch.empty(m, device="cuda", dtype=torch.int32)
+        oi = torch.empty(m, device="cuda", dtype=torch.int32)
+        orr = torch.empty(m, device="cuda", dtype=torch.float32)
+        self._tag += 1
+        N.check(N.lib().fps_mf_sample_negatives(self.mf.users.view_ref(), C.byref(self._state), N.ptr(users),
+                                                N.ptr(items), N.ptr(ratings), n, self._tag, N.ptr(ou), N.ptr(oi),
+                                                N.ptr(orr), N.current_stream()), "fps_mf_sample_negatives")
+        return ou, oi, orr
+
+    def items_seen(self) -> int:
+        return int(self._pool_count.item())
+
+
 def _ratings_to_tensors(ratings, rank: int, world: int):
     import torch
     u = np.fromiter((r.user for r in ratings), dtype=np.int32)
@@ -334,7 +386,8 @@ def _ratings_to_tensors(ratings, rank: int, world: int):
 
 
 def ps_offline_mf_device(src, num_factors: int = 10, range_min: float = -0.01, range_max: float = 0.01,
-                         learning_rate: float = 0.01, iterations: int = 1, pull_limit: int = 1600,
+                         learning_rate: float = 0.01, negative_sample_rate: int = 0, user_memory: int = 128,
+                         iterations: int = 1, pull_limit: int = 1600,
                          *, n_users: Optional[int] = None, n_items: Optional[int] = None, seed: int = 0,
                          shuffle: bool = True, lambda_: float = 0.0, lazy: bool = True,
                          conflict_free: bool = False, n_shards: Optional[int] = None,
@@ -354,6 +407,15 @@ def ps_offline_mf_device(src, num_factors: int = 10, range_min: float = -0.01, r
     mf = DeviceMF(n_users, n_items, num_factors, range_min, range_max, learning_rate, lambda_=lambda_,
                   pull_limit=pull_limit, seed=seed, lazy=lazy, variant=variant, ctx=ctx, n_shards=n_shards)
     u, i, v = _ratings_to_tensors(ratings, ctx.rank, ctx.world_size)
+    if negative_sample_rate > 0 and u.numel():
+        # ingest phase of the reference worker (":64-95"): every rating becomes a block of its negatives +
+        # itself, drawn once, in arrival order (micro-batches keep "items seen so far" meaningful); the
+        # epochs then replay the blocks
+        sampler = NegativeSampler(mf, negative_sample_rate, user_memory, seed)
+        parts = [sampler.expand(u[s:s + 4096], i[s:s + 4096], v[s:s + 4096]) for s in range(0, u.numel(), 4096)]
+        u, i, v = (torch.cat([p[k] for p in parts]) for k in range(3))
+        keep = u != N.SKIP_ID
+        u, i, v = u[keep].contiguous(), i[keep].contiguous(), v[keep].contiguous()
     gen = torch.Generator(device="cpu").manual_seed(seed)
     for _ in range(iterations):
         if shuffle and u.numel():
@@ -388,6 +450,25 @@ def conflict_free_waves(u, i, v):
         yield u[idx], i[idx], v[idx]
 
 
+class _HostSeenRing:
+    """Host twin of the device sampler's per-user ring, for the streaming producer (which is the host):
+    ``[n_users, user_memory]`` item ids, vectorised membership test."""
+
+    def __init__(self, n_users: int, user_memory: int):
+        self.ring = np.full((n_users, user_memory), -1, dtype=np.int32)
+        self.count = np.zeros(n_users, dtype=np.int64)
+        self.mem = user_memory
+
+    def add(self, u: np.ndarray, i: np.ndarray) -> None:
+        for a, b in zip(u.tolist(), i.tolist()):          # arrival order matters for the FIFO
+            self.ring[a, self.count[a] % self.mem] = b
+            self.count[a] += 1
+
+    def contains(self, u: np.ndarray, cand: np.ndarray) -> np.ndarray:
+        """``cand`` ``[n, k]`` -> bool ``[n, k]``: candidate is in its user's memory."""
+        return (self.ring[u][:, None, :] == cand[:, :, None]).any(axis=2)
+
+
 def ps_online_mf_device(src, num_factors: int = 10, range_min: float = -0.01, range_max: float = 0.01,
                         learning_rate: float = 0.01, negative_sample_rate: int = 9, user_memory: int = 128,
                         pull_limit: int = 1600, *, n_users: Optional[int] = None, n_items: Optional[int] = None,
@@ -395,24 +476,23 @@ def ps_online_mf_device(src, num_factors: int = 10, range_min: float = -0.01, ra
                         iteration_wait_time: int = 1000, return_model: bool = False):
     """Device twin of ``ps_online_mf`` (single pass over a rating stream with negative sampling).
 
-    Records are consumed in arrival order in micro-batches.  Negatives (rating 0) are drawn on the
-    device from the items seen *so far in the stream* (``PSOnlineMatrixFactorizationWorker.scala:71-78``);
-    the per-user exclusion set of the reference (last ``user_memory`` items of that user) is
-    approximated by excluding the record's own item - with ``negative_sample_rate`` draws out of
-    thousands of seen items the two differ on a vanishing fraction of draws.
+    Records are consumed in arrival order in micro-batches.  Per rating, up to ``negative_sample_rate``
+    negatives (rating 0) are drawn from the items seen so far in the stream and rejected while they are
+    among the user's last ``user_memory`` items (``PSOnlineMatrixFactorizationWorker.scala:59-89``) - on
+    the device, by ``NegativeSampler`` (per-user rings + Philox rejection sampler in ``csrc/sampler.cu``);
+    negatives of a record come right before it, like the reference's block order.
     ``streaming=True`` feeds the persistent ring-consumer kernel (``OnlineStream``) instead of one
-    launch per micro-batch; the job then ends by the device-side idle timeout."""
+    launch per micro-batch; the job then ends by the device-side idle timeout.  There the producer is
+    the host, so the same sampling runs on the host (``_HostSeenRing``)."""
     import torch
     from ...parallel.device_context import get_context
     ctx = get_context()
-    ratings = list(src)
+    ratings = list(src) if not isinstance(src, list) else src
     n_users = n_users or (max(r.user for r in ratings) + 1)
     n_items = n_items or (max(r.item for r in ratings) + 1)
     mf = DeviceMF(n_users, n_items, num_factors, range_min, range_max, learning_rate, pull_limit=pull_limit,
                   seed=seed, lazy=lazy, variant="direct", ctx=ctx)
     u_all, i_all, r_all = _ratings_to_tensors(ratings, ctx.rank, ctx.world_size)
-    gen = torch.Generator(device="cuda").manual_seed(seed * 31 + ctx.rank)
-    seen = torch.zeros(n_items, dtype=torch.bool, device="cuda")
     if streaming:
         # The producer of a stream is the host: negatives are drawn with numpy and the records go straight
         # into the ring.  (Besides being the natural place, it keeps the GPU free of producer work - a
@@ -424,48 +504,37 @@ def ps_online_mf_device(src, num_factors: int = 10, range_min: float = -0.01, ra
         rng = np.random.default_rng(seed * 31 + ctx.rank)
         u_np, i_np, r_np = u_all.cpu().numpy(), i_all.cpu().numpy(), r_all.cpu().numpy()
         seen_np = np.zeros(n_items, dtype=bool)
+        memory = _HostSeenRing(n_users, user_memory) if negative_sample_rate > 0 else None
         for s in range(0, len(u_np), batch_size):
             u, i, r = u_np[s:s + batch_size], i_np[s:s + batch_size], r_np[s:s + batch_size]
-            pool = np.flatnonzero(seen_np).astype(np.int32)
             seen_np[i] = True
-            if negative_sample_rate > 0 and pool.size > 1:
+            pool = np.flatnonzero(seen_np).astype(np.int32)
+            if memory is not None and pool.size > 1:
+                memory.add(u, i)
                 k = negative_sample_rate
                 neg_i = pool[rng.integers(0, pool.size, size=(len(u), k))]
-                keep = (neg_i != i[:, None]).ravel()
-                nu = np.repeat(u, k)[keep]
-                ni = neg_i.ravel()[keep]
-                u = np.concatenate([nu, u])
-                i = np.concatenate([ni, i])
-                r = np.concatenate([np.zeros(len(nu), np.float32), r])
+                bad = memory.contains(u, neg_i)
+                for _ in range(4):                       # re-draw the rejected candidates a few times
+                    if not bad.any():
+                        break
+                    neg_i[bad] = pool[rng.integers(0, pool.size, size=int(bad.sum()))]
+                    bad = memory.contains(u, neg_i)
+                keep = ~bad
+                # block order: the negatives of a record, then the record
+                blk_u = np.concatenate([np.repeat(u[:, None], k, 1), u[:, None]], axis=1)
+                blk_i = np.concatenate([neg_i, i[:, None]], axis=1)
+                blk_r = np.concatenate([np.zeros((len(u), k), np.float32), r[:, None]], axis=1)
+                blk_k = np.concatenate([keep, np.ones((len(u), 1), bool)], axis=1).ravel()
+                u, i, r = blk_u.ravel()[blk_k], blk_i.ravel()[blk_k], blk_r.ravel()[blk_k]
             stream.feed(u, i, r)
         stream.join()
-        torch.cuda.synchronize()
-        ctx.barrier()
-        mf.stats()
-        out = mf.dump()
-        return (out, mf) if return_model else out
-    stream = None
-    for s in range(0, u_all.numel(), batch_size):
-        u, i, r = u_all[s:s + batch_size], i_all[s:s + batch_size], r_all[s:s + batch_size]
-        pool = torch.nonzero(seen).flatten().int()
-        seen[i.long()] = True
-        if negative_sample_rate > 0 and pool.numel() > 1:
-            k = negative_sample_rate
-            pick = torch.randint(0, pool.numel(), (u.numel(), k), device="cuda", generator=gen)
-            neg_i = pool[pick]
-            keep = (neg_i != i[:, None]).flatten()
-            nu = u[:, None].expand(-1, k).flatten()[keep]
-            ni = neg_i.flatten()[keep]
-            # negatives of a record come right before it, like the reference's block order
-            u = torch.cat([nu, u])
-            i = torch.cat([ni, i])
-            r = torch.cat([torch.zeros(nu.numel(), device="cuda"), r])
-        if stream is not None:
-            stream.feed(u.cpu(), i.cpu(), r.cpu())
-        else:
+    else:
+        sampler = NegativeSampler(mf, negative_sample_rate, user_memory, seed) if negative_sample_rate > 0 else None
+        for s in range(0, u_all.numel(), batch_size):
+            u, i, r = u_all[s:s + batch_size], i_all[s:s + batch_size], r_all[s:s + batch_size]
+            if sampler is not None:
+                u, i, r = sampler.expand(u.contiguous(), i.contiguous(), r.contiguous())
             mf.step(u.contiguous(), i.contiguous(), r.contiguous())
-    if stream is not None:
-        stream.join()
     torch.cuda.synchronize()
     ctx.barrier()
     mf.stats()

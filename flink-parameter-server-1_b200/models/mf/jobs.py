@@ -37,8 +37,15 @@ def ps_offline_mf(src, num_factors: int = 10, range_min: float = -0.01, range_ma
                   learning_rate: float = 0.01, negative_sample_rate: int = 0, user_memory: int = 128,
                   iterations: int = 1, pull_limit: int = 1600, worker_parallelism: int = 1,
                   ps_parallelism: int = 1, iteration_wait_time: int = 10000, *, seed: int = 0,
-                  shuffle: bool = True, lambda_: float = 0.0, **engine_kw):
-    """Returns the stream of ``Left((user, vec))`` / ``Right((item, vec))`` updates."""
+                  shuffle: bool = True, lambda_: float = 0.0, engine: str = "host", **engine_kw):
+    """Returns the stream of ``Left((user, vec))`` / ``Right((item, vec))`` updates.
+    ``engine="device"``: the same job on the GPU engine (``models/mf/device.py``; ``ps_parallelism``
+    becomes the number of item shards on one GPU, one shard per rank under torchrun)."""
+    if _use_device(engine):
+        from .device import ps_offline_mf_device
+        return ps_offline_mf_device(src, num_factors, range_min, range_max, learning_rate, negative_sample_rate,
+                                    user_memory, iterations, pull_limit, seed=seed, shuffle=shuffle,
+                                    lambda_=lambda_, n_shards=_device_shards(ps_parallelism), **engine_kw)
     ratings = flat_map_with_eof(src, WrapWithEOF, worker_parallelism,
                                 lambda key, n: key % n, lambda r: r.user)
     init_desc = RangedRandomFactorInitializerDescriptor(num_factors, range_min, range_max, seed,
@@ -55,7 +62,14 @@ def ps_offline_mf(src, num_factors: int = 10, range_min: float = -0.01, range_ma
 def ps_online_mf(src, num_factors: int = 10, range_min: float = -0.01, range_max: float = 0.01,
                  learning_rate: float = 0.01, negative_sample_rate: int = 9, user_memory: int = 128,
                  pull_limit: int = 1600, worker_parallelism: int = 1, ps_parallelism: int = 1,
-                 iteration_wait_time: int = 10000, *, seed: int = 0, lambda_: float = 0.0, **engine_kw):
+                 iteration_wait_time: int = 10000, *, seed: int = 0, lambda_: float = 0.0,
+                 engine: str = "host", **engine_kw):
+    """``engine="device"``: micro-batched launches (or ``streaming=True``: the persistent ring consumer)
+    with the device negative sampler honouring ``user_memory`` (``models/mf/device.py``)."""
+    if _use_device(engine):
+        from .device import ps_online_mf_device
+        return ps_online_mf_device(src, num_factors, range_min, range_max, learning_rate, negative_sample_rate,
+                                   user_memory, pull_limit, seed=seed, **engine_kw)
     init = RangedRandomFactorInitializerDescriptor(num_factors, range_min, range_max, seed,
                                                    philox.STREAM_ITEM).open()
     worker = PSOnlineMatrixFactorizationWorker(
@@ -66,6 +80,41 @@ def ps_online_mf(src, num_factors: int = 10, range_min: float = -0.01, range_max
     return transform(part, logic, ps_logic=SimplePSLogic(lambda i: init.next_factor(i), vector_sum),
                      worker_parallelism=worker_parallelism, ps_parallelism=ps_parallelism,
                      iteration_wait_time=iteration_wait_time, **engine_kw)
+
+
+def _use_device(engine: str) -> bool:
+    if engine not in ("host", "device", "auto"):
+        raise ValueError("engine must be 'host', 'device' or 'auto'")
+    if engine == "host":
+        return False
+    from ...parallel import device_engine
+    ok, why = device_engine.device_ready()
+    if not ok:
+        device_engine.fallback(why, strict=False)
+    return ok
+
+
+def _device_shards(ps_parallelism: int):
+    from ...parallel.device_context import get_context
+    return None if get_context().distributed else max(1, min(int(ps_parallelism), 16))
+
+
+def device_pruning(strategy: LEMPPruningStrategy) -> bool:
+    """What the device top-K kernel does with a ``LEMPPruningStrategy``
+    (``pruning/LEMPPruningStrategy.scala:6-50``).  The kernel scores whole 64-item tiles on the tensor
+    cores and applies the LENGTH bound per bucket (skip every later tile once ``max|p| * |q| <= theta``).
+    COORD and INCR are *per-candidate* filters that only avoid scalar dot products of items that cannot
+    enter the top-K - they never change the result, and a tile's MMA is issued for all 64 items anyway.
+    So every strategy returns exactly what the reference's would; for the ones with a COORD / INCR part
+    a ``DeviceFallbackWarning``-class note says that this part is not executed."""
+    from .pruning import LENGTH
+    if not isinstance(strategy, LENGTH):
+        import warnings
+        from ...parallel.device_engine import DeviceFallbackWarning
+        warnings.warn(f"engine='device': pruning strategy {strategy!r} runs as the LENGTH bucket bound; its "
+                      "COORD / INCR candidate filters do not change results and are not executed on the "
+                      "tensor-core path", DeviceFallbackWarning, stacklevel=3)
+    return True
 
 
 def _broadcast_queries(src, worker_parallelism: int) -> DataStream:
@@ -80,10 +129,17 @@ def ps_top_k_generator(src, model, num_factors: int = 10, user_memory: int = 0, 
                        worker_k: int = 75, bucket_size: int = 100,
                        pruning_algorithm: LEMPPruningStrategy = COORD(), pull_limit: int = 1600,
                        worker_parallelism: int = 4, ps_parallelism: int = 4,
-                       iteration_wait_time: int = 10000, **engine_kw):
-    """``model`` yields ``Left((user, (len, vec)))`` -> PS and ``Right((item, (len, vec)))`` -> the
+                       iteration_wait_time: int = 10000, *, engine: str = "host", **engine_kw):
+    """``engine="device"``: tcgen05 scoring of the local item tiles + cross-GPU merge
+    (``models/mf/device_topk.py``); see ``device_pruning`` for how ``pruning_algorithm`` is honoured.
+
+    ``model`` yields ``Left((user, (len, vec)))`` -> PS and ``Right((item, (len, vec)))`` -> the
     worker ``item % W`` (placement by key).  Unknown users answer an empty top-K.
     Returns ``[(item, timestamp, [(score, item), ...]), ...]``."""
+    if _use_device(engine):
+        from .device_topk import ps_top_k_generator_device
+        return ps_top_k_generator_device(src, model, num_factors, user_memory, K, worker_k,
+                                         use_pruning=device_pruning(pruning_algorithm), **engine_kw)
     invalid = (-1, np.zeros(0))
     worker = PSTopKGeneratorWorker(worker_k, bucket_size, worker_parallelism, pruning_algorithm)
     logic = add_pull_limiter(worker, pull_limit)
@@ -103,8 +159,16 @@ def ps_online_learner_and_generator(src, num_factors: int = 10, range_min: float
                                     pruning_algorithm: LEMPPruningStrategy = LI(5, 2.5),
                                     pull_limit: int = 500, worker_parallelism: int = 4,
                                     ps_parallelism: int = 4, iteration_wait_time: int = 10000, *,
-                                    seed: int = 0, **engine_kw):
-    """Prequential recommend-then-learn.  Returns ``[(user, item, timestamp, topK), ...]``."""
+                                    seed: int = 0, engine: str = "host", **engine_kw):
+    """Prequential recommend-then-learn.  Returns ``[(user, item, timestamp, topK), ...]``.
+    ``engine="device"`` needs ``n_users`` and ``n_items`` (table sizes) among the keyword arguments."""
+    if _use_device(engine):
+        from .device_topk import ps_online_learner_and_generator_device
+        out, _lg = ps_online_learner_and_generator_device(
+            src, num_factors=num_factors, range_min=range_min, range_max=range_max, learning_rate=learning_rate,
+            negative_sample_rate=negative_sample_rate, user_memory=user_memory, K=K, worker_k=worker_k,
+            pull_limit=pull_limit, seed=seed, use_pruning=device_pruning(pruning_algorithm), **engine_kw)
+        return out
     item_desc = RangedRandomFactorInitializerDescriptor(num_factors, range_min, range_max, seed,
                                                         philox.STREAM_ITEM)
     user_init = RangedRandomFactorInitializerDescriptor(num_factors, range_min, range_max, seed,

@@ -72,6 +72,7 @@ class PSOfflineMatrixFactorizationWorker(WorkerLogic):
             num_factors, range_min, range_max, seed, philox.STREAM_USER)
         self.factor_update = SGDUpdater(learning_rate, lambda_)
         self.negative_sample_rate = negative_sample_rate
+        self.user_memory = user_memory
         self.iterations = iterations
         self.shuffle = shuffle
         self.seed = seed

@@ -169,3 +169,40 @@ def _run_stream(pa: DevicePA, input_source, batch_size: int, long_id: bool, to_l
     torch.cuda.synchronize()
     pa.ctx.barrier()
     return out + pa.dump(), pa
+
+
+def method_to_device(method) -> dict:
+    """Maps a host ``PassiveAggressiveAlgorithm`` object (``models/pa/algorithm.py``) to the kernel's
+    parameters: ``algorithm`` (binary / ova / pb / ml), ``variant`` (pa / pa_i / pa_ii), ``aggressiveness``,
+    ``label_count`` and the class-cost matrix of the cost-based rules."""
+    from . import algorithm as A
+    variants = {0: "pa", 1: "pa_i", 2: "pa_ii"}
+    if isinstance(method, A.PassiveAggressiveCostBased):
+        L = method.label_count
+        cost = np.array([[float(method.cost(y, q)) for q in range(L)] for y in range(L)], dtype=np.float32)
+        return {"algorithm": "pb" if method.mode.upper() == "PB" else "ml", "variant": "pa", "aggressiveness": 1.0,
+                "label_count": L, "cost": cost}
+    if isinstance(method, A.PassiveAggressiveOneVersusAll):
+        return {"algorithm": "ova", "variant": variants[method.VARIANT], "aggressiveness": method.aggressiveness or 1.0,
+                "label_count": method.label_count, "cost": None}
+    if isinstance(method, A.PassiveAggressiveBinaryAlgorithm):
+        return {"algorithm": "binary", "variant": variants[method.VARIANT], "aggressiveness": method.aggressiveness or 1.0,
+                "label_count": 1, "cost": None}
+    raise NotImplementedError(f"no device kernel for {type(method).__name__}")
+
+
+def run_pa_method_device(input_source, method, *, feature_count: int, pull_limit: int = 0,
+                         range_partitioning: bool = True, batch_size: int = 4096, model=None,
+                         long_id: bool = False, n_shards: Optional[int] = None):
+    """The online PA job of ``transformGeneric`` (``PassiveAggressiveParameterServer.scala:239-368``) on
+    the device for any of the built-in update rules; ``model`` = ``(feature, param)`` pairs to warm-start
+    from (``transformWithModelLoad``).  Returns ``(output stream, DevicePA)``."""
+    kw = method_to_device(method)
+    pa = DevicePA(feature_count, label_count=kw["label_count"], algorithm=kw["algorithm"], variant=kw["variant"],
+                  aggressiveness=kw["aggressiveness"], range_partitioning=range_partitioning,
+                  pull_limit=pull_limit, cost=kw["cost"], n_shards=n_shards)
+    if model is not None:
+        pa.load(model)
+    binary = kw["algorithm"] == "binary"
+    return _run_stream(pa, input_source, batch_size, long_id=long_id,
+                       to_label=(lambda p: p > 0) if binary else int)

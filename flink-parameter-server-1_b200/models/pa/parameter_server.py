@@ -93,7 +93,27 @@ class PAWorkerLogic(WorkerLogic):
 
 def _transform_generic(model, init, add, input_source, worker_parallelism, ps_parallelism, method,
                        pull_limit, feature_count, range_partitioning, iteration_wait_time, long_id,
-                       **engine_kw):
+                       engine: str = "host", **engine_kw):
+    if engine not in ("host", "device", "auto"):
+        raise ValueError("engine must be 'host', 'device' or 'auto'")
+    if engine != "host":
+        # the device twin: CSR mini-batches through the fused gather / margin / scatter kernel
+        from ...parallel import device_engine
+        ok, why = device_engine.device_ready()
+        if ok:
+            from ...parallel.device_context import get_context
+            from .device import run_pa_method_device
+            records = input_source.collect() if hasattr(input_source, "collect") else list(input_source)
+            warm = None
+            if model is not None:
+                warm = [(e.value if hasattr(e, "value") else e) for e in
+                        (model.collect() if hasattr(model, "collect") else list(model))]
+            shards = None if get_context().distributed else max(1, min(int(ps_parallelism), 16))
+            out, _pa = run_pa_method_device(records, method, feature_count=feature_count, pull_limit=pull_limit,
+                                            range_partitioning=range_partitioning, model=warm, long_id=long_id,
+                                            n_shards=shards, **engine_kw)
+            return out
+        device_engine.fallback(why)
     if range_partitioning:
         server_logic = RangePSLogicWithClose(feature_count, init, add)
         partitioner = range_partitioner_ps(feature_count, ps_parallelism)

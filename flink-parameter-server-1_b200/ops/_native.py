@@ -83,6 +83,25 @@ class FpsMfParams(C.Structure):
     ]
 
 
+class FpsNegSampler(C.Structure):
+    _fields_ = [
+        ("seen", C.c_void_p),
+        ("seen_count", C.c_void_p),
+        ("item_bitmap", C.c_void_p),
+        ("item_pool", C.c_void_p),
+        ("pool_count", C.c_void_p),
+        ("n_items", C.c_int64),
+        ("seed", C.c_uint64),
+        ("user_memory", C.c_int32),
+        ("rate", C.c_int32),
+        ("local_shard", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+
+SKIP_ID = -2147483648
+
+
 class FpsPaParams(C.Structure):
     _fields_ = [
         ("variant", C.c_int32),
@@ -140,6 +159,7 @@ def lib() -> C.CDLL:
         "fps_table_dump_shard": (C.c_int, [P(FpsTableView), C.c_int, i64, i64, vp, vp, i64, vp, vp]),
         "fps_mf_sgd_step": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, vp, i64, P(FpsMfParams), vp, vp]),
         "fps_mf_predict": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, i64, vp, vp]),
+        "fps_mf_sample_negatives": (C.c_int, [P(FpsTableView), P(FpsNegSampler), vp, vp, vp, i64, u64, vp, vp, vp, vp]),
         "fps_mf_tiles_scratch_bytes": (C.c_size_t, [i64]),
         "fps_mf_bucket": (C.c_int, [vp, vp, vp, i64, vp, C.c_size_t, vp]),
         "fps_mf_sgd_tiles": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, i64, P(FpsMfParams), vp, vp]),

@@ -1,0 +1,219 @@
+"""The device engine behind the public API.
+
+``transform(training_data, worker_logic, param_init, param_update, W, S, wait, engine="device")``
+(``M/FlinkParameterServer.scala:62-77``, ``:108-149``) and the named jobs
+(``ps_offline_mf``, ``ps_online_mf``, ``ps_top_k_generator``, ``ps_online_learner_and_generator``,
+``transform_binary``, ``transform_multiclass``) accept ``engine="host" | "device" | "auto"``.
+
+On the device a worker logic is not Python code but a *device functor* - a fused kernel that does
+pull, compute and push for a whole batch.  This module is the registry that maps the built-in
+``WorkerLogic`` classes to their functors and the known ``param_update`` callables to the update
+modes the tables implement, so a new functor can be plugged in without touching the front-ends:
+
+    @register_device_logic(MyWorkerLogic)
+    def run_my_logic(job: DeviceJob) -> list: ...
+
+    register_param_update(my_update_fn, "add")        # "add" | "overwrite" | "add_norm"
+
+A logic or an update rule with no device twin falls back to the host engine **with a warning**
+(``DeviceFallbackWarning``), never silently; ``engine="device"`` with ``strict=True`` raises instead.
+"""
+from __future__ import annotations
+
+import warnings
+from dataclasses import dataclass, field
+from typing import Any, Callable, Dict, List, Optional, Tuple
+
+
+class DeviceFallbackWarning(UserWarning):
+    """The requested job ran on the host engine because it has no device twin."""
+
+
+@dataclass
+class DeviceJob:
+    """Everything a device runner gets: the unwrapped logic, the limiter's limit, the materialised
+    input records and the arguments of ``transform``."""
+    logic: Any
+    pull_limit: int
+    records: List[Any]
+    param_init: Optional[Callable] = None
+    param_update: Optional[Callable] = None
+    update_mode: Optional[str] = None
+    ps_logic: Any = None
+    worker_parallelism: int = 1
+    ps_parallelism: int = 1
+    iteration_wait_time: int = 10000
+    extra: Dict[str, Any] = field(default_factory=dict)
+
+
+_RUNNERS: Dict[type, Callable[[DeviceJob], list]] = {}
+_PARAM_UPDATES: List[Tuple[Callable, str]] = []
+UPDATE_MODES = ("add", "overwrite", "add_norm")
+
+
+def register_device_logic(logic_cls: type):
+    def deco(fn: Callable[[DeviceJob], list]):
+        _RUNNERS[logic_cls] = fn
+        return fn
+    return deco
+
+
+def register_param_update(fn: Callable, mode: str) -> None:
+    if mode not in UPDATE_MODES:
+        raise ValueError(f"update mode must be one of {UPDATE_MODES}")
+    _PARAM_UPDATES.append((fn, mode))
+
+
+def param_update_mode(fn: Optional[Callable]) -> Optional[str]:
+    """The table update mode a ``param_update`` callable stands for, or ``None``."""
+    if fn is None:
+        return None
+    tagged = getattr(fn, "device_update_mode", None)
+    if tagged in UPDATE_MODES:
+        return tagged
+    for known, mode in _PARAM_UPDATES:
+        if fn is known:
+            return mode
+    return None
+
+
+def unwrap_limiter(worker_logic) -> Tuple[Any, int]:
+    """``add_pull_limiter(logic, n)`` -> ``(logic, n)``; a bare logic -> ``(logic, 0)``."""
+    limit = 0
+    seen = 0
+    while hasattr(worker_logic, "inner") and seen < 8:
+        limit = int(getattr(worker_logic, "pull_limit", limit) or limit)
+        worker_logic = worker_logic.inner
+        seen += 1
+    return worker_logic, limit
+
+
+def device_ready() -> Tuple[bool, str]:
+    try:
+        import torch
+    except Exception as e:      # pragma: no cover
+        return False, f"torch is not importable ({e})"
+    if not torch.cuda.is_available():
+        return False, "no CUDA device"
+    from ..ops import _native
+    if not _native.available():
+        return False, f"{_native.LIB_PATH} has not been built"
+    return True, ""
+
+
+def runner_for(logic) -> Optional[Callable[[DeviceJob], list]]:
+    _ensure_builtin_runners()
+    for cls in type(logic).__mro__:
+        if cls in _RUNNERS:
+            return _RUNNERS[cls]
+    return None
+
+
+def _materialise(training_data) -> list:
+    if hasattr(training_data, "collect"):
+        return training_data.collect()
+    return list(training_data)
+
+
+def fallback(reason: str, strict: bool = False) -> None:
+    if strict:
+        raise NotImplementedError(f"engine='device': {reason}")
+    warnings.warn(f"engine='device': {reason}; running on the host engine", DeviceFallbackWarning, stacklevel=3)
+
+
+def try_transform(training_data, worker_logic, param_init, param_update, worker_parallelism: int,
+                  ps_parallelism: int, iteration_wait_time: int, ps_logic=None, strict: bool = False,
+                  **extra) -> Tuple[bool, Optional[list]]:
+    """Run the job on the device engine if its logic has a registered functor.  Returns
+    ``(handled, output)``; ``handled`` False = the caller should run the host engine (a
+    ``DeviceFallbackWarning`` has been issued)."""
+    ok, why = device_ready()
+    if not ok:
+        fallback(why, strict)
+        return False, None
+    logic, limit = unwrap_limiter(worker_logic)
+    run = runner_for(logic)
+    if run is None:
+        fallback(f"no device functor is registered for {type(logic).__name__} "
+                 f"(register one with parallel.device_engine.register_device_logic)", strict)
+        return False, None
+    if ps_logic is not None and param_update is None:
+        param_update = getattr(ps_logic, "param_update", None) or getattr(ps_logic, "update", None)
+        param_init = param_init or getattr(ps_logic, "param_init", None) or getattr(ps_logic, "init", None)
+    mode = param_update_mode(param_update)
+    if param_update is not None and mode is None:
+        fallback(f"param_update {getattr(param_update, '__name__', param_update)!r} has no device update mode "
+                 f"(known: {UPDATE_MODES}; tag it with register_param_update)", strict)
+        return False, None
+    job = DeviceJob(logic, limit, _materialise(training_data), param_init, param_update, mode, ps_logic,
+                    worker_parallelism, ps_parallelism, iteration_wait_time, dict(extra))
+    return True, run(job)
+
+
+# ---------------------------------------------------------------------------------------------
+# built-in functors
+# ---------------------------------------------------------------------------------------------
+_builtin_done = False
+
+
+def _ensure_builtin_runners() -> None:
+    """Registers the functors of the reference's own worker logics (imported lazily: the model
+    packages import ``parameter_server``, which imports this module)."""
+    global _builtin_done
+    if _builtin_done:
+        return
+    _builtin_done = True
+    from ..models.mf import vector as mf_vector
+    from ..models.mf.workers import (PSOfflineMatrixFactorizationWorker, PSOnlineMatrixFactorizationWorker)
+    from ..models.pa.parameter_server import PAWorkerLogic
+
+    register_param_update(mf_vector.vector_sum, "add")
+
+    def _ratings(records):
+        out = []
+        for r in records:
+            if hasattr(r, "is_right"):          # Right(Rating) / Left(EOF) wrappers of flat_map_with_eof
+                if r.is_right:
+                    out.append(r.value)
+            else:
+                out.append(r)
+        return out
+
+    def _n_shards(job: DeviceJob):
+        from .device_context import get_context
+        return None if get_context().distributed else max(1, min(job.ps_parallelism, 16))
+
+    @register_device_logic(PSOfflineMatrixFactorizationWorker)
+    def _offline_mf(job: DeviceJob) -> list:
+        from ..models.mf.device import ps_offline_mf_device
+        w = job.logic
+        d = w.factor_init_desc
+        if job.update_mode not in (None, "add"):
+            raise NotImplementedError("the MF functor applies param_update = add")
+        return ps_offline_mf_device(_ratings(job.records), d.num_factors, d.range_min, d.range_max,
+                                    w.factor_update.learning_rate, w.negative_sample_rate,
+                                    getattr(w, "user_memory", 128), w.iterations, job.pull_limit,
+                                    seed=w.seed, shuffle=w.shuffle, lambda_=w.factor_update.lambda_,
+                                    n_shards=_n_shards(job), **job.extra)
+
+    @register_device_logic(PSOnlineMatrixFactorizationWorker)
+    def _online_mf(job: DeviceJob) -> list:
+        from ..models.mf.device import ps_online_mf_device
+        w = job.logic
+        d = w.factor_init_desc
+        if job.update_mode not in (None, "add"):
+            raise NotImplementedError("the MF functor applies param_update = add")
+        return ps_online_mf_device(_ratings(job.records), d.num_factors, d.range_min, d.range_max,
+                                   w.factor_update.learning_rate, w.negative_sample_rate, w.user_memory,
+                                   job.pull_limit, seed=w.seed, **job.extra)
+
+    @register_device_logic(PAWorkerLogic)
+    def _pa(job: DeviceJob) -> list:
+        from ..models.pa.device import run_pa_method_device
+        feature_count = job.extra.pop("feature_count", None) or getattr(job.ps_logic, "feature_count", None)
+        if not feature_count:
+            raise ValueError("the PA functor needs feature_count (pass it to transform(..., feature_count=n))")
+        out, _pa_model = run_pa_method_device(job.records, job.logic.method, feature_count=feature_count,
+                                              pull_limit=job.pull_limit, long_id=job.logic.long_id,
+                                              n_shards=_n_shards(job), **job.extra)
+        return out

@@ -52,9 +52,24 @@ def transform_generic(training_data, worker_logic: WorkerLogic, ps_logic: Parame
 def transform(training_data, worker_logic: WorkerLogic, param_init=None, param_update=None,
               worker_parallelism: int = 1, ps_parallelism: int = 1, iteration_wait_time: int = 10000,
               *, ps_logic: Optional[ParameterServerLogic] = None, param_partitioner=None,
-              w_in_partition=None, by_name: bool = False, return_engine: bool = False, **engine_kw):
+              w_in_partition=None, by_name: bool = False, return_engine: bool = False,
+              engine: str = "host", device_kw: Optional[dict] = None, **engine_kw):
     """README signature.  Give either ``param_init`` + ``param_update`` (builds a
-    ``SimplePSLogic``) or a ready ``ps_logic``."""
+    ``SimplePSLogic``) or a ready ``ps_logic``.
+
+    ``engine="device"`` runs the job on the GPU engine when the worker logic (under its pull limiter,
+    if any) has a registered device functor and ``param_update`` a device update mode
+    (``parallel/device_engine.py``); otherwise it says so in a ``DeviceFallbackWarning`` and runs
+    here.  ``device_kw`` are passed to the functor (e.g. ``n_users``, ``feature_count``)."""
+    if engine not in ("host", "device", "auto"):
+        raise ValueError("engine must be 'host', 'device' or 'auto'")
+    if engine != "host":
+        from .parallel import device_engine
+        handled, out = device_engine.try_transform(
+            training_data, worker_logic, param_init, param_update, worker_parallelism, ps_parallelism,
+            iteration_wait_time, ps_logic=ps_logic, **(device_kw or {}))
+        if handled:
+            return out
     if ps_logic is None:
         if param_init is None or param_update is None:
             raise ValueError("transform needs param_init and param_update, or ps_logic")

@@ -195,6 +195,40 @@ int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const fl
 int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, void* d_scratch, int64_t n,
                      const FpsMfParams* params, FpsFlow* d_flow, void* stream);
 
+/* ---- negative sampling on the device (K4) ------------------------------------------------------ */
+/* A record whose user id is FPS_SKIP_ID is passed over by every MF kernel without being counted.   */
+#define FPS_SKIP_ID (-2147483647 - 1)
+/* Device-resident state of one worker's sampler; the caller allocates and zeroes the arrays (seen may
+ * hold anything: seen_count says how much of a ring is valid).
+ *   seen        [n_rings * user_memory] int32 - ring of the last user_memory items of every local user
+ *   seen_count  [n_rings] int32              - items appended to the ring so far
+ *   item_bitmap [ceil(n_items / 32)] uint32   - items this worker has seen
+ *   item_pool   [n_items] int32, pool_count [1] int32 - the same as a list, in order of first sight
+ * n_rings = rows_per_shard of the user table (local_shard >= 0) or n_shards * rows_per_shard (-1).    */
+typedef struct FpsNegSampler {
+  int32_t*  seen;
+  int32_t*  seen_count;
+  uint32_t* item_bitmap;
+  int32_t*  item_pool;
+  int32_t*  pool_count;
+  int64_t   n_items;
+  uint64_t  seed;
+  int32_t   user_memory;     /* userMemory of the reference (default 128)                           */
+  int32_t   rate;            /* negativeSampleRate                                                  */
+  int32_t   local_shard;     /* shard of the user table that lives here, -1 = all of them           */
+  int32_t   reserved;
+} FpsNegSampler;
+/* Registers the n positive ratings (item -> the user's recent-items ring and the worker's item pool),
+ * then writes the expanded batch of n * (rate + 1) records: per rating its negatives (rating 0, drawn
+ * from the items seen so far, rejected while in the user's ring, at most 32 candidates each) followed
+ * by the rating itself; unused negative slots get user id FPS_SKIP_ID.  Draws are keyed by
+ * (seed, step_tag, record, draw).  PSOnlineMatrixFactorizationWorker.scala:59-89,
+ * PSOfflineMatrixFactorizationWorker.scala:64-95.                                                     */
+int fps_mf_sample_negatives(const FpsTableView* users, const FpsNegSampler* sampler,
+                            const int32_t* d_user_ids, const int32_t* d_item_ids, const float* d_ratings,
+                            int64_t n, uint64_t step_tag, int32_t* d_out_users, int32_t* d_out_items,
+                            float* d_out_ratings, void* stream);
+
 /* Replicated table with deferred pushes: add the locally accumulated deltas to every other replica
  * (red.add.v4 per peer, all-zero 16-byte chunks are skipped) and clear them.  Run it on the stream of
  * the step kernels, after them.                                                                    */

@@ -16,6 +16,7 @@ STRUCTS = {
     "FpsFlow": N.FpsFlow,
     "FpsMfParams": N.FpsMfParams,
     "FpsPaParams": N.FpsPaParams,
+    "FpsNegSampler": N.FpsNegSampler,
 }
 RENAMED = {"lambda_": "lambda"}          # Python keyword
 

@@ -1,0 +1,175 @@
+"""The ``engine=`` switch of the public entry points (parallel/device_engine.py).
+
+CPU part: registry, limiter unwrapping, and the loud fallback when no GPU engine is available.
+GPU part (marked): the same test body through ``engine="host"`` and ``engine="device"`` of the public
+entry points only - ``transform``, ``ps_offline_mf``, ``ps_online_mf``, ``transform_binary``."""
+import math
+import random
+import warnings
+
+import numpy as np
+import pytest
+
+from fps_b200 import Left, Right, last_write_wins, lefts, rights
+from fps_b200.models.mf import Rating, ps_offline_mf, ps_online_mf
+from fps_b200.models.mf.vector import vector_sum
+from fps_b200.parallel import device_engine as DE
+from fps_b200.parameter_server import transform
+from fps_b200.worker_logic import add_pull_limiter
+
+
+def _has_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def _ratings(seed=47, n=100, users=20, items=15):
+    rnd = random.Random(seed)
+    seen, out = set(), []
+    for _ in range(n):
+        a, b = rnd.randrange(users), rnd.randrange(items)
+        if (a, b) not in seen:
+            seen.add((a, b)); out.append(Rating(a, b, rnd.random()))
+    return out
+
+
+def _rmse(out, ratings):
+    users, items = last_write_wins(lefts(out)), last_write_wins(rights(out))
+    se = sum((r.rating - float(np.dot(users[r.user], items[r.item]))) ** 2 for r in ratings)
+    return math.sqrt(se / len(ratings))
+
+
+def test_registry_knows_the_builtin_logics_and_update_rules():
+    from fps_b200.models.mf.workers import PSOfflineMatrixFactorizationWorker
+    w = PSOfflineMatrixFactorizationWorker(4, 0.0, 1.0, 0.01, 0, 128, 1)
+    inner, limit = DE.unwrap_limiter(add_pull_limiter(w, 77))
+    assert inner is w and limit == 77
+    assert DE.unwrap_limiter(w) == (w, 0)
+    assert DE.runner_for(w) is not None
+    assert DE.param_update_mode(vector_sum) == "add"
+    assert DE.param_update_mode(lambda a, b: b) is None
+
+    def overwrite(_old, new):
+        return new
+    DE.register_param_update(overwrite, "overwrite")
+    assert DE.param_update_mode(overwrite) == "overwrite"
+    with pytest.raises(ValueError):
+        DE.register_param_update(overwrite, "multiply")
+
+
+@pytest.mark.skipif(_has_gpu(), reason="checks the no-GPU fallback")
+def test_engine_device_without_a_gpu_falls_back_loudly():
+    ratings = _ratings()
+    with pytest.warns(DE.DeviceFallbackWarning):
+        out = ps_offline_mf(ratings, num_factors=15, range_min=0.0, range_max=1.0, learning_rate=0.01,
+                            iterations=10, pull_limit=10, worker_parallelism=2, ps_parallelism=2,
+                            iteration_wait_time=10, engine="device", seed=1)
+    assert _rmse(out, ratings) < 0.5
+    with pytest.raises(ValueError):
+        ps_offline_mf(ratings, engine="tpu")
+
+
+def test_unknown_logic_falls_back_with_a_warning_even_on_a_gpu_box():
+    from fps_b200.api import WorkerLogic
+
+    class Echo(WorkerLogic):
+        def on_recv(self, data, ps):
+            ps.pull(data)
+
+        def on_pull_recv(self, param_id, value, ps):
+            ps.push(param_id, 1)
+            ps.output((param_id, value))
+
+    with pytest.warns(DE.DeviceFallbackWarning):
+        out = transform([1, 2, 3, 1], Echo(), lambda i: 10 * i, lambda a, b: a + b, 2, 2, 10, engine="device")
+    assert sorted(e.value for e in out if e.is_left)[0][0] == 1
+    assert last_write_wins(rights(out)) == {1: 12, 2: 21, 3: 31}
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU: same body, both engines, public entry points only
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("engine", ["host", "device"])
+def test_ps_offline_mf_reference_acceptance_on_both_engines(engine):
+    ratings = _ratings()
+    out = ps_offline_mf(ratings, num_factors=15, range_min=0.0, range_max=1.0, learning_rate=0.01,
+                        iterations=10, pull_limit=10, worker_parallelism=4, ps_parallelism=4,
+                        iteration_wait_time=10, engine=engine, seed=1)
+    assert _rmse(out, ratings) < 0.5
+    users, items = last_write_wins(lefts(out)), last_write_wins(rights(out))
+    assert set(users) == {r.user for r in ratings} and set(items) == {r.item for r in ratings}
+
+
+@pytest.mark.gpu
+def test_transform_with_a_builtin_logic_dispatches_to_the_device_functor():
+    """README-signature ``transform`` with the offline MF worker under a pull limiter: the device run
+    (conflict-free waves) ends in the same factors as the host engine's serial schedule."""
+    from fps_b200.models.mf.factors import RangedRandomFactorInitializerDescriptor
+    from fps_b200.models.mf.workers import PSOfflineMatrixFactorizationWorker
+    from fps_b200.ops import philox
+    from fps_b200.utils.eof import WrapWithEOF, flat_map_with_eof
+    rnd = random.Random(9)
+    ratings = [Rating(rnd.randrange(30), rnd.randrange(25), rnd.random()) for _ in range(400)]
+    res = {}
+    for engine in ("host", "device"):
+        src = flat_map_with_eof(ratings, WrapWithEOF, 1, lambda key, n: key % n, lambda r: r.user)
+        worker = PSOfflineMatrixFactorizationWorker(12, 0.0, 0.5, 0.02, 0, 128, 2, seed=4, shuffle=False)
+        init = RangedRandomFactorInitializerDescriptor(12, 0.0, 0.5, 4, philox.STREAM_ITEM).open()
+        kw = dict(schedule="feedback_first") if engine == "host" else dict(device_kw=dict(conflict_free=True))
+        with warnings.catch_warnings():
+            warnings.simplefilter("error", DE.DeviceFallbackWarning)      # a fallback would be a failure here
+            out = transform(src, add_pull_limiter(worker, 1), lambda i: init.next_factor(i), vector_sum, 1, 1, 10,
+                            engine=engine, **kw)
+        res[engine] = (last_write_wins(lefts(out)), last_write_wins(rights(out)))
+    (hu, hi), (du, di) = res["host"], res["device"]
+    assert set(hu) == set(du) and set(hi) == set(di)
+    for k in hu:
+        np.testing.assert_allclose(du[k], hu[k], rtol=5e-4, atol=5e-5)
+    for k in hi:
+        np.testing.assert_allclose(di[k], hi[k], rtol=5e-4, atol=5e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("engine", ["host", "device"])
+def test_ps_online_mf_honours_user_memory_and_learns_on_both_engines(engine):
+    rnd = random.Random(3)
+    stream = []
+    for t in range(6000 if engine == "host" else 30000):
+        u = rnd.randrange(200)
+        stream.append(Rating(u, (u % 8) * 25 + rnd.randrange(25), 1.0, t))
+    out = ps_online_mf(stream, num_factors=8, range_min=-0.1, range_max=0.1, learning_rate=0.2,
+                       negative_sample_rate=3, user_memory=16, pull_limit=1600, iteration_wait_time=10,
+                       engine=engine, seed=2, **({"batch_size": 500} if engine == "device" else {}))
+    users, items = last_write_wins(lefts(out)), last_write_wins(rights(out))
+    pos = np.mean([users[r.user] @ items[r.item] for r in stream[-500:]])
+    neg = np.mean([users[r.user] @ items[(r.item + 100) % 200] for r in stream[-500:] if (r.item + 100) % 200 in items])
+    assert pos > neg + 0.1, (engine, pos, neg)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("engine", ["host", "device"])
+def test_transform_binary_on_both_engines(engine):
+    from fps_b200.models.pa import PassiveAggressiveBinaryAlgorithm, SparseVector, transform_binary
+    rng = np.random.default_rng(50)
+    n_feat = 2000
+    w_true = rng.normal(size=n_feat)
+    recs, vecs, labels = [], [], []
+    for _ in range(300):
+        ix = np.sort(rng.choice(n_feat, 40, replace=False))
+        vv = rng.normal(size=40)
+        v = SparseVector(ix, vv, n_feat)
+        vecs.append(v); labels.append(bool(vv @ w_true[ix] > 0))
+        recs.append(Left((v, labels[-1])))
+    recs = recs * 3 + [Right((k, v)) for k, v in enumerate(vecs[:100])]
+    out = transform_binary()(recs, 3, 3, PassiveAggressiveBinaryAlgorithm.build_pa_i(1.0), 10_000, n_feat, True,
+                             10, engine=engine)
+    preds = {e.value[0]: e.value[1] for e in out if e.is_left}
+    if engine == "host":       # the host job identifies an unlabelled example by its vector
+        preds = {k: preds[v] for k, v in enumerate(vecs[:100]) if v in preds}
+    acc = np.mean([preds[k] == labels[k] for k in range(100)])
+    assert acc >= 0.8, (engine, acc)
+    assert len(last_write_wins(rights(out))) > 0

@@ -394,3 +394,49 @@ def test_step_from_host_pipelines_the_tile_path(native):
     s = mf.stats()
     assert s["records"] == 12 * n and s["nan_count"] == 0
     assert 0 < last < 0.5
+
+
+def test_negative_sampler_respects_user_memory_and_pool(native):
+    """K4 on the device: negatives come from the items seen so far, never from the user's last
+    ``user_memory`` items; the positive closes its block; slots that cannot be filled are skipped."""
+    from fps_b200.models.mf.device import DeviceMF, NegativeSampler
+    from fps_b200.ops import _native as N
+    mf = DeviceMF(50, 400, 8, 0.0, 0.1, 0.05, n_shards=3)
+    rate, mem = 4, 6
+    sm = NegativeSampler(mf, rate, mem, seed=3)
+    rng = np.random.default_rng(0)
+    history = {u: [] for u in range(50)}
+    pool = set()
+    for step in range(6):
+        n = 300
+        u = rng.integers(0, 50, n).astype(np.int32)
+        i = rng.integers(0, 40 + 60 * step, n).astype(np.int32)
+        r = rng.random(n).astype(np.float32)
+        ou, oi, orr = (t.cpu().numpy() for t in sm.expand(*(torch.from_numpy(x).cuda() for x in (u, i, r))))
+        pool |= set(i.tolist())
+        for a, b in zip(u.tolist(), i.tolist()):
+            history[a].append(b)
+        assert sm.items_seen() == len(pool)
+        blocks_u, blocks_i, blocks_r = ou.reshape(n, rate + 1), oi.reshape(n, rate + 1), orr.reshape(n, rate + 1)
+        np.testing.assert_array_equal(blocks_u[:, rate], u)
+        np.testing.assert_array_equal(blocks_i[:, rate], i)
+        np.testing.assert_array_equal(blocks_r[:, rate], r)
+        filled = 0
+        for k in range(n):
+            # the ring holds the user's last `mem` items as of the end of this batch (batch granularity)
+            recent = set(history[int(u[k])][-mem:])
+            for d in range(rate):
+                if blocks_u[k, d] == N.SKIP_ID:
+                    continue
+                filled += 1
+                assert blocks_u[k, d] == u[k] and blocks_r[k, d] == 0.0
+                assert int(blocks_i[k, d]) in pool and int(blocks_i[k, d]) not in recent
+        assert filled > 0.95 * n * rate
+    # skipped slots are neither trained nor counted as bad ids
+    ou, oi, orr = sm.expand(*(torch.from_numpy(x).cuda() for x in (u, i, r)))
+    ou[::7] = N.SKIP_ID
+    for variant in ("direct", "tiles"):
+        m2 = DeviceMF(50, 400, 8, 0.0, 0.1, 0.05, n_shards=3, variant=variant)
+        m2.step(ou, oi, orr)
+        s = m2.stats()
+        assert s["bad_ids"] == 0 and s["records"] == int((ou != N.SKIP_ID).sum()), (variant, s)
