@@ -1,6 +1,6 @@
 // Negative sampling on the device (K4): the per-user recent-items memory and the rejection sampler
 // of the MF workers, as two kernels that turn a batch of positive ratings into the expanded batch
-// (negatives with rating 0 first, then the positive) the fused SGD kernels consume.
+// (all negatives with rating 0 first, draw by draw, then the positives) the fused SGD kernels consume.
 //
 // Reference behaviour (PSOnlineMatrixFactorizationWorker.scala:59-89,
 // PSOfflineMatrixFactorizationWorker.scala:64-95): per rating, (1) the item enters the user's
@@ -62,10 +62,15 @@ k_neg_draw(const __grid_constant__ FpsTableView users, const FpsNegSampler s, co
     const long long k = t / per;
     const int d = (int)(t - k * per);
     const int u = uid[k];
-    if (d == s.rate) {                      // the positive itself comes last in its block
-      out_u[t] = u;
-      out_i[t] = iid[k];
-      out_r[t] = rating ? rating[k] : 1.f;
+    // Layout: draw-major - all first negatives, all second negatives, ..., then all positives.  Record-major
+    // blocks would put the rate + 1 records of one user next to each other, i.e. into sub-warps that run
+    // at the same time and overwrite each other's update of that user's row (measured: the online job
+    // stopped learning).  The order "negatives before their positive" of the reference is kept.
+    const long long o = (long long)d * n + k;
+    if (d == s.rate) {
+      out_u[o] = u;
+      out_i[o] = iid[k];
+      out_r[o] = rating ? rating[k] : 1.f;
       continue;
     }
     int pick = FPS_SKIP_ID;
@@ -90,9 +95,9 @@ k_neg_draw(const __grid_constant__ FpsTableView users, const FpsNegSampler s, co
         }
       }
     }
-    out_u[t] = pick == FPS_SKIP_ID ? FPS_SKIP_ID : u;
-    out_i[t] = pick == FPS_SKIP_ID ? 0 : pick;
-    out_r[t] = 0.f;
+    out_u[o] = pick == FPS_SKIP_ID ? FPS_SKIP_ID : u;
+    out_i[o] = pick == FPS_SKIP_ID ? 0 : pick;
+    out_r[o] = 0.f;
   }
 }
 

@@ -329,8 +329,9 @@ class NegativeSampler:
 
     Parity: the ingest half of ``PSOnlineMatrixFactorizationWorker.onRecv`` (``:59-89``) and of
     ``PSOfflineMatrixFactorizationWorker.onRecv`` (``:64-95``).  ``expand`` turns a batch of positives
-    into ``n * (rate + 1)`` records - per positive its negatives (rating 0) then the positive itself -
-    with unused slots marked ``SKIP_ID`` (the SGD kernels pass over them)."""
+    into ``n * (rate + 1)`` records - first negatives of every rating, second negatives, ..., then the
+    ratings themselves (records of one user are kept apart: neighbours run concurrently) - with unused
+    slots marked ``SKIP_ID`` (the SGD kernels pass over them)."""
 
     def __init__(self, mf: "DeviceMF", negative_sample_rate: int, user_memory: int = 128, seed: int = 0):
         import torch
@@ -480,7 +481,7 @@ def ps_online_mf_device(src, num_factors: int = 10, range_min: float = -0.01, ra
     negatives (rating 0) are drawn from the items seen so far in the stream and rejected while they are
     among the user's last ``user_memory`` items (``PSOnlineMatrixFactorizationWorker.scala:59-89``) - on
     the device, by ``NegativeSampler`` (per-user rings + Philox rejection sampler in ``csrc/sampler.cu``);
-    negatives of a record come right before it, like the reference's block order.
+    within a micro-batch all negatives come before the positives.
     ``streaming=True`` feeds the persistent ring-consumer kernel (``OnlineStream``) instead of one
     launch per micro-batch; the job then ends by the device-side idle timeout.  There the producer is
     the host, so the same sampling runs on the host (``_HostSeenRing``)."""
@@ -520,12 +521,14 @@ def ps_online_mf_device(src, num_factors: int = 10, range_min: float = -0.01, ra
                     neg_i[bad] = pool[rng.integers(0, pool.size, size=int(bad.sum()))]
                     bad = memory.contains(u, neg_i)
                 keep = ~bad
-                # block order: the negatives of a record, then the record
-                blk_u = np.concatenate([np.repeat(u[:, None], k, 1), u[:, None]], axis=1)
-                blk_i = np.concatenate([neg_i, i[:, None]], axis=1)
-                blk_r = np.concatenate([np.zeros((len(u), k), np.float32), r[:, None]], axis=1)
-                blk_k = np.concatenate([keep, np.ones((len(u), 1), bool)], axis=1).ravel()
-                u, i, r = blk_u.ravel()[blk_k], blk_i.ravel()[blk_k], blk_r.ravel()[blk_k]
+                # draw-major order (all first negatives, ..., then the positives): the records of one user
+                # must not sit next to each other, neighbours run concurrently on the device
+                keep_t = keep.T.ravel()
+                nu = np.repeat(u[None, :], k, 0).ravel()[keep_t]
+                ni = neg_i.T.ravel()[keep_t]
+                u = np.concatenate([nu, u])
+                i = np.concatenate([ni, i])
+                r = np.concatenate([np.zeros(len(nu), np.float32), r])
             stream.feed(u, i, r)
         stream.join()
     else:

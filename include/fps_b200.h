@@ -219,9 +219,9 @@ typedef struct FpsNegSampler {
   int32_t   reserved;
 } FpsNegSampler;
 /* Registers the n positive ratings (item -> the user's recent-items ring and the worker's item pool),
- * then writes the expanded batch of n * (rate + 1) records: per rating its negatives (rating 0, drawn
- * from the items seen so far, rejected while in the user's ring, at most 32 candidates each) followed
- * by the rating itself; unused negative slots get user id FPS_SKIP_ID.  Draws are keyed by
+ * then writes the expanded batch of n * (rate + 1) records: slot d * n + k holds negative d of rating k
+ * (rating 0, drawn from the items seen so far, rejected while in the user's ring, at most 32 candidates
+ * each), slots rate * n + k the ratings themselves; unused negative slots get user id FPS_SKIP_ID.  Draws are keyed by
  * (seed, step_tag, record, draw).  PSOnlineMatrixFactorizationWorker.scala:59-89,
  * PSOfflineMatrixFactorizationWorker.scala:64-95.                                                     */
 int fps_mf_sample_negatives(const FpsTableView* users, const FpsNegSampler* sampler,

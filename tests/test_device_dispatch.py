@@ -167,9 +167,8 @@ def test_transform_binary_on_both_engines(engine):
     recs = recs * 3 + [Right((k, v)) for k, v in enumerate(vecs[:100])]
     out = transform_binary()(recs, 3, 3, PassiveAggressiveBinaryAlgorithm.build_pa_i(1.0), 10_000, n_feat, True,
                              10, engine=engine)
-    preds = {e.value[0]: e.value[1] for e in out if e.is_left}
-    if engine == "host":       # the host job identifies an unlabelled example by its vector
-        preds = {k: preds[v] for k, v in enumerate(vecs[:100]) if v in preds}
+    by_vec = {e.value[0]: e.value[1] for e in out if e.is_left}      # an unlabelled example is identified by its vector
+    preds = {k: by_vec[v] for k, v in enumerate(vecs[:100]) if v in by_vec}
     acc = np.mean([preds[k] == labels[k] for k in range(100)])
     assert acc >= 0.8, (engine, acc)
     assert len(last_write_wins(rights(out))) > 0
