@@ -89,7 +89,9 @@ __device__ __forceinline__ RowRef locate(const FpsTableView& t, long long id) {
 }
 
 __device__ __forceinline__ bool in_table(const FpsTableView& t, long long id, const RowRef& r) {
-  return id >= 0 && r.owner < t.n_shards && r.slot < t.rows_per_shard;
+  // n_ids, not just the shard capacity: with ceil-division padding the slots past the last id exist in
+  // memory but are not parameters (they were trained on and counted as valid before)
+  return id >= 0 && (t.n_ids <= 0 || id < t.n_ids) && r.owner < t.n_shards && r.slot < t.rows_per_shard;
 }
 
 // ---------------------------------------------------------------------------------------------

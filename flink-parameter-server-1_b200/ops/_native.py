@@ -39,6 +39,7 @@ class FpsTableView(C.Structure):
         ("replica_rows", C.c_void_p * FPS_MAX_SHARDS),
         ("n_replicas", C.c_int32),
         ("replica_rank", C.c_int32),
+        ("n_ids", C.c_int64),
     ]
 
 

@@ -91,6 +91,7 @@ class ShardedTable:
         v = self._view
         v.n_shards, v.dim, v.stride, v.partition = self.n_shards, self.dim, self.stride, self.partition
         v.div, v.rows_per_shard = self.div, self.rows_per_shard
+        v.n_ids = self.n_ids
         v.init_lo, v.init_hi = self.init_range
         v.seed, v.stream_tag, v.lazy = self.seed, self.stream_tag, int(self.lazy)
         n_state = ((self.rows_per_shard + 3) // 4) * 4

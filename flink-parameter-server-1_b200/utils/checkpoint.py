@@ -18,9 +18,10 @@ from ..entities import Left, Right, last_write_wins
 
 def fold(stream: Iterable) -> Tuple[Dict[int, np.ndarray], Dict[int, np.ndarray]]:
     """Last-write-wins per id for both halves of an output stream."""
-    lefts = last_write_wins(e.value for e in stream if e.is_left)
-    rights = last_write_wins(e.value for e in stream if e.is_right)
-    return lefts, rights
+    left_values, right_values = [], []
+    for e in stream:                      # one pass: `stream` may be a generator
+        (left_values if e.is_left else right_values).append(e.value)
+    return last_write_wins(left_values), last_write_wins(right_values)
 
 
 def write_id_value(path: str, vectors: Dict[int, Iterable[float]]) -> None:

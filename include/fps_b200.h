@@ -68,6 +68,7 @@ typedef struct FpsTableView {
   float*    replica_rows[FPS_MAX_SHARDS];
   int32_t   n_replicas;
   int32_t   replica_rank;            /* index of the local replica in replica_rows                */
+  int64_t   n_ids;                   /* ids are valid in [0, n_ids); 0 = only the shard capacity bounds them */
 } FpsTableView;
 
 /* Device-side flow control + observability block (one per worker; 256 B, zero it before use).

@@ -441,3 +441,16 @@ def test_negative_sampler_respects_user_memory_and_pool(native):
         m2.step(ou, oi, orr)
         s = m2.stats()
         assert s["bad_ids"] == 0 and s["records"] == int((ou != N.SKIP_ID).sum()), (variant, s)
+
+
+def test_ids_in_the_padding_of_the_last_shard_are_bad_ids(native):
+    """n_ids % n_shards != 0: the slots past the last id exist in memory but are not parameters."""
+    from fps_b200.ops.table import ShardedTable, new_flow, read_flow
+    for part in ("hash", "range"):
+        t = ShardedTable(10, 4, n_shards=3, partition=part, init_range=(1.0, 1.0))
+        flow = new_flow()
+        t.scatter(torch.tensor([9, 10, 11]), torch.ones(3, 4), "add", flow)
+        s = read_flow(flow)
+        assert s["bad_ids"] == 2 and s["pushes"] == 1, (part, s)
+        ids, _ = t.dump()
+        assert ids.tolist() == list(range(10))

@@ -113,3 +113,11 @@ def test_observability_reports():
                       "loss_sum": 25.0, "max_in_flight": 64}, link_row_bytes=512)
     assert fr["combine_ratio"] == 2.5 and fr["remote_fraction"] == 0.75 and fr["mean_loss"] == 0.25
     assert fr["nvlink_bytes_each_way"] == 30 * 512
+
+
+def test_fold_accepts_a_generator():
+    from fps_b200 import Left, Right
+    from fps_b200.utils.checkpoint import fold
+    stream = [Left((1, 1.0)), Right((7, 2.0)), Left((1, 3.0)), Right((8, 4.0))]
+    lefts_, rights_ = fold(iter(stream))
+    assert lefts_ == {1: 3.0} and rights_ == {7: 2.0, 8: 4.0}
