@@ -67,19 +67,20 @@ def config1(ctx):
     r = ((truth_u[u.long()] * truth_i[i.long()]).sum(1) * 0.1 + 0.6).clamp(0.2, 1.0).float()   # stars / 5
     out = {"config": 1, "what": "offline MF rank 10, ML-100K-shaped, 10 epochs", "ratings_per_job": n * epochs}
     if ctx.world_size == 1:
-        mf = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=0, seed=1, ctx=ctx, variant="direct")
+        mf = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=1600, seed=1, ctx=ctx, variant="auto")
         du, di, dr = u.cuda(), i.cuda(), r.cuda()
 
         def job():
             for _ in range(epochs):
                 mf.step(du, di, dr)
         ms = timed(job, 2, 5)
-        fresh = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=0, seed=1, ctx=ctx, variant="direct")
+        fresh = DeviceMF(nu, ni, dim, -0.01, 0.01, 0.01, pull_limit=1600, seed=1, ctx=ctx, variant="auto")
         for _ in range(epochs):
             fresh.step(du, di, dr)
         st = fresh.stats(check_nan=False)
         out.update(device_ms_per_job=ms, device_ratings_per_sec=n * epochs / ms * 1e3,
-                   rmse_after_10_epochs=fresh.rmse(du, di, dr), nan_count=st["nan_count"])
+                   rmse_after_10_epochs=fresh.rmse(du, di, dr), nan_count=st["nan_count"], pull_limit=1600,
+                   variant=fresh.variant, max_in_flight=st["max_in_flight"])
         # CPU restatement, W = PS = 4 (the reference's own parallelism for this config)
         W = S = 4
         per = n // W
@@ -112,7 +113,8 @@ def config2(ctx):
     # from stale reads; at lr 0.01 that diverges on 2+ GPUs (nan_count > 0 - and a diverged run looks fast
     # because non-finite updates are skipped), so the learning rate is the one that trains at every N
     lr = float(os.environ.get("FPS_CONFIG2_LR", "0.002"))
-    mf = DeviceMF(nu, ni, dim, -0.01, 0.01, lr, pull_limit=0, seed=2, ctx=ctx,
+    limit = int(os.environ.get("FPS_CONFIG2_PULL_LIMIT", "65536"))
+    mf = DeviceMF(nu, ni, dim, -0.01, 0.01, lr, pull_limit=limit, seed=2, ctx=ctx,
                   variant=os.environ.get("FPS_CONFIG2_VARIANT", "auto"))    # FPS_MF_REPLICATE_ITEMS=1: replicated item table
     g = torch.Generator().manual_seed(2 + rank)
     batches = []
@@ -129,7 +131,9 @@ def config2(ctx):
     st = mf.stats(check_nan=False)      # a diverged model would skip its updates and look fast: report it
     return {"config": 2, "what": "online MF rank 64, ML-20M-shaped stream", "n_gpus": W, "variant": mf.variant,
             "batch_per_gpu": B, "ms_per_step": ms, "ratings_per_sec": B * W / ms * 1e3,
-            "learning_rate": lr, "nan_count": st["nan_count"], "mse": st["loss_sum"] / max(st["records"], 1),
+            "learning_rate": lr, "pull_limit": limit, "max_in_flight": st["max_in_flight"],
+            "rows_pulled_per_record": st["pulls"] / max(st["records"], 1),
+            "nan_count": st["nan_count"], "mse": st["loss_sum"] / max(st["records"], 1),
             "items_table": "replicated" if mf.items.replicated else "sharded"}
 
 
@@ -150,9 +154,9 @@ def config3(ctx):
     g = torch.Generator().manual_seed(3 + ctx.rank)
     indptr, idx, val = _csr_batch(B, F, nnz, g, "cuda")
     lab = (torch.randint(0, 2, (B,), generator=g) * 2 - 1).int().cuda()
+    ms_unlimited = timed(lambda: pa.step(indptr, idx, val, lab), 3, 20)
+    pa.params.pull_limit = 10_000            # the config's title says "with pull limiter": this is the headline
     ms = timed(lambda: pa.step(indptr, idx, val, lab), 3, 20)
-    pa.params.pull_limit = 10_000
-    ms_lim = timed(lambda: pa.step(indptr, idx, val, lab), 2, 5)
     s = pa.stats()
     cpu = None
     if ctx.rank == 0:
@@ -164,7 +168,8 @@ def config3(ctx):
             "table": ("replicated, deferred delta exchange" if pa.table.deferred else
                       "replicated, multimem.red pushes" if pa.table.multicast else "replicated, red.add per replica")
             if pa.table.replicated else "sharded",
-            "with_pull_limit_10000": {"ms_per_step": ms_lim, "max_in_flight": s["max_in_flight"]}}
+            "pull_limit": 10_000, "max_in_flight": s["max_in_flight"],
+            "without_limiter": {"ms_per_step": ms_unlimited, "examples_per_sec": B * ctx.world_size / ms_unlimited * 1e3}}
 
 
 def config4(ctx):
@@ -176,9 +181,12 @@ def config4(ctx):
     g = torch.Generator().manual_seed(4 + ctx.rank)
     indptr, idx, val = _csr_batch(B, F, nnz, g, "cuda")
     lab = torch.randint(0, L, (B,), generator=g).int().cuda()
+    ms_unlimited = timed(lambda: pa.step(indptr, idx, val, lab), 3, 20)
+    pa.params.pull_limit = 10_000
     ms = timed(lambda: pa.step(indptr, idx, val, lab), 3, 20)
     rows = B * nnz * ctx.world_size
-    return {"config": 4, "what": "multiclass OVA PA-I, 100 classes, 1M features, 100 nnz", "n_gpus": ctx.world_size,
+    return {"config": 4, "pull_limit": 10_000, "max_in_flight": pa.stats()["max_in_flight"],
+            "without_limiter_ms_per_step": ms_unlimited, "what": "multiclass OVA PA-I, 100 classes, 1M features, 100 nnz", "n_gpus": ctx.world_size,
             "examples_per_gpu": B, "ms_per_step": ms, "examples_per_sec": B * ctx.world_size / ms * 1e3,
             "pull_rows_per_sec": rows / ms * 1e3, "push_rows_per_sec": rows / ms * 1e3,
             "row_bytes": L * 4, "gather_scatter_gbs": rows * L * 4 * 3 / ms / 1e6}
@@ -255,22 +263,32 @@ def config7(ctx):
     kw = dict(num_factors=10, range_min=-0.01, range_max=0.01, learning_rate=0.05, negative_sample_rate=9,
               K=100, worker_k=75, pull_limit=500)
     res = {"config": 7, "what": "prequential learner+generator, 69K events / 12.5K users / 19K items, rank 10, K=100, 9 negatives"}
-    for bs in (256, 2048):
+    ps_online_learner_and_generator_device(stream[:4096], n_users=n_users, n_items=n_items, batch_size=2048,
+                                           user_memory=128, **kw)          # warm-up (module load, allocator)
+    for bs in (256, 2048, 8192):
         torch.cuda.synchronize()
         t0 = time.time()
         out, lg = ps_online_learner_and_generator_device(stream, n_users=n_users, n_items=n_items, batch_size=bs,
                                                          user_memory=128, **kw)
         torch.cuda.synchronize()
         dt = time.time() - t0
-        sink = NDCGSink().consume(out[-20000:])
-        res[f"device_batch{bs}"] = {"events_per_sec": n_events / dt, "seconds": dt, "ndcg_last20k": sink.ndcg,
-                                    "hit_rate_last20k": sink.hit_rate}
+        s = lg.stats()
+        res[f"device_batch{bs}"] = {"events_per_sec": n_events / dt, "seconds": dt,
+                                    "ndcg_last20k": out.ndcg(n_events - 20000),
+                                    "hit_rate_last20k": out.hit_rate(n_events - 20000),
+                                    "sgd_records": s["records"], "nan_count": s["nan_count"],
+                                    "max_in_flight": s["max_in_flight"]}
     n_host = 3000
     t0 = time.time()
     out_h = ps_online_learner_and_generator(stream[:n_host], user_memory=128, worker_parallelism=4, ps_parallelism=4,
                                             iteration_wait_time=0, **kw)
     dt = time.time() - t0
-    res["host_engine_prefix"] = {"events": n_host, "events_per_sec": n_host / dt, "seconds": dt, "outputs": len(out_h)}
+    sink = NDCGSink().consume(out_h)
+    res["host_engine_prefix"] = {"events": n_host, "events_per_sec": n_host / dt, "seconds": dt, "outputs": len(out_h),
+                                 "ndcg": sink.ndcg, "hit_rate": sink.hit_rate}
+    dev_prefix, _ = ps_online_learner_and_generator_device(stream[:n_host], n_users=n_users, n_items=n_items,
+                                                           batch_size=64, user_memory=128, **kw)
+    res["device_same_prefix_batch64"] = {"ndcg": dev_prefix.ndcg(), "hit_rate": dev_prefix.hit_rate()}
     return res
 
 

@@ -362,7 +362,9 @@ struct TCarry {
   float* row;
   float4 v[VPL];
   float4 acc[VPL];
-  bool remote;
+  float4 back[VPL];     // long runs: the row as the last push-and-refresh found it (arrives asynchronously)
+  float4 sent[VPL];     // ... and the delta that push carried
+  bool remote, pending;
 };
 
 template <int LANES, int VPL>
@@ -381,10 +383,13 @@ __device__ __forceinline__ void tcarry_push(TCarry<LANES, VPL>& cy, int nvec, Ti
   }
 }
 
-// Long run: publish the delta gathered so far AND refresh the carried row in one round trip (the
-// add returns the previous value), so walkers on the same hot item feed back into each other every
-// TL_RUN_FLUSH records - without it the sum of many walkers' deltas, all computed from the same
-// stale row, overshoots (diverged on a 6 %-hot item at rank 16).
+// Long run: every TL_RUN_FLUSH records publish the delta gathered so far AND refresh the carried row
+// in the same round trip (the add returns the previous value), so walkers on the same hot item feed
+// back into each other - without it the sum of many walkers' deltas, all computed from the same stale
+// row, overshoots (diverged on a 6 %-hot item at rank 16).  The returned row is only consumed at the
+// NEXT flush point (v = returned + what that push carried + what was gathered since), so the warp
+// never waits for the round trip: feedback lags by one flush period instead of stalling the walker
+// (the blocking form cost 35 % on the rank-64 online config).
 template <int LANES, int VPL>
 __device__ __forceinline__ void tcarry_exchange(TCarry<LANES, VPL>& cy, int nvec, TileCounters& c) {
   const int lane = threadIdx.x % LANES;
@@ -392,12 +397,16 @@ __device__ __forceinline__ void tcarry_exchange(TCarry<LANES, VPL>& cy, int nvec
   for (int q = 0; q < VPL; ++q) {
     const int b = lane + q * LANES;
     if (b < nvec) {
-      const float4 o = atom_add4(cy.row + b * 4, cy.acc[q]);
-      cy.v[q].x = o.x + cy.acc[q].x; cy.v[q].y = o.y + cy.acc[q].y;
-      cy.v[q].z = o.z + cy.acc[q].z; cy.v[q].w = o.w + cy.acc[q].w;
+      if (cy.pending) {
+        cy.v[q].x = cy.back[q].x + cy.sent[q].x + cy.acc[q].x; cy.v[q].y = cy.back[q].y + cy.sent[q].y + cy.acc[q].y;
+        cy.v[q].z = cy.back[q].z + cy.sent[q].z + cy.acc[q].z; cy.v[q].w = cy.back[q].w + cy.sent[q].w + cy.acc[q].w;
+      }
+      cy.back[q] = atom_add4(cy.row + b * 4, cy.acc[q]);
     }
+    cy.sent[q] = cy.acc[q];
     cy.acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
+  cy.pending = true;
   cy.run_len = 0;
   if (lane == 0) {
     ++c.pushes; ++c.pulls;
@@ -479,6 +488,7 @@ k_mf_tiles_reg(const __grid_constant__ FpsTableView items, const __grid_constant
     cy.run_len = 0;
     cy.row = nullptr;
     cy.remote = false;
+    cy.pending = false;
 #pragma unroll
     for (int q = 0; q < VPL; ++q) cy.acc[q] = cy.v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
     // user row of the next record is loaded one iteration ahead (register double buffer)
@@ -521,6 +531,7 @@ k_mf_tiles_reg(const __grid_constant__ FpsTableView items, const __grid_constant
           cy.item = item;
           cy.row = pack_row(items, (unsigned int)rec.pad);
           cy.remote = (int)((unsigned int)rec.pad >> 28) != p.local_shard;
+          cy.pending = false;
           cy.run_len = 0;
 #pragma unroll
           for (int q = 0; q < VPL; ++q) {
@@ -632,6 +643,7 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
     cy.run_len = 0;
     cy.row = nullptr;
     cy.remote = false;
+    cy.pending = false;
     cy.acc[0] = cy.v[0] = make_float4(0.f, 0.f, 0.f, 0.f);
     int recent[TL_RU];                     // users of the last RU records (their stores may be newer than a prefetch)
 #pragma unroll
@@ -670,6 +682,7 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
                               : make_float4(0.f, 0.f, 0.f, 0.f);
         cy.acc[0] = make_float4(0.f, 0.f, 0.f, 0.f);
         cy.run_len = 0;
+        cy.pending = false;
         cy.remote = (int)((unsigned int)r.pad >> 28) != p.local_shard;
         if (lane == 0) {
           ++c.pulls;

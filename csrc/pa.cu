@@ -78,22 +78,23 @@ __global__ void __launch_bounds__(PA_THREADS)
 k_pa_binary(const __grid_constant__ FpsTableView t, const long long* __restrict__ indptr,
             const int* __restrict__ indices, const float* __restrict__ values,
             const int* __restrict__ labels, long long n, const FpsPaParams p, int* __restrict__ pred,
-            FpsFlow* flow) {
-  constexpr int WPB = PA_THREADS / 32;
+            int warps_active, int lanes_active, FpsFlow* flow) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   PaCounters c = {0.f, 0, 0, 0, 0, 0};
+  // Limiter (counted in features, like the reference's): an active warp has one weight load per
+  // active lane outstanding, so the CTA's allowance is warps_active * lanes_active, taken from the
+  // worker's pool once for the CTA's lifetime; the host sizes the grid so that all allowances fit.
+  // (The first version took min(limit, nnz of 8 examples) per pass: more loads than credits for long
+  // examples, and one CAS round trip per pass: 36x slower with the limiter on.)
+  const int WPB = warps_active;
+  const int credits = warps_active * lanes_active;
+  if (p.pull_limit > 0) flow_acquire(flow, credits, p.pull_limit);
   for (long long e0 = (long long)blockIdx.x * WPB; e0 < n; e0 += (long long)gridDim.x * WPB) {
-    const long long e1 = min(e0 + WPB, n);
-    int credits = 0;
-    if (p.pull_limit > 0) {   // limiter counts features (rows), like the reference's limiter
-      credits = (int)min((long long)p.pull_limit, indptr[e1] - indptr[e0]);
-      if (credits > 0) flow_acquire(flow, credits, p.pull_limit);
-    }
     const long long e = e0 + warp;
-    if (e < n) {
+    if (e < n && warp < WPB) {
       const long long b = indptr[e], end = indptr[e + 1];
       float m = 0.f, n2 = 0.f;
-      for (long long k = b + lane; k < end; k += 32) {
+      for (long long k = b + lane; k < end && lane < lanes_active; k += lanes_active) {
         const long long id = indices[k];
         const float x = values[k];
         const RowRef r = locate(t, id);
@@ -129,8 +130,8 @@ k_pa_binary(const __grid_constant__ FpsTableView t, const long long* __restrict_
         }
       }
     }
-    if (p.pull_limit > 0 && credits > 0) flow_release(flow, credits);
   }
+  if (p.pull_limit > 0) flow_release(flow, credits);
   pa_flush(c, flow);
 }
 
@@ -142,7 +143,7 @@ __global__ void __launch_bounds__(PA_THREADS)
 k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__ indptr,
            const int* __restrict__ indices, const float* __restrict__ values,
            const int* __restrict__ labels, long long n, const FpsPaParams p,
-           const float* __restrict__ cost, int* __restrict__ pred, FpsFlow* flow) {
+           const float* __restrict__ cost, int* __restrict__ pred, int warps_pulling, int pull_u, FpsFlow* flow) {
   constexpr int WPB = PA_THREADS / 32;
   extern __shared__ __align__(16) float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -153,13 +154,12 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
   __shared__ int s_q;
   __shared__ float s_tau;
   PaCounters c = {0.f, 0, 0, 0, 0, 0};
+  // Limiter: a pulling warp has pull_u feature rows outstanding, the CTA's allowance is warps_pulling *
+  // pull_u, taken once for the CTA's lifetime (grid sized by the host to fit the limit).
+  const int credits = warps_pulling * pull_u;
+  if (p.pull_limit > 0) flow_acquire(flow, credits, p.pull_limit);
   for (long long e = blockIdx.x; e < n; e += gridDim.x) {
     const long long b = indptr[e], end = indptr[e + 1];
-    int credits = 0;
-    if (p.pull_limit > 0) {
-      credits = (int)min((long long)p.pull_limit, end - b);
-      if (credits > 0) flow_acquire(flow, credits, p.pull_limit);
-    }
     // ---- pull + decision vector
     float n2 = 0.f;
     for (int v0 = 0; v0 < nvec; v0 += 32) {
@@ -168,7 +168,7 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
       // PULL_U features of this warp in flight at once: ids first, then all row loads, then the FMAs
       // (one feature per iteration left the warp waiting on a dependent id -> row load chain)
       constexpr int PULL_U = 2;
-      for (long long k0 = b + warp; k0 < end; k0 += WPB * PULL_U) {
+      for (long long k0 = b + warp; k0 < end && warp < warps_pulling; k0 += (long long)warps_pulling * PULL_U) {
         long long id[PULL_U];
         float x[PULL_U];
         RowRef r[PULL_U];
@@ -176,8 +176,8 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
         float4 w[PULL_U];
 #pragma unroll
         for (int u = 0; u < PULL_U; ++u) {
-          const long long k = k0 + (long long)u * WPB;
-          const bool have = k < end;
+          const long long k = k0 + (long long)u * warps_pulling;
+          const bool have = k < end && u < pull_u;
           id[u] = have ? (long long)indices[k] : 0;
           x[u] = have ? values[k] : 0.f;
           r[u] = locate(t, id[u]);
@@ -304,9 +304,9 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
         }
       }
     }
-    if (p.pull_limit > 0 && credits > 0) flow_release(flow, credits);
     __syncthreads();
   }
+  if (p.pull_limit > 0) flow_release(flow, credits);
   pa_flush(c, flow);
 }
 
@@ -331,10 +331,19 @@ extern "C" int fps_pa_step_cost(const FpsTableView* weights, const int64_t* d_in
   const int sms = fps_num_sms();
   if (params->multiclass == 0) {
     FPS_REQUIRE(weights->dim == 1, FPS_E_INVALID, "fps_pa_step: binary PA needs a dim-1 table");
+    int warps_active = PA_THREADS / 32, lanes_active = 32;
     long long blocks = (n_examples + 7) / 8;
     if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
+    if (params->pull_limit > 0) {
+      const long long limit = params->pull_limit;
+      if (limit < 32) { lanes_active = (int)limit; warps_active = 1; }
+      else if (limit < 32 * (PA_THREADS / 32)) warps_active = (int)(limit / 32);
+      const long long fit = limit / (warps_active * lanes_active);
+      if (fit < (long long)sms * 8 && blocks > fit) blocks = fit > 0 ? fit : 1;   // else: only resident CTAs hold credits
+    }
     k_pa_binary<<<(int)blocks, PA_THREADS, 0, st>>>(*weights, (const long long*)d_indptr, d_indices, d_values,
-                                                    d_labels, n_examples, *params, d_pred, d_flow);
+                                                    d_labels, n_examples, *params, d_pred, warps_active,
+                                                    lanes_active, d_flow);
   } else {
     FPS_REQUIRE(weights->stride % 4 == 0 && weights->dim == params->n_classes, FPS_E_INVALID,
                 "fps_pa_step: multiclass table must have dim == n_classes (%d vs %d)", weights->dim, params->n_classes);
@@ -343,8 +352,17 @@ extern "C" int fps_pa_step_cost(const FpsTableView* weights, const int64_t* d_in
     if (smem > 48 * 1024) FPS_CUDA(cudaFuncSetAttribute(k_pa_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long blocks = n_examples;
     if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
+    int warps_pulling = PA_THREADS / 32, pull_u = 2;
+    if (params->pull_limit > 0) {
+      const long long limit = params->pull_limit;
+      if (limit < 2) { pull_u = 1; warps_pulling = 1; }
+      else if (limit < 2 * (PA_THREADS / 32)) warps_pulling = (int)(limit / 2);
+      const long long fit = limit / (warps_pulling * pull_u);
+      if (fit < (long long)sms * 8 && blocks > fit) blocks = fit > 0 ? fit : 1;
+    }
     k_pa_multi<<<(int)blocks, PA_THREADS, smem, st>>>(*weights, (const long long*)d_indptr, d_indices, d_values,
-                                                      d_labels, n_examples, *params, d_cost, d_pred, d_flow);
+                                                      d_labels, n_examples, *params, d_cost, d_pred, warps_pulling,
+                                                      pull_u, d_flow);
   }
   FPS_LAUNCH_CHECK();
   return 0;

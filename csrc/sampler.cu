@@ -28,6 +28,7 @@ constexpr int NEG_MAX_RETRIES = 32;
 // index of the user's ring: its row in the worker-resident user table (local_shard >= 0: the one local
 // shard; -1: every shard is local, rings are laid out shard after shard), -1 for a user that is not ours
 __device__ __forceinline__ long long ring_of(const FpsTableView& users, const FpsNegSampler& s, int u) {
+  if (s.local_shard == -2) return (u >= 0 && u < s.n_rings) ? u : -1;   // one ring per user id (replicated memory)
   const RowRef ur = locate(users, u);
   if (!in_table(users, u, ur)) return -1;
   if (s.local_shard >= 0) return ur.owner == s.local_shard ? ur.slot : -1;
@@ -39,7 +40,7 @@ k_neg_register(const __grid_constant__ FpsTableView users, const FpsNegSampler s
                const int* __restrict__ iid, long long n) {
   for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
     const int u = uid[k], i = iid[k];
-    if (i < 0 || i >= s.n_items) continue;
+    if (u == FPS_SKIP_ID || i < 0 || i >= s.n_items) continue;
     const unsigned int bit = 1u << (i & 31);
     const unsigned int old = atomicOr(&s.item_bitmap[i >> 5], bit);
     if (!(old & bit)) s.item_pool[atomicAdd(s.pool_count, 1)] = i;
@@ -101,9 +102,61 @@ k_neg_draw(const __grid_constant__ FpsTableView users, const FpsNegSampler s, co
   }
 }
 
+// the merger's / worker's per-user memory when every rank sees every event: ring = user id
+__global__ void __launch_bounds__(256)
+k_ring_append(int* __restrict__ seen, int* __restrict__ seen_count, int user_memory, long long n_rings,
+              const int* __restrict__ uid, const int* __restrict__ iid, long long n) {
+  for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
+    const int u = uid[k];
+    if (u < 0 || u >= n_rings) continue;
+    const int pos = atomicAdd(&seen_count[u], 1);
+    seen[(long long)u * user_memory + pos % user_memory] = iid[k];
+  }
+}
+
+// an item becomes a top-K candidate with its first rating on the worker that owns it
+__global__ void __launch_bounds__(256)
+k_mark_live(const __grid_constant__ FpsTableView items, int local_shard, const int* __restrict__ uid,
+            const int* __restrict__ iid, long long n, int* __restrict__ live_ids) {
+  for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
+    if (uid[k] == FPS_SKIP_ID) continue;
+    const int i = iid[k];
+    const RowRef r = locate(items, i);
+    if (!in_table(items, i, r)) continue;
+    if (local_shard >= 0) {
+      if (r.owner == local_shard) live_ids[r.slot] = i;
+    } else {
+      live_ids[(long long)r.owner * items.rows_per_shard + r.slot] = i;
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" {
+
+int fps_seen_ring_append(int32_t* d_seen, int32_t* d_seen_count, int32_t user_memory, int64_t n_rings,
+                         const int32_t* d_user_ids, const int32_t* d_item_ids, int64_t n, void* stream) {
+  FPS_REQUIRE(d_seen && d_seen_count && user_memory > 0 && n_rings > 0, FPS_E_INVALID, "fps_seen_ring_append: bad arguments");
+  if (n <= 0) return 0;
+  long long b = (n + 255) / 256;
+  if (b > fps_num_sms() * 16) b = fps_num_sms() * 16;
+  k_ring_append<<<(int)b, 256, 0, (cudaStream_t)stream>>>(d_seen, d_seen_count, user_memory, n_rings, d_user_ids, d_item_ids, n);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int fps_mark_live_items(const FpsTableView* items, int32_t local_shard, const int32_t* d_user_ids,
+                        const int32_t* d_item_ids, int64_t n, int32_t* d_live_ids, void* stream) {
+  if (int e = fps_check_view(items, "fps_mark_live_items")) return e;
+  FPS_REQUIRE(d_live_ids != nullptr, FPS_E_INVALID, "fps_mark_live_items: live_ids is required");
+  if (n <= 0) return 0;
+  long long b = (n + 255) / 256;
+  if (b > fps_num_sms() * 16) b = fps_num_sms() * 16;
+  k_mark_live<<<(int)b, 256, 0, (cudaStream_t)stream>>>(*items, local_shard, d_user_ids, d_item_ids, n, d_live_ids);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
 
 int fps_mf_sample_negatives(const FpsTableView* users, const FpsNegSampler* sampler, const int32_t* d_user_ids,
                             const int32_t* d_item_ids, const float* d_ratings, int64_t n, uint64_t step_tag,

@@ -25,7 +25,12 @@ __global__ void __launch_bounds__(TK_THREADS, 1)
 k_lemp_topk(const float* __restrict__ queries, int q_stride, long long n_q,
             const float* __restrict__ items, int item_stride, const float* __restrict__ item_len,
             const int* __restrict__ item_ids, long long n_items, int dim, int kblks, int k, int n_splits,
-            int use_pruning, TopkScratch sc, unsigned long long* __restrict__ stats) {
+            int flags, TopkScratch sc, unsigned long long* __restrict__ stats) {
+  // flags: bit 0 = LEMP LENGTH pruning (items sorted by length), bit 1 = items whose id is negative are not
+  // candidates (a live-item mask for tables scored in place)
+  const int use_pruning = flags & 1;
+  const bool mask_dead = (flags & 2) != 0 && item_ids != nullptr;
+  __shared__ int s_live[TK_N];
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by SWIZZLE_128B; dynamic smem base is only 16-byte aligned
   uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -90,6 +95,7 @@ k_lemp_topk(const float* __restrict__ queries, int q_stride, long long n_q,
       if (__syncthreads_and(can_skip)) break;
     }
     // ---- stage the item tile
+    if (mask_dead && t < TK_N) s_live[t] = t < i_valid ? item_ids[i0 + t] : -1;
     stage_tile<TC>(sB_hi, sB_lo, items + i0 * item_stride, item_stride, TK_N, i_valid, dim, kblks);
     float sc_row[TK_N];
     if (TC) {
@@ -142,7 +148,7 @@ k_lemp_topk(const float* __restrict__ queries, int q_stride, long long n_q,
     if (t < q_valid) {
 #pragma unroll
       for (int j = 0; j < TK_N; ++j) {
-        if (j < i_valid && sc_row[j] > theta) {
+        if (j < i_valid && sc_row[j] > theta && (!mask_dead || s_live[j] >= 0)) {
           cs[cnt * TK_M] = sc_row[j];
           ci[cnt * TK_M] = (int)(i0 + j);
           ++cnt;
@@ -201,7 +207,7 @@ int run_topk(const float* d_queries, int q_stride, long long n_q, const float* d
   FPS_REQUIRE(k >= 1 && k <= TK_MAX_K, FPS_E_TOO_LARGE, "topk: k = %d outside [1, %d]", k, TK_MAX_K);
   FPS_REQUIRE(dim <= 128, FPS_E_UNSUPPORTED, "topk: rank %d > 128 not supported by the tile kernel", dim);
   FPS_REQUIRE(q_stride % 4 == 0 && item_stride % 4 == 0, FPS_E_INVALID, "topk: strides must be multiples of 4 floats");
-  FPS_REQUIRE(!use_pruning || d_item_len != nullptr, FPS_E_INVALID, "topk: pruning needs item lengths");
+  FPS_REQUIRE(!(use_pruning & 1) || d_item_len != nullptr, FPS_E_INVALID, "topk: pruning needs item lengths");
   const Plan p = make_plan(n_q, k, n_items, dim);
   FPS_REQUIRE(scratch_bytes >= p.total, FPS_E_INVALID, "topk: scratch too small (%zu < %zu)", scratch_bytes, p.total);
   uint8_t* sb = (uint8_t*)d_scratch;

@@ -26,7 +26,9 @@ import numpy as np
 from ...ops import _native as N
 from ...ops import philox
 from ...ops.table import ShardedTable, new_flow, read_flow
-from ...ops.topk import PackedItems, lemp_topk, lemp_topk_packed, sort_items_by_length, topk_merge
+from ...ops.topk import (PackedItems, lemp_topk, lemp_topk_packed, lemp_topk_table, sort_items_by_length,
+                         topk_merge)
+from ...utils.observability import nvtx_range
 
 
 class _LocalItems:
@@ -169,104 +171,187 @@ class DeviceTopK:
         return out
 
 
+class PrequentialOutput:
+    """The output of the prequential job kept as arrays (``scores`` / ``ids`` ``[n, K]``, ``-1`` = no
+    item) and turned into the reference's records ``(user, item, timestamp, [(score, item), ...])``
+    only when somebody indexes or iterates it - building 100-entry Python lists for every event was
+    what bound the first device version to 30 K events/s."""
+
+    def __init__(self, users, items, timestamps, scores, ids):
+        self.users, self.items, self.timestamps, self.scores, self.ids = users, items, timestamps, scores, ids
+
+    def __len__(self) -> int:
+        return len(self.users)
+
+    def _one(self, r: int):
+        keep = self.ids[r] >= 0
+        return (int(self.users[r]), int(self.items[r]), self.timestamps[r],
+                list(zip(self.scores[r][keep].tolist(), self.ids[r][keep].tolist())))
+
+    def __getitem__(self, key):
+        if isinstance(key, slice):
+            return [self._one(r) for r in range(*key.indices(len(self)))]
+        return self._one(key if key >= 0 else len(self) + key)
+
+    def __iter__(self):
+        return (self._one(r) for r in range(len(self)))
+
+    def ranks(self) -> np.ndarray:
+        """1-based rank of the consumed item in its top-K list, 0 = not recommended (``nDCGSink``)."""
+        hit = self.ids == self.items[:, None]
+        return np.where(hit.any(axis=1), hit.argmax(axis=1) + 1, 0)
+
+    def ndcg(self, start: int = 0) -> float:
+        r = self.ranks()[start:]
+        return float(np.where(r > 0, np.log(2.0) / np.log(1.0 + np.maximum(r, 1)), 0.0).mean()) if len(r) else 0.0
+
+    def hit_rate(self, start: int = 0) -> float:
+        r = self.ranks()[start:]
+        return float((r > 0).mean()) if len(r) else 0.0
+
+
 class DeviceLearnerGenerator:
-    """Prequential recommend-then-learn in mini-batches: the whole batch is answered with the
-    model as of the batch start (asynchronous semantics: reads may be stale by up to one batch),
-    then learnt."""
+    """Prequential recommend-then-learn (N8) as a fixed sequence of kernels per micro-batch with no
+    host round trip in between: the whole batch is answered with the model as of the batch start
+    (asynchronous semantics: reads may be stale by up to one batch), then learnt.
+
+      recommend   pull of the batch's user rows (P2P gather) -> tcgen05 scoring of this worker's item
+                  table *in place* (live-item mask; catalogues up to ``dense_catalog`` rows - beyond that
+                  the length-sorted, packed snapshot with LEMP pruning, refreshed every
+                  ``refresh_every`` batches) -> all-gather of the partial lists (X8) -> merge with
+                  the per-user seen filter read from the device ring
+      learn       only for events whose item this worker owns (``:128``): the item becomes live, its
+                  negatives are drawn by the device sampler from this worker's live items and
+                  rejected against the user's ring (``:143-156``), then one fused SGD launch with the
+                  tables swapped - the pulled / pushed row is the *user's* (PS side), the row updated
+                  in place is the local *item's* (``:150-163``)
+
+    The user's recent-items memory is one device ring per user id on every rank (all ranks see all
+    events), shared by the merge filter and the sampler; memories longer than ``max_ring`` are cut."""
 
     def __init__(self, n_users: int, n_items: int, num_factors: int = 10, range_min: float = -0.001,
                  range_max: float = 0.001, learning_rate: float = 0.01, negative_sample_rate: int = 0,
                  user_memory: int = 65535, K: int = 100, worker_k: int = 75, pull_limit: int = 500,
-                 seed: int = 0, use_pruning: bool = True, ctx=None):
+                 seed: int = 0, use_pruning: bool = True, ctx=None, dense_catalog: int = 1 << 18,
+                 refresh_every: int = 8, max_ring: int = 512):
         import torch
         from ...parallel.device_context import get_context
         self.ctx = ctx or get_context()
         W = self.ctx.world_size
+        self.n_users, self.n_items = n_users, n_items
         self.K, self.worker_k, self.dim = K, min(worker_k, 128), num_factors
         self.negative_sample_rate, self.use_pruning = negative_sample_rate, use_pruning
         self.users = ShardedTable(n_users, num_factors, partition="hash", init_range=(range_min, range_max),
                                   seed=seed, stream_tag=philox.STREAM_USER, ctx=self.ctx)
-        # worker-resident items, lazily created by their first rating (only rated items are candidates)
+        # worker-resident items: every row holds init(id) from the start, but an item only becomes a
+        # candidate (live) with its first rating
         self.items = ShardedTable(n_items, num_factors, partition="hash", init_range=(range_min, range_max),
-                                  seed=seed, stream_tag=philox.STREAM_ITEM, lazy=True, ctx=self.ctx,
+                                  seed=seed, stream_tag=philox.STREAM_ITEM, lazy=False, ctx=self.ctx,
                                   local_only=True)
+        self._shard = self.ctx.rank if self.ctx.distributed else 0
+        if not self.ctx.distributed and self.items.n_shards != 1:
+            raise ValueError("one local item shard per process")
+        self.live_ids = torch.full((self.items.rows_per_shard,), -1, device="cuda", dtype=torch.int32)
         self.params = N.FpsMfParams()
         self.params.lr, self.params.lambda_ = learning_rate, 0.0
         self.params.pull_limit = int(pull_limit)
         self.params.local_shard = self.ctx.rank if self.ctx.distributed else -1
         self.flow = new_flow()
+        # per-user ring on every rank + this worker's pool of live items
+        self.mem = max(1, min(int(user_memory) if user_memory > 0 else max_ring, max_ring))
+        self._seen = torch.full((n_users * self.mem,), -1, device="cuda", dtype=torch.int32)
+        self._seen_count = torch.zeros(n_users, device="cuda", dtype=torch.int32)
+        self._bitmap = torch.zeros((n_items + 31) // 32, device="cuda", dtype=torch.int32)
+        self._pool = torch.zeros(n_items, device="cuda", dtype=torch.int32)
+        self._pool_count = torch.zeros(1, device="cuda", dtype=torch.int32)
+        st = N.FpsNegSampler()
+        st.seen, st.seen_count = self._seen.data_ptr(), self._seen_count.data_ptr()
+        st.item_bitmap, st.item_pool, st.pool_count = self._bitmap.data_ptr(), self._pool.data_ptr(), self._pool_count.data_ptr()
+        st.n_items, st.seed = n_items, (seed * 0x9E3779B97F4A7C15 + 977 * (self.ctx.rank + 1)) & (2 ** 64 - 1)
+        st.user_memory, st.rate, st.local_shard, st.n_rings = self.mem, int(negative_sample_rate), -2, n_users
+        self._sampler = st
+        self._tag = 0
+        self.dense = self.items.rows_per_shard <= dense_catalog and num_factors <= 128
+        self.refresh_every = max(1, int(refresh_every))
         self.local = _LocalItems()
-        self.seen = _SeenMemory(user_memory)
-        self._np_rng = np.random.default_rng(seed * 977 + self.ctx.rank)
-        self._dirty = False
+        self._since_refresh = 1 << 30
+        self._scratch = None
+        self._skip = torch.tensor(N.SKIP_ID, device="cuda", dtype=torch.int32)
+        self.batches = 0
 
-    def _refresh_items(self) -> None:
-        if self._dirty or self.local.empty:
-            ids, rows = self.items.dump()
-            self.local.refresh(ids, rows[:, : self.dim])
-            self._dirty = False
+    # -- recommend ---------------------------------------------------------------------------------
+    def _local_topk(self, q):
+        import torch
+        n_q = q.shape[0]
+        if self.dense:
+            rows = self.items.rows[self._shard]
+            ls, li, self._scratch = lemp_topk_table(q, rows, self.dim, self.worker_k, self.live_ids, scratch=self._scratch)
+            return ls, li
+        # large catalogue: length-sorted packed snapshot, refreshed every few batches
+        if self._since_refresh >= self.refresh_every:
+            live = torch.nonzero(self.live_ids >= 0).flatten()
+            self.local.refresh(self.live_ids[live], self.items.rows[self._shard][live][:, : self.dim])
+            self._since_refresh = 0
+        self._since_refresh += 1
+        if self.local.empty:
+            return (torch.full((n_q, self.worker_k), -float("inf"), device="cuda"),
+                    torch.full((n_q, self.worker_k), -1, device="cuda", dtype=torch.int32))
+        return self.local.topk(q, self.worker_k, self.use_pruning)
+
+    def step_tensors(self, users, items, ratings):
+        """``users`` / ``items`` int32, ``ratings`` fp32 device tensors - the same batch on every rank.
+        Returns ``(scores, ids)`` ``[n, K]`` device tensors; nothing here synchronises with the host."""
+        import torch
+        W, rank = self.ctx.world_size, self.ctx.rank
+        n = users.numel()
+        with nvtx_range("fps.learner_generator.step"):
+            uid = users.long()
+            q = self.users.gather(uid)[:, : self.dim].contiguous()
+            ls, li = self._local_topk(q)
+            ps, pi = _all_gather_parts(self.ctx, ls, li)
+            seen = self._seen.view(self.n_users, self.mem)[uid]
+            out_s, out_i = topk_merge(ps, pi, min(self.K, ps.shape[1] * ps.shape[2]), seen)
+            # ---- learn (item owner only); the rings take every event
+            owned = (items % W) == rank if W > 1 else None
+            u_own = users if owned is None else torch.where(owned, users, self._skip)
+            if owned is not None:
+                u_other = torch.where(owned, torch.full_like(users, -1), users)
+                N.check(N.lib().fps_seen_ring_append(N.ptr(self._seen), N.ptr(self._seen_count), self.mem, self.n_users,
+                                                     N.ptr(u_other), N.ptr(items), n, N.current_stream()),
+                        "fps_seen_ring_append")
+            N.check(N.lib().fps_mark_live_items(self.items.view_ref(), self.params.local_shard if W > 1 else 0,
+                                                N.ptr(u_own), N.ptr(items), n, N.ptr(self.live_ids),
+                                                N.current_stream()), "fps_mark_live_items")
+            m = n * (self.negative_sample_rate + 1)
+            ou = torch.empty(m, device="cuda", dtype=torch.int32)
+            oi = torch.empty(m, device="cuda", dtype=torch.int32)
+            orr = torch.empty(m, device="cuda", dtype=torch.float32)
+            self._tag += 1
+            N.check(N.lib().fps_mf_sample_negatives(self.users.view_ref(), C.byref(self._sampler), N.ptr(u_own),
+                                                    N.ptr(items), N.ptr(ratings), n, self._tag, N.ptr(ou), N.ptr(oi),
+                                                    N.ptr(orr), N.current_stream()), "fps_mf_sample_negatives")
+            # tables swapped: the kernel's "item" operand = PS-side users (pulled / pushed remotely), its
+            # "user" operand = worker-resident items (updated in place) - so the skip marker goes with the items
+            skipped = ou == self._skip
+            wi = torch.where(skipped, self._skip, oi)
+            wu = torch.where(skipped, torch.zeros_like(ou), ou)
+            N.check(N.lib().fps_mf_sgd_step(self.users.view_ref(), self.items.view_ref(), N.ptr(wi), N.ptr(wu),
+                                            N.ptr(orr), m, C.byref(self.params), N.ptr(self.flow),
+                                            N.current_stream()), "fps_mf_sgd_step (learner)")
+        self.batches += 1
+        return out_s, out_i
 
     def step(self, ratings) -> list:
         """``ratings``: list of ``Rating`` (same list on every rank).  Returns
         ``[(user, item, timestamp, [(score, item), ...]), ...]`` for the batch."""
         import torch
-        W, rank = self.ctx.world_size, self.ctx.rank
-        users = [r.user for r in ratings]
-        # ---- recommend with the current model
-        self._refresh_items()
-        uid = torch.tensor(users, dtype=torch.int64)
-        q = self.users.gather(uid)[:, : self.dim].contiguous()
-        n_q = len(users)
-        if self.local.empty:
-            ls = torch.full((n_q, self.worker_k), -float("inf"), device="cuda")
-            li = torch.full((n_q, self.worker_k), -1, device="cuda", dtype=torch.int32)
-        else:
-            ls, li = self.local.topk(q, self.worker_k, self.use_pruning)
-        ps, pi = _all_gather_parts(self.ctx, ls, li)
-        out_s, out_i = topk_merge(ps, pi, min(self.K, ps.shape[1] * ps.shape[2]), self.seen.matrix(users))
-        s_np, i_np = out_s.cpu().numpy(), out_i.cpu().numpy()
-        out = []
-        for row, r in enumerate(ratings):
-            out.append((r.user, r.item, r.timestamp,
-                        [(float(a), int(b)) for a, b in zip(s_np[row], i_np[row]) if b >= 0]))
-            self.seen.add(r.user, r.item)
-        # ---- learn: only the owner of the rated item (item % W == rank)
-        mine = [r for r in ratings if r.item % W == rank]
-        if mine:
-            u = torch.tensor([r.user for r in mine], dtype=torch.int32)
-            it = torch.tensor([r.item for r in mine], dtype=torch.int32)
-            rt = torch.tensor([r.rating for r in mine], dtype=torch.float32)
-            if self.negative_sample_rate > 0 and not self.local.empty:
-                # negatives are drawn from this worker's live items (rating 0) and retried against the
-                # user's seen set like the reference (":145-149", which retries up to 32 times; here 8)
-                # (drawn in one vectorised call: 8 candidates per wanted negative, first unseen one wins;
-                # the per-draw retry loop was the slowest part of a step)
-                pool = self.local.ids.cpu().numpy()
-                neg_u, neg_i = [], []
-                rate = self.negative_sample_rate
-                cand = pool[self._np_rng.integers(0, len(pool), size=(len(mine), rate, 8))]
-                for row, r in enumerate(mine):
-                    seen = self.seen.sets.get(r.user, ())
-                    for j in range(min(rate, max(len(pool) - len(seen), 0))):
-                        for c in cand[row, j]:
-                            if int(c) not in seen:
-                                neg_u.append(r.user)
-                                neg_i.append(int(c))
-                                break
-                if neg_u:
-                    u = torch.cat([torch.tensor(neg_u, dtype=torch.int32), u])
-                    it = torch.cat([torch.tensor(neg_i, dtype=torch.int32), it])
-                    rt = torch.cat([torch.zeros(len(neg_u)), rt])
-            u, it, rt = u.cuda(), it.cuda(), rt.cuda()
-            # tables swapped: "items" operand = PS-side users (pulled / pushed remotely),
-            # "users" operand = worker-resident items (updated in place)
-            N.check(N.lib().fps_mf_sgd_step(self.users.view_ref(), self.items.view_ref(), N.ptr(it), N.ptr(u),
-                                            N.ptr(rt), u.numel(), C.byref(self.params), N.ptr(self.flow),
-                                            N.current_stream()), "fps_mf_sgd_step (learner)")
-            self._dirty = True
-        torch.cuda.synchronize()
-        self.ctx.barrier()
-        return out
+        u = torch.tensor([r.user for r in ratings], dtype=torch.int32).cuda()
+        i = torch.tensor([r.item for r in ratings], dtype=torch.int32).cuda()
+        v = torch.tensor([r.rating for r in ratings], dtype=torch.float32).cuda()
+        s, ids = self.step_tensors(u, i, v)
+        out = PrequentialOutput(np.array([r.user for r in ratings]), np.array([r.item for r in ratings]),
+                                [r.timestamp for r in ratings], s.cpu().numpy(), ids.cpu().numpy())
+        return out[:]
 
     def stats(self) -> dict:
         return read_flow(self.flow)
@@ -286,14 +371,26 @@ def ps_top_k_generator_device(src, model, num_factors: int = 10, user_memory: in
 
 
 def ps_online_learner_and_generator_device(src, n_users: int, n_items: int, batch_size: int = 256, **kw):
-    """Device twin of ``ps_online_learner_and_generator`` (mini-batched prequential loop)."""
+    """Device twin of ``ps_online_learner_and_generator`` (mini-batched prequential loop).  Returns
+    ``(PrequentialOutput, DeviceLearnerGenerator)``; the output behaves like the reference's list of
+    ``(user, item, timestamp, topK)`` records and also offers vectorised ``ndcg()`` / ``hit_rate()``."""
+    import torch
     lg = DeviceLearnerGenerator(n_users, n_items, **kw)
-    out, buf = [], []
-    for r in src:
-        buf.append(r)
-        if len(buf) >= batch_size:
-            out.extend(lg.step(buf))
-            buf = []
-    if buf:
-        out.extend(lg.step(buf))
-    return out, lg
+    ratings = src if isinstance(src, list) else list(src)
+    n = len(ratings)
+    u = np.fromiter((r.user for r in ratings), dtype=np.int32, count=n)
+    i = np.fromiter((r.item for r in ratings), dtype=np.int32, count=n)
+    v = np.fromiter((r.rating for r in ratings), dtype=np.float32, count=n)
+    ts = [r.timestamp for r in ratings]
+    du, di, dv = (torch.from_numpy(x).cuda() for x in (u, i, v))
+    parts = []
+    for s in range(0, n, batch_size):
+        parts.append(lg.step_tensors(du[s:s + batch_size], di[s:s + batch_size], dv[s:s + batch_size]))
+    if parts:
+        scores = torch.cat([p[0] for p in parts]).cpu().numpy()
+        ids = torch.cat([p[1] for p in parts]).cpu().numpy()
+    else:
+        scores, ids = np.zeros((0, lg.K), np.float32), np.zeros((0, lg.K), np.int32)
+    torch.cuda.synchronize()
+    lg.ctx.barrier()
+    return PrequentialOutput(u, i, ts, scores, ids), lg

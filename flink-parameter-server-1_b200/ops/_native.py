@@ -97,6 +97,7 @@ class FpsNegSampler(C.Structure):
         ("rate", C.c_int32),
         ("local_shard", C.c_int32),
         ("reserved", C.c_int32),
+        ("n_rings", C.c_int64),
     ]
 
 
@@ -161,6 +162,8 @@ def lib() -> C.CDLL:
         "fps_mf_sgd_step": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, vp, i64, P(FpsMfParams), vp, vp]),
         "fps_mf_predict": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, i64, vp, vp]),
         "fps_mf_sample_negatives": (C.c_int, [P(FpsTableView), P(FpsNegSampler), vp, vp, vp, i64, u64, vp, vp, vp, vp]),
+        "fps_seen_ring_append": (C.c_int, [vp, vp, i32, i64, vp, vp, i64, vp]),
+        "fps_mark_live_items": (C.c_int, [P(FpsTableView), i32, vp, vp, i64, vp, vp]),
         "fps_mf_tiles_scratch_bytes": (C.c_size_t, [i64]),
         "fps_mf_bucket": (C.c_int, [vp, vp, vp, i64, vp, C.c_size_t, vp]),
         "fps_mf_sgd_tiles": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, i64, P(FpsMfParams), vp, vp]),

@@ -128,3 +128,23 @@ def topk_merge(part_scores, part_ids, k_out: int, seen=None):
     N.check(N.lib().fps_topk_merge(N.ptr(ps), N.ptr(pi), n_parts, n_q, k_in, k_out, N.ptr(seen), seen_stride,
                                    N.ptr(out_s), N.ptr(out_i), N.current_stream()), "fps_topk_merge")
     return out_s, out_i
+
+
+def lemp_topk_table(queries, table_rows, dim: int, k: int, live_ids, *, scratch=None):
+    """Top-``k`` of every query against a worker-resident table scored *in place*: ``table_rows`` is the
+    shard's ``[rows, stride]`` tensor, ``live_ids[slot]`` the id of the item living in that slot or a
+    negative number for a slot that is not a candidate (masked inside the kernel).  No length order,
+    hence no LENGTH pruning: for catalogues small enough that a dump + sort + pack per model refresh
+    would cost more than scoring every tile."""
+    import torch
+    q = _pad4(queries.float())
+    n_q, n_items = q.shape[0], table_rows.shape[0]
+    need = scratch_bytes(n_q, k, n_items)
+    if scratch is None or scratch.numel() < need:
+        scratch = torch.empty(need, device="cuda", dtype=torch.uint8)
+    out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
+    out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
+    N.check(N.lib().fps_lemp_topk(N.ptr(q), q.shape[1], n_q, N.ptr(table_rows), table_rows.shape[1], None,
+                                  N.ptr(live_ids), n_items, dim, k, 2, N.ptr(scratch), scratch.numel(),
+                                  N.ptr(out_s), N.ptr(out_i), None, N.current_stream()), "fps_lemp_topk (in place)")
+    return out_s, out_i, scratch

@@ -196,6 +196,17 @@ int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const fl
 int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, void* d_scratch, int64_t n,
                      const FpsMfParams* params, FpsFlow* d_flow, void* stream);
 
+/* Appends (user, item) to per-user-id rings of user_memory entries (the seen filter of
+ * CollectTopKFromEachWorker.scala:50-55 kept on the device; same layout as FpsNegSampler.seen).         */
+int fps_seen_ring_append(int32_t* d_seen, int32_t* d_seen_count, int32_t user_memory, int64_t n_rings,
+                         const int32_t* d_user_ids, const int32_t* d_item_ids, int64_t n, void* stream);
+/* live_ids[slot of item in the local shard(s)] = item id for every record whose item this worker owns
+ * (local_shard >= 0: that shard; -1: all shards, laid out shard after shard) and whose user id is not
+ * FPS_SKIP_ID: an item becomes a top-K candidate with its first rating
+ * (PSOnlineMatrixFactorizationAndTopKGeneratorWorker.scala:169-187).                                   */
+int fps_mark_live_items(const FpsTableView* items, int32_t local_shard, const int32_t* d_user_ids,
+                        const int32_t* d_item_ids, int64_t n, int32_t* d_live_ids, void* stream);
+
 /* ---- negative sampling on the device (K4) ------------------------------------------------------ */
 /* A record whose user id is FPS_SKIP_ID is passed over by every MF kernel without being counted.   */
 #define FPS_SKIP_ID (-2147483647 - 1)
@@ -216,8 +227,11 @@ typedef struct FpsNegSampler {
   uint64_t  seed;
   int32_t   user_memory;     /* userMemory of the reference (default 128)                           */
   int32_t   rate;            /* negativeSampleRate                                                  */
-  int32_t   local_shard;     /* shard of the user table that lives here, -1 = all of them           */
+  int32_t   local_shard;     /* shard of the user table that lives here, -1 = all of them, -2 = rings
+                                are indexed by the user id itself (n_rings of them; a memory kept on
+                                every rank, as in the learner+generator job where all ranks see all events) */
   int32_t   reserved;
+  int64_t   n_rings;         /* local_shard == -2 only                                              */
 } FpsNegSampler;
 /* Registers the n positive ratings (item -> the user's recent-items ring and the worker's item pool),
  * then writes the expanded batch of n * (rate + 1) records: slot d * n + k holds negative d of rating k
@@ -275,7 +289,9 @@ int fps_pa_step_cost(const FpsTableView* weights, const int64_t* d_indptr, const
  * Partial top-k lists per (query, item-split) go to caller-provided scratch, then are merged.
  * Outputs: d_out_scores/d_out_ids [n_q, k] sorted descending, ids are d_item_ids[slot] or the
  * slot itself when d_item_ids is NULL; unused entries have id -1.
- * scratch_bytes must be >= fps_topk_scratch_bytes(n_q, k, n_items).                               */
+ * scratch_bytes must be >= fps_topk_scratch_bytes(n_q, k, n_items).
+ * use_pruning: bit 0 = the LENGTH bound; bit 1 = items whose d_item_ids entry is negative are skipped
+ * (scoring a worker-resident table in place, where not every slot is a live item).                 */
 size_t fps_topk_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items);
 int fps_lemp_topk(const float* d_queries, int32_t q_stride, int64_t n_q,
                   const float* d_items, int32_t item_stride, const float* d_item_len,

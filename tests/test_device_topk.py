@@ -132,3 +132,29 @@ def test_merge_with_seen_filter():
     torch.testing.assert_close(out_s, ref_v)
     assert torch.equal(out_i.long(), torch.gather(ids.long(), 1, ref_idx))
     assert not (out_i == seen[:, :1]).any()
+
+
+def test_in_place_table_scoring_masks_dead_slots():
+    """``lemp_topk_table``: the worker-resident table is scored where it lies; slots whose live id is
+    negative never appear, whatever their score."""
+    from fps_b200.ops.topk import lemp_topk_table
+    g = torch.Generator(device="cuda").manual_seed(11)
+    n_rows, stride, dim, k = 5000, 12, 10, 20
+    table = torch.randn(n_rows, stride, device="cuda", generator=g)
+    table[:, dim:] = 7.0                                   # padding columns must not contribute
+    live = torch.arange(n_rows, device="cuda", dtype=torch.int32) * 3 + 1      # slot -> id
+    dead = torch.rand(n_rows, device="cuda", generator=g) < 0.4
+    live[dead] = -1
+    table[dead] *= 50.0                                    # dead slots would win every query if scored
+    q = torch.randn(300, dim, device="cuda", generator=g)
+    s, ids, _ = lemp_topk_table(q, table, dim, k, live)
+    ref = q.double() @ table[:, :dim].double().T
+    ref[:, dead] = -float("inf")
+    want_s, want_slot = ref.topk(k, dim=1)
+    torch.testing.assert_close(s.double(), want_s, rtol=2e-5, atol=2e-5)
+    assert (ids >= 0).all()
+    same = (ids.long() == live[want_slot].long()).float().mean().item()
+    assert same > 0.99, same
+    # nothing live at all -> empty lists
+    s0, i0, _ = lemp_topk_table(q, table, dim, k, torch.full_like(live, -1))
+    assert (i0 == -1).all() and torch.isinf(s0).all()
