@@ -153,7 +153,7 @@ k_scatter(const __grid_constant__ FpsTableView t, const long long* __restrict__ 
 }
 
 __global__ void __launch_bounds__(256)
-k_dump_shard(const __grid_constant__ FpsTableView t, int shard, long long n_rows, long long n_ids_total,
+k_dump_shard(const __grid_constant__ FpsTableView t, int shard, long long row_begin, long long n_rows, long long n_ids_total,
              long long* __restrict__ out_ids, float* __restrict__ out_rows, long long capacity,
              unsigned long long* count) {
   // one warp per row: lane 0 claims an output slot (warp-aggregated per block would save little:
@@ -162,7 +162,7 @@ k_dump_shard(const __grid_constant__ FpsTableView t, int shard, long long n_rows
   const long long warps = (long long)gridDim.x * (blockDim.x / 32);
   const int nvec = t.stride / 4;
   const float* base = t.rows[shard];
-  for (long long slot = (long long)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32; slot < n_rows; slot += warps) {
+  for (long long slot = row_begin + (long long)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32; slot < n_rows; slot += warps) {
     const long long id = slot_to_id(t, shard, slot);
     if (id >= n_ids_total) continue;
     int state = FPS_ROW_PUSHED;
@@ -249,11 +249,11 @@ k_scatter_scalar(const __grid_constant__ FpsTableView t, const long long* __rest
 }
 
 __global__ void __launch_bounds__(256)
-k_dump_shard_scalar(const __grid_constant__ FpsTableView t, int shard, long long n_rows, long long n_ids_total,
+k_dump_shard_scalar(const __grid_constant__ FpsTableView t, int shard, long long row_begin, long long n_rows, long long n_ids_total,
                     long long* __restrict__ out_ids, float* __restrict__ out_rows, long long capacity,
                     unsigned long long* count) {
   const float* base = t.rows[shard];
-  for (long long slot = (long long)blockIdx.x * blockDim.x + threadIdx.x; slot < n_rows;
+  for (long long slot = row_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x; slot < n_rows;
        slot += (long long)gridDim.x * blockDim.x) {
     const long long id = slot_to_id(t, shard, slot);
     if (id >= n_ids_total) continue;
@@ -412,29 +412,38 @@ int fps_table_scatter(const FpsTableView* view, const int64_t* d_ids, int64_t n,
   return 0;
 }
 
-int fps_table_dump_shard(const FpsTableView* view, int shard, int64_t n_rows, int64_t n_ids_total,
+int fps_table_dump_range(const FpsTableView* view, int shard, int64_t row_begin, int64_t row_end, int64_t n_ids_total,
                          int64_t* d_out_ids, float* d_out_rows, int64_t capacity, int64_t* d_count,
                          void* stream) {
-  if (int e = check_view(view, "fps_table_dump_shard")) return e;
+  if (int e = check_view(view, "fps_table_dump_range")) return e;
   FPS_REQUIRE(shard >= 0 && shard < view->n_shards && view->rows[shard] != nullptr, FPS_E_INVALID,
-              "fps_table_dump_shard: shard %d not mapped", shard);
-  if (n_rows <= 0) return 0;
+              "fps_table_dump_range: shard %d not mapped", shard);
+  FPS_REQUIRE(row_begin >= 0 && row_end <= view->rows_per_shard, FPS_E_INVALID, "fps_table_dump_range: bad row range");
+  const long long n = row_end - row_begin;
+  if (n <= 0) return 0;
   if (view->stride == 1) {
-    long long b = (n_rows + 255) / 256;
+    long long b = (n + 255) / 256;
     if (b > (long long)fps_num_sms() * 8) b = (long long)fps_num_sms() * 8;
-    k_dump_shard_scalar<<<(int)b, 256, 0, (cudaStream_t)stream>>>(*view, shard, n_rows, n_ids_total, (long long*)d_out_ids,
-                                                                  d_out_rows, capacity, (unsigned long long*)d_count);
+    k_dump_shard_scalar<<<(int)b, 256, 0, (cudaStream_t)stream>>>(*view, shard, row_begin, row_end, n_ids_total,
+                                                                  (long long*)d_out_ids, d_out_rows, capacity,
+                                                                  (unsigned long long*)d_count);
     FPS_LAUNCH_CHECK();
     return 0;
   }
-  long long blocks = (n_rows + 7) / 8;
+  long long blocks = (n + 7) / 8;
   const long long cap = (long long)fps_num_sms() * 8;
   if (blocks > cap) blocks = cap;
   k_dump_shard<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
-      *view, shard, n_rows, n_ids_total, (long long*)d_out_ids, d_out_rows, capacity,
+      *view, shard, row_begin, row_end, n_ids_total, (long long*)d_out_ids, d_out_rows, capacity,
       (unsigned long long*)d_count);
   FPS_LAUNCH_CHECK();
   return 0;
+}
+
+int fps_table_dump_shard(const FpsTableView* view, int shard, int64_t n_rows, int64_t n_ids_total,
+                         int64_t* d_out_ids, float* d_out_rows, int64_t capacity, int64_t* d_count,
+                         void* stream) {
+  return fps_table_dump_range(view, shard, 0, n_rows, n_ids_total, d_out_ids, d_out_rows, capacity, d_count, stream);
 }
 
 }  // extern "C"

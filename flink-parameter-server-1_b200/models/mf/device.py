@@ -45,7 +45,8 @@ class DeviceMF:
     def __init__(self, n_users: int, n_items: int, num_factors: int = 10, range_min: float = -0.01,
                  range_max: float = 0.01, learning_rate: float = 0.01, *, lambda_: float = 0.0,
                  pull_limit: int = 0, seed: int = 0, lazy: bool = False, variant: str = "auto",
-                 ctx=None, n_shards: Optional[int] = None, replicate_items: Optional[bool] = None):
+                 ctx=None, n_shards: Optional[int] = None, replicate_items: Optional[bool] = None,
+                 emit: str = "on_close", emit_capacity: int = 1 << 20):
         """``replicate_items`` (several GPUs, eager tables): every GPU keeps the whole item table, pulls
         stay local and the item deltas of a launch cross NVLink once per touched row
         (``ShardedTable(replicated=True)``).  Default: item tables up to ``REPLICATE_BELOW_BYTES``."""
@@ -107,6 +108,18 @@ class DeviceMF:
         self._tile_slot = 0
         self.launches = 0
         self.kernel_launches = 0          # kernels of ours launched by step() so far
+        # Output stream form.  "on_close": one record per live row at the end (dump(); what the ...WithClose
+        # logics and every reference sink fold to).  "every_update": additionally one Right((item, vec)) per
+        # push and one Left((user, vec)) per rating, appended on the device after every step
+        # (SimplePSLogic.scala:24, PSOfflineMatrixFactorizationWorker.scala:144) and drained by drain_updates().
+        if emit not in ("on_close", "every_update"):
+            raise ValueError("emit must be 'on_close' or 'every_update'")
+        self.emit = emit
+        self._item_log = self._user_log = None
+        if emit == "every_update":
+            from ...ops.table import DeviceAppendLog
+            self._item_log = DeviceAppendLog(self.items, emit_capacity)
+            self._user_log = DeviceAppendLog(self.users, emit_capacity)
 
     def _variant_for(self, n: int) -> str:
         """``auto``: the tile path whenever combining pays -
@@ -190,6 +203,10 @@ class DeviceMF:
                                                 N.ptr(self.flow), N.current_stream()), "fps_mf_sgd_step")
                 self.kernel_launches += 3 if self.variant == "combine" else 1
             self.items.flush_deltas()            # replicated items: this launch's summed deltas -> the other replicas
+            if self._item_log is not None:       # values as of the end of this step, one record per push / rating
+                keep = users != N.SKIP_ID
+                self._item_log.append(items[keep] if not bool(keep.all()) else items)
+                self._user_log.append(users[keep] if not bool(keep.all()) else users)
         self.launches += 1
 
     def _ensure_staging(self, n: int):
@@ -297,6 +314,52 @@ class DeviceMF:
         for k, v in zip(iid.tolist(), irows.cpu().numpy().astype(np.float64)):
             out.append(Right((k, v)))
         return out
+
+    def drain_updates(self, as_stream: bool = False):
+        """``emit="every_update"``: everything emitted since the last drain, in emission order, as
+        ``((user_ids, user_rows), (item_ids, item_rows))`` numpy arrays - or, with ``as_stream``, as the
+        reference's ``Left((user, vec))`` / ``Right((item, vec))`` records."""
+        if self._item_log is None:
+            raise ValueError("this model was built with emit='on_close'")
+        import torch
+        torch.cuda.current_stream().synchronize()
+        u, i = self._user_log.drain(), self._item_log.drain()
+        if not as_stream:
+            return u, i
+        return ([Left((int(k), v.astype(np.float64))) for k, v in zip(*u)] +
+                [Right((int(k), v.astype(np.float64))) for k, v in zip(*i)])
+
+    def save(self, prefix: str, chunk_rows: int = 1 << 18) -> dict:
+        """Streaming checkpoint: every rank writes ``<prefix>.users.r<rank>`` and ``<prefix>.items.r<rank>``
+        (its worker-resident user rows and its shard of the item table) chunk by chunk; no Python object per
+        row, no host copy of a whole table."""
+        import torch
+        torch.cuda.synchronize()
+        self.ctx.barrier()
+        r = self.ctx.rank
+        out = {"users": self.users.dump_to(f"{prefix}.users.r{r}", chunk_rows),
+               "items": self.items.dump_to(f"{prefix}.items.r{r}", chunk_rows)}
+        self.ctx.barrier()
+        return out
+
+    def restore(self, prefix: str, world: Optional[int] = None) -> dict:
+        """Loads a ``save`` written by ``world`` ranks (default: as many as now).  Item rows are pushed to
+        their owner shards whatever the sharding was; user rows are kept by the rank that owns them now."""
+        import torch
+        world = world or self.ctx.world_size
+        cur, me = self.ctx.world_size, self.ctx.rank
+        n_u = n_i = 0
+        if world == cur:                        # same layout: every rank reads back its own two files
+            n_u = self.users.load_from(f"{prefix}.users.r{me}")
+            n_i = self.items.load_from(f"{prefix}.items.r{me}")
+        else:
+            for r in range(world):
+                n_u += self.users.load_from(f"{prefix}.users.r{r}")    # rows of users owned elsewhere are skipped
+                if r % cur == me:                                      # item files are shared out; rows go to their owners
+                    n_i += self.items.load_from(f"{prefix}.items.r{r}")
+        torch.cuda.synchronize()
+        self.ctx.barrier()
+        return {"users": n_u, "items": n_i}
 
     def load(self, model: Iterable) -> None:
         """Warm start from a previous output stream (``transform_with_double_model_load``):

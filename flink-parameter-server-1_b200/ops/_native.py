@@ -159,6 +159,7 @@ def lib() -> C.CDLL:
         "fps_table_gather": (C.c_int, [P(FpsTableView), vp, i64, vp, C.c_int, vp, vp]),
         "fps_table_scatter": (C.c_int, [P(FpsTableView), vp, i64, vp, C.c_int, C.c_int, vp, vp]),
         "fps_table_dump_shard": (C.c_int, [P(FpsTableView), C.c_int, i64, i64, vp, vp, i64, vp, vp]),
+        "fps_table_dump_range": (C.c_int, [P(FpsTableView), C.c_int, i64, i64, i64, vp, vp, i64, vp, vp]),
         "fps_mf_sgd_step": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, vp, i64, P(FpsMfParams), vp, vp]),
         "fps_mf_predict": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, i64, vp, vp]),
         "fps_mf_sample_negatives": (C.c_int, [P(FpsTableView), P(FpsNegSampler), vp, vp, vp, i64, u64, vp, vp, vp, vp]),

@@ -198,11 +198,14 @@ class ShardedTable:
         owner = ids // self.div
         return owner, ids - owner * self.div
 
-    def gather(self, ids, flow=None):
-        """Pull without compute: ``[len(ids), dim]`` values (remote rows come over NVLink)."""
+    def gather(self, ids, flow=None, out=None):
+        """Pull without compute: ``[len(ids), dim]`` values (remote rows come over NVLink).  ``out``: an
+        optional ``[len(ids), stride]`` fp32 device tensor to write into (e.g. a slice of an append log)."""
         import torch
         ids = ids.to(device="cuda", dtype=torch.int64).contiguous()
-        out = torch.empty((ids.numel(), self.stride), device="cuda", dtype=torch.float32)
+        if out is None:
+            out = torch.empty((ids.numel(), self.stride), device="cuda", dtype=torch.float32)
+        assert out.shape == (ids.numel(), self.stride) and out.is_contiguous()
         N.check(N.lib().fps_table_gather(C.byref(self._view), N.ptr(ids), ids.numel(), N.ptr(out),
                                          self.stride, N.ptr(flow), N.current_stream()), "fps_table_gather")
         return out[:, : self.dim + self.aux_cols]
@@ -267,6 +270,100 @@ class ShardedTable:
         order = torch.argsort(ids)
         return ids[order], rows[order]
 
+    # -- streaming checkpoint -----------------------------------------------------------------------
+    def dump_chunks(self, chunk_rows: int = 1 << 18):
+        """The live rows of the local shard(s) as a stream of ``(ids int64[k], rows fp32[k, dim + aux])``
+        numpy pairs, at most ``chunk_rows`` slots at a time through two pinned staging buffers: a table of
+        any size is dumped without ever being materialised on the host or turned into Python objects
+        (the on-close dump of ``SimplePSLogicWithClose.scala:29-31``, streamed).  The yielded arrays are
+        views of the staging buffers: consume (write out / copy) each pair before asking for the next."""
+        import torch
+        if self.replicated:
+            self.flush_deltas()
+            torch.cuda.synchronize()
+            self.ctx.barrier()
+            if self.ctx.rank != 0:
+                return
+        cols = self.dim + self.aux_cols
+        d_ids = [torch.empty(chunk_rows, device="cuda", dtype=torch.int64) for _ in range(2)]
+        d_rows = [torch.empty((chunk_rows, self.stride), device="cuda", dtype=torch.float32) for _ in range(2)]
+        d_cnt = [torch.zeros(1, device="cuda", dtype=torch.int64) for _ in range(2)]
+        h_ids = [torch.empty(chunk_rows, dtype=torch.int64).pin_memory() for _ in range(2)]
+        h_rows = [torch.empty((chunk_rows, self.stride), dtype=torch.float32).pin_memory() for _ in range(2)]
+        h_cnt = [torch.zeros(1, dtype=torch.int64).pin_memory() for _ in range(2)]
+        done = [torch.cuda.Event() for _ in range(2)]
+        work = [(s, b) for s in self.local_shards for b in range(0, self.rows_per_shard, chunk_rows)]
+
+        def launch(k):
+            s, b = work[k]
+            j = k & 1
+            d_cnt[j].zero_()
+            N.check(N.lib().fps_table_dump_range(C.byref(self._view), s, b, min(b + chunk_rows, self.rows_per_shard),
+                                                 self.n_ids, N.ptr(d_ids[j]), N.ptr(d_rows[j]), chunk_rows,
+                                                 N.ptr(d_cnt[j]), N.current_stream()), "fps_table_dump_range")
+            h_cnt[j].copy_(d_cnt[j], non_blocking=True)
+            h_ids[j].copy_(d_ids[j], non_blocking=True)
+            h_rows[j].copy_(d_rows[j], non_blocking=True)
+            done[j].record()
+
+        if work:
+            launch(0)
+        for k in range(len(work)):
+            j = k & 1
+            done[j].synchronize()
+            n = int(h_cnt[j][0])
+            ids_np, rows_np = h_ids[j][:n].numpy(), h_rows[j][:n, :cols].numpy()
+            if k + 1 < len(work):
+                launch(k + 1)            # the other buffer: its copy overlaps the consumer's work on this one
+            if n:
+                yield ids_np, rows_np
+
+    def dump_to(self, path: str, chunk_rows: int = 1 << 18) -> int:
+        """Streams the local live rows into ``path`` (binary: a JSON header line, then per chunk
+        ``int64 k, k int64 ids, k * cols fp32 values``, closed by ``k = 0``).  Returns the row count."""
+        import json
+        import numpy as np
+        total = 0
+        cols = self.dim + self.aux_cols
+        with open(path, "wb") as f:
+            f.write((json.dumps({"format": "fps_b200.table.v1", "cols": cols, "dim": self.dim, "n_ids": self.n_ids,
+                                 "rank": self.ctx.rank, "world": self.ctx.world_size}) + "\n").encode())
+            for ids, rows in self.dump_chunks(chunk_rows):
+                f.write(np.int64(len(ids)).tobytes())
+                f.write(np.ascontiguousarray(ids).tobytes())
+                f.write(np.ascontiguousarray(rows).tobytes())
+                total += len(ids)
+            f.write(np.int64(0).tobytes())
+        return total
+
+    def load_from(self, path: str) -> int:
+        """Streams a ``dump_to`` file back in (``transformWithModelLoad``: stored values replace whatever
+        was there; rows of a worker-resident table that belong to another rank are skipped).  Any rank
+        may load any file: PS-side rows are routed to their owner shard."""
+        import json
+        import numpy as np
+        import torch
+        total = 0
+        with open(path, "rb") as f:
+            hdr = json.loads(f.readline().decode())
+            if hdr.get("format") != "fps_b200.table.v1" or hdr["cols"] != self.dim + self.aux_cols:
+                raise ValueError(f"{path}: not a table dump of {self.dim + self.aux_cols} columns")
+            while True:
+                k = int(np.frombuffer(f.read(8), dtype=np.int64)[0])
+                if k == 0:
+                    break
+                ids = torch.from_numpy(np.frombuffer(f.read(8 * k), dtype=np.int64).copy())
+                rows = torch.from_numpy(np.frombuffer(f.read(4 * k * hdr["cols"]), dtype=np.float32)
+                                        .reshape(k, hdr["cols"]).copy())
+                if self.local_only and self.ctx.world_size > 1:
+                    keep = self.owner_of(ids)[0] == self.ctx.rank
+                    ids, rows = ids[keep], rows[keep]
+                if ids.numel():
+                    self.load(ids.pin_memory().cuda(non_blocking=True), rows.pin_memory().cuda(non_blocking=True))
+                    total += ids.numel()
+        torch.cuda.synchronize()
+        return total
+
     def resync(self, src: int = 0) -> None:
         """Replicated table: make every replica bit-identical to rank ``src``'s (replicas apply the
         same adds in different orders, so they drift by fp32 rounding)."""
@@ -305,3 +402,53 @@ def read_flow(flow) -> dict:
     d = {name: getattr(f, name) for name, _ in N.FpsFlow._fields_ if name != "reserved"}
     d["combined_rows"] = int(f.reserved[0])      # item rows really pulled/pushed by the combine variant
     return d
+
+
+class DeviceAppendLog:
+    """A device-resident append buffer of ``(id, row)`` records with a host-side cursor, drained by the
+    host in one copy: the per-update form of the output stream (``SimplePSLogic`` emits ``(id, value)``
+    on every push, ``M/server/SimplePSLogic.scala:24``; the MF workers emit ``(user, vec)`` per rating,
+    ``PSOfflineMatrixFactorizationWorker.scala:144``) without a Python object per record.  ``append``
+    gathers the current values of ``ids`` from the table straight into the buffer; when it would not
+    fit, the buffer is drained to pinned host memory first (kept as numpy chunks until ``drain``)."""
+
+    def __init__(self, table: ShardedTable, capacity: int = 1 << 20):
+        import torch
+        self.table, self.capacity = table, int(capacity)
+        self.ids = torch.empty(self.capacity, device="cuda", dtype=torch.int64)
+        self.rows = torch.empty((self.capacity, table.stride), device="cuda", dtype=torch.float32)
+        self.cursor = 0
+        self._spilled: list = []
+        self.records = 0
+
+    def append(self, ids) -> None:
+        import torch
+        ids = ids.to(device="cuda", dtype=torch.int64).contiguous()
+        n, pos = ids.numel(), 0
+        while pos < n:
+            if self.cursor == self.capacity:
+                self._spill()
+            take = min(n - pos, self.capacity - self.cursor)
+            part = ids[pos:pos + take]
+            self.ids[self.cursor:self.cursor + take].copy_(part)
+            self.table.gather(part, out=self.rows[self.cursor:self.cursor + take])
+            self.cursor += take
+            pos += take
+        self.records += n
+
+    def _spill(self) -> None:
+        if self.cursor:
+            cols = self.table.dim + self.table.aux_cols
+            self._spilled.append((self.ids[:self.cursor].cpu().numpy(), self.rows[:self.cursor, :cols].cpu().numpy()))
+            self.cursor = 0
+
+    def drain(self):
+        """``(ids int64[n], rows fp32[n, dim + aux])`` numpy arrays of everything appended since the last
+        drain, in append order."""
+        import numpy as np
+        self._spill()
+        chunks, self._spilled = self._spilled, []
+        cols = self.table.dim + self.table.aux_cols
+        if not chunks:
+            return np.zeros(0, np.int64), np.zeros((0, cols), np.float32)
+        return np.concatenate([c[0] for c in chunks]), np.concatenate([c[1] for c in chunks])

@@ -142,6 +142,13 @@ int fps_table_dump_shard(const FpsTableView* view, int shard, int64_t n_rows, in
                          int64_t* d_out_ids, float* d_out_rows, int64_t capacity, int64_t* d_count,
                          void* stream);
 
+/* The same for the slots [row_begin, row_end) of the shard only: a checkpoint streams a table through a
+ * fixed-size buffer chunk by chunk instead of materialising it (M/FlinkParameterServer.scala:377-566 is
+ * the matching streamed load).                                                                        */
+int fps_table_dump_range(const FpsTableView* view, int shard, int64_t row_begin, int64_t row_end,
+                         int64_t n_ids_total, int64_t* d_out_ids, float* d_out_rows, int64_t capacity,
+                         int64_t* d_count, void* stream);
+
 /* ---- matrix factorisation (N1, N2) ----------------------------------------------------------- */
 typedef struct FpsMfParams {
   float   lr;
