@@ -185,7 +185,11 @@ def config4(ctx):
     pa.params.pull_limit = 10_000
     ms = timed(lambda: pa.step(indptr, idx, val, lab), 3, 20)
     rows = B * nnz * ctx.world_size
-    return {"config": 4, "pull_limit": 10_000, "max_in_flight": pa.stats()["max_in_flight"],
+    cpu = None
+    if ctx.rank == 0:
+        from fps_b200.parallel import cpu_baseline
+        cpu = cpu_baseline.bench_pa_ova(F, L, nnz, 1 << 12, workers=4, shards=4, variant="pa_i", pull_limit=10_000)
+    return {"config": 4, "cpu_restatement": cpu, "pull_limit": 10_000, "max_in_flight": pa.stats()["max_in_flight"],
             "without_limiter_ms_per_step": ms_unlimited, "what": "multiclass OVA PA-I, 100 classes, 1M features, 100 nnz", "n_gpus": ctx.world_size,
             "examples_per_gpu": B, "ms_per_step": ms, "examples_per_sec": B * ctx.world_size / ms * 1e3,
             "pull_rows_per_sec": rows / ms * 1e3, "push_rows_per_sec": rows / ms * 1e3,

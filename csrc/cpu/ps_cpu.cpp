@@ -348,6 +348,160 @@ double fps_cpu_pa_binary_run(int W, int S, int64_t n_per_worker, int64_t nnz_per
   return std::chrono::duration<double>(t1 - t0).count();
 }
 
+// Multiclass one-vs-all passive-aggressive (PassiveAggressiveOneVersusAll.scala:52-69 through the same
+// worker / shard protocol): a parameter is the row of L class weights of one feature; Pull / PullAnswer /
+// Push messages carry L doubles.  d = W^T x over the pulled rows, y_c = +1 for the label else -1,
+// loss_c = max(0, 1 - d_c y_c), tau_c per variant, push of x_i * (tau o y) per active feature.
+// labels are class indices.  weights [S][div][L].  *out_mistakes = examples whose argmax was wrong.
+double fps_cpu_pa_ova_run(int W, int S, int L, int64_t n_per_worker, int64_t nnz_per_worker, const int64_t* indptr,
+                          const int32_t* indices, const float* values, const int32_t* labels, double* weights,
+                          int64_t div, int variant, double C, int pull_limit, double* out_loss,
+                          int64_t* out_mistakes) {
+  const uint64_t slot = (sizeof(Msg) + (size_t)(L - 1) * sizeof(double) + 63) & ~(size_t)63;
+  const uint64_t cap = pow2_at_least((uint64_t)2 * pull_limit + 4);
+  std::vector<Ring> req((size_t)W * S), ans((size_t)S * W);
+  for (auto& r : req) r.init(cap, slot);
+  for (auto& r : ans) r.init(cap, slot);
+  std::atomic<int> workers_done{0};
+  std::vector<double> loss(W, 0.0);
+  std::vector<int64_t> wrong(W, 0);
+  auto t0 = std::chrono::steady_clock::now();
+
+  auto shard_fn = [&](int s) {
+    double* table = weights + (size_t)s * div * L;
+    while (true) {
+      bool any = false;
+      for (int w = 0; w < W; ++w) {
+        Ring& in = req[(size_t)w * S + s];
+        for (int burst = 0; burst < 64; ++burst) {
+          char* p = in.try_front();
+          if (!p) break;
+          Msg* m = (Msg*)p;
+          double* row = table + ((int64_t)m->id - (int64_t)s * div) * L;
+          if (m->type == 0) {
+            Ring& out = ans[(size_t)s * W + w];
+            char* q;
+            while (!(q = out.try_reserve())) std::this_thread::yield();
+            Msg* a = (Msg*)q;
+            a->type = 1;
+            a->id = m->id;
+            memcpy(a->row, row, (size_t)L * sizeof(double));
+            out.commit();
+          } else {
+            for (int c = 0; c < L; ++c) row[c] += m->row[c];
+          }
+          in.pop();
+          any = true;
+        }
+      }
+      if (!any) {
+        if (workers_done.load(std::memory_order_acquire) == W) {
+          bool empty = true;
+          for (int w = 0; w < W; ++w) empty = empty && req[(size_t)w * S + s].try_front() == nullptr;
+          if (empty) break;
+        }
+        std::this_thread::yield();
+      }
+    }
+  };
+
+  auto worker_fn = [&](int w) {
+    const int64_t* ip = indptr + (size_t)w * (n_per_worker + 1);
+    const int32_t* idx = indices + (size_t)w * nnz_per_worker;
+    const float* val = values + (size_t)w * nnz_per_worker;
+    const int32_t* lab = labels + (size_t)w * n_per_worker;
+    std::vector<double> dvec((size_t)n_per_worker * L, 0.0);   // decision vector, accumulated as the answers arrive
+    std::vector<double> n2((size_t)n_per_worker, 0.0);
+    std::vector<int32_t> missing((size_t)n_per_worker, 0);
+    std::vector<std::vector<int64_t>> pend(S);
+    std::vector<size_t> pend_head(S, 0);
+    std::vector<int64_t> owner_example((size_t)nnz_per_worker);
+    std::vector<double> mult(L);
+    int64_t next_ex = 0, next_pos = 0, in_flight = 0, done_ex = 0;
+    double local_loss = 0.0;
+    int64_t local_wrong = 0;
+    while (done_ex < n_per_worker) {
+      for (int s = 0; s < S; ++s) {
+        Ring& in = ans[(size_t)s * W + w];
+        char* p;
+        while ((p = in.try_front())) {
+          Msg* a = (Msg*)p;
+          const int64_t pos = pend[s][pend_head[s]++];
+          const int64_t e = owner_example[pos];
+          double* d = &dvec[(size_t)e * L];
+          const double x = (double)val[pos];
+          for (int c = 0; c < L; ++c) d[c] += x * a->row[c];
+          n2[e] += x * x;
+          in.pop();
+          --in_flight;
+          if (--missing[e] == 0) {
+            int am = 0;
+            for (int c = 1; c < L; ++c) if (d[c] > d[am]) am = c;
+            if (am != lab[e]) ++local_wrong;
+            bool any = false;
+            for (int c = 0; c < L; ++c) {
+              const double y = c == lab[e] ? 1.0 : -1.0;
+              const double l = std::max(0.0, 1.0 - d[c] * y);
+              local_loss += l;
+              double tau = 0.0;
+              if (n2[e] > 0.0) tau = variant == 0 ? l / n2[e] : variant == 1 ? std::min(C, l / n2[e]) : l / (n2[e] + 1.0 / (2.0 * C));
+              mult[c] = tau * y;
+              any = any || mult[c] != 0.0;
+            }
+            if (any) {
+              for (int64_t k = ip[e]; k < ip[e + 1]; ++k) {
+                const int so = (int)((int64_t)idx[k] / div);
+                Ring& out = req[(size_t)w * S + so];
+                char* q;
+                while (!(q = out.try_reserve())) std::this_thread::yield();
+                Msg* msg = (Msg*)q;
+                msg->type = 1;
+                msg->id = idx[k];
+                for (int c = 0; c < L; ++c) msg->row[c] = mult[c] * (double)val[k];
+                out.commit();
+              }
+            }
+            ++done_ex;
+          }
+        }
+      }
+      while (next_ex < n_per_worker && in_flight < pull_limit) {
+        if (next_pos == ip[next_ex]) {
+          missing[next_ex] = (int32_t)(ip[next_ex + 1] - ip[next_ex]);
+          if (missing[next_ex] == 0) { ++done_ex; ++next_ex; continue; }
+        }
+        const int so = (int)((int64_t)idx[next_pos] / div);
+        Ring& out = req[(size_t)w * S + so];
+        char* q = out.try_reserve();
+        if (!q) break;
+        Msg* msg = (Msg*)q;
+        msg->type = 0;
+        msg->id = idx[next_pos];
+        out.commit();
+        pend[so].push_back(next_pos);
+        owner_example[next_pos] = next_ex;
+        ++in_flight;
+        if (++next_pos == ip[next_ex + 1]) ++next_ex;
+      }
+    }
+    loss[w] = local_loss;
+    wrong[w] = local_wrong;
+    workers_done.fetch_add(1, std::memory_order_release);
+  };
+
+  std::vector<std::thread> th;
+  for (int s = 0; s < S; ++s) th.emplace_back(shard_fn, s);
+  for (int w = 0; w < W; ++w) th.emplace_back(worker_fn, w);
+  for (auto& t : th) t.join();
+  auto t1 = std::chrono::steady_clock::now();
+  double tl = 0.0;
+  int64_t tw = 0;
+  for (int w = 0; w < W; ++w) { tl += loss[w]; tw += wrong[w]; }
+  if (out_loss) *out_loss = tl;
+  if (out_mistakes) *out_mistakes = tw;
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
 // deterministic table fill in [lo, hi)
 void fps_cpu_fill_uniform(double* p, int64_t n, double lo, double hi, uint64_t seed) {
   uint64_t s = seed;

@@ -18,6 +18,7 @@ from ...entities import Left, Right
 from ...ops import _native as N
 from ...ops import philox
 from ...ops.table import ShardedTable, new_flow, read_flow
+from ...utils.observability import nvtx_range
 from .sparse import SparseVector
 
 MULTI = {"binary": 0, "ova": 1, "pb": 2, "ml": 3}
@@ -73,11 +74,12 @@ class DevicePA:
         n = indptr.numel() - 1
         pred = torch.empty(n, device="cuda", dtype=torch.int32)
         self.params.predict_only = int(predict_only or labels is None)
-        N.check(N.lib().fps_pa_step_cost(self.table.view_ref(), N.ptr(indptr), N.ptr(indices), N.ptr(values),
-                                         N.ptr(labels), n, C.byref(self.params), N.ptr(self.cost),
-                                         N.ptr(pred), N.ptr(self.flow), N.current_stream()), "fps_pa_step")
-        if not self.params.predict_only:
-            self.table.flush_deltas()        # replicated table: this launch's summed deltas -> the other replicas
+        with nvtx_range("fps.pa.step"):
+            N.check(N.lib().fps_pa_step_cost(self.table.view_ref(), N.ptr(indptr), N.ptr(indices), N.ptr(values),
+                                             N.ptr(labels), n, C.byref(self.params), N.ptr(self.cost),
+                                             N.ptr(pred), N.ptr(self.flow), N.current_stream()), "fps_pa_step")
+            if not self.params.predict_only:
+                self.table.flush_deltas()    # replicated table: this launch's summed deltas -> the other replicas
         self.launches += 1
         return pred
 

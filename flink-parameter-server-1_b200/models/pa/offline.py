@@ -137,8 +137,76 @@ class PAOfflineWorker(WorkerLogic):
             self._advance(ps)
 
 
+def _offline_job_device(training_src, test_src, ps_parallelism, method, iterations, pull_limit, seed, shuffle,
+                        feature_count, batch_size: int = 4096, return_model: bool = False):
+    """The offline job on the device engine (``PABinaryClassificationOffline.scala:47-387``): the training
+    set is turned into CSR mini-batches once and stays on the device, every epoch launches the fused
+    gather / margin / scatter kernel over the batches (order reshuffled per epoch), then the test set is
+    scored with the final weights.  The feature-counted limiter (``:230-249``) is the kernels' credit
+    pool.  Output: ``Left((label, prediction, vector))`` per test record + the on-close weight dump."""
+    import torch
+    from ...parallel.device_context import get_context
+    from .device import DevicePA, method_to_device, to_csr
+    inner = getattr(method, "inner", method)
+    binary_pm1 = inner is not method                      # +1 / -1 labels of the binary offline job
+    train = [(_to_sparse(v, feature_count), l) for v, l in as_stream(training_src, 1).collect()]
+    test = [(_to_sparse(v, feature_count), l) for v, l in as_stream(test_src, 1).collect()]
+    if not feature_count:
+        feature_count = 1 + max([int(v.indices.max()) for v, _ in train + test if v.active_size] + [0])
+    kw = method_to_device(inner)
+    ctx = get_context()
+    shards = None if ctx.distributed else max(1, min(int(ps_parallelism), 16))
+    pa = DevicePA(feature_count, label_count=kw["label_count"], algorithm=kw["algorithm"], variant=kw["variant"],
+                  aggressiveness=kw["aggressiveness"], pull_limit=pull_limit, cost=kw["cost"], n_shards=shards)
+
+    def batches(records):
+        out = []
+        for s in range(0, len(records), batch_size):
+            part = records[s:s + batch_size]
+            indptr, indices, values = to_csr([v for v, _ in part])
+            lab = [l for _, l in part]
+            if kw["algorithm"] == "binary":
+                lab_t = torch.tensor([1 if (l is True or l > 0) else -1 for l in lab], dtype=torch.int32).cuda()
+            else:
+                lab_t = torch.tensor([int(l) for l in lab], dtype=torch.int32).cuda()
+            out.append((torch.from_numpy(indptr).cuda(), torch.from_numpy(indices).cuda(),
+                        torch.from_numpy(values).cuda(), lab_t, part))
+        return out
+
+    rnd = random.Random(seed)
+    train_b = batches(train)
+    for _ in range(iterations):
+        order = list(range(len(train_b)))
+        if shuffle:
+            rnd.shuffle(order)
+        for k in order:
+            indptr, indices, values, lab, _part = train_b[k]
+            pa.step(indptr, indices, values, lab)
+    out = []
+    for indptr, indices, values, _lab, part in batches(test):
+        pred = pa.step(indptr, indices, values, None, predict_only=True).cpu().tolist()
+        for (vec, label), p in zip(part, pred):
+            if kw["algorithm"] == "binary":
+                p = (1 if p > 0 else -1) if binary_pm1 else (p > 0)
+            out.append(Left((label, p, vec)))
+    torch.cuda.synchronize()
+    ctx.barrier()
+    out = out + pa.dump()
+    return (out, pa) if return_model else out
+
+
 def _offline_job(training_src, test_src, worker_parallelism, ps_parallelism, method, init, add,
-                 iterations, pull_limit, iteration_wait_time, seed, shuffle, feature_count, **engine_kw):
+                 iterations, pull_limit, iteration_wait_time, seed, shuffle, feature_count,
+                 engine: str = "host", **engine_kw):
+    if engine not in ("host", "device", "auto"):
+        raise ValueError("engine must be 'host', 'device' or 'auto'")
+    if engine != "host":
+        from ...parallel import device_engine
+        ok, why = device_engine.device_ready()
+        if ok:
+            return _offline_job_device(training_src, test_src, ps_parallelism, method, iterations, pull_limit, seed,
+                                       shuffle, feature_count, **engine_kw)
+        device_engine.fallback(why)
     rnd = random.Random(seed)
     W = worker_parallelism
 

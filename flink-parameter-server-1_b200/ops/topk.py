@@ -9,6 +9,7 @@ from __future__ import annotations
 from typing import Optional, Tuple
 
 from . import _native as N
+from ..utils.observability import nvtx_range
 
 
 def sort_items_by_length(items, ids=None):
@@ -101,10 +102,11 @@ def lemp_topk_packed(queries, packed: PackedItems, k: int, *, use_pruning: bool 
                               dtype=torch.uint8)
     out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
     out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
-    N.check(N.lib().fps_lemp_topk_packed(N.ptr(q), q.shape[1], n_q, N.ptr(packed.data), N.ptr(packed.item_len),
-                                         N.ptr(packed.item_ids), packed.n_items, packed.dim, k, int(use_pruning),
-                                         N.ptr(scratch), scratch.numel(), N.ptr(out_s), N.ptr(out_i), N.ptr(stats),
-                                         N.current_stream()), "fps_lemp_topk_packed")
+    with nvtx_range("fps.topk.packed"):
+        N.check(N.lib().fps_lemp_topk_packed(N.ptr(q), q.shape[1], n_q, N.ptr(packed.data), N.ptr(packed.item_len),
+                                             N.ptr(packed.item_ids), packed.n_items, packed.dim, k, int(use_pruning),
+                                             N.ptr(scratch), scratch.numel(), N.ptr(out_s), N.ptr(out_i),
+                                             N.ptr(stats), N.current_stream()), "fps_lemp_topk_packed")
     return out_s, out_i
 
 

@@ -35,6 +35,10 @@ def lib():
         L.fps_cpu_pa_binary_run.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_int,
                                             C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+        L.fps_cpu_pa_ova_run.restype = C.c_double
+        L.fps_cpu_pa_ova_run.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_int,
+                                         C.POINTER(C.c_double), C.POINTER(C.c_int64)]
         L.fps_cpu_fill_uniform.restype = None
         L.fps_cpu_fill_uniform.argtypes = [C.c_void_p, C.c_int64, C.c_double, C.c_double, C.c_uint64]
         _lib = L
@@ -80,6 +84,48 @@ def run_pa_binary(indptr, indices, values, labels, weights, variant: str = "pa",
                                        {"pa": 0, "pa_i": 1, "pa_ii": 2}[variant], float(C_), int(pull_limit),
                                        C.byref(loss), C.byref(wrong))
     return secs, loss.value, wrong.value
+
+
+def run_pa_ova(indptr, indices, values, labels, weights, variant: str = "pa", C_: float = 1.0,
+               pull_limit: int = 10_000):
+    """One-vs-all multiclass passive-aggressive through the C++ PS loop
+    (``PassiveAggressiveOneVersusAll.scala:52-69``): parameters are rows of ``L`` class weights, ``labels``
+    ``[W, n]`` class indices, ``weights`` ``[S, div, L]`` fp64 updated in place.  Same array layout as
+    ``run_pa_binary``.  Returns ``(seconds, summed hinge loss over classes, argmax mistakes)``."""
+    indptr = np.ascontiguousarray(indptr, dtype=np.int64)
+    indices = np.ascontiguousarray(indices, dtype=np.int32)
+    values = np.ascontiguousarray(values, dtype=np.float32)
+    labels = np.ascontiguousarray(labels, dtype=np.int32)
+    W, n1 = indptr.shape
+    S, div, L = weights.shape
+    assert indices.shape == values.shape and indices.shape[0] == W and labels.shape == (W, n1 - 1)
+    assert weights.flags.c_contiguous and weights.dtype == np.float64
+    loss, wrong = C.c_double(0.0), C.c_int64(0)
+    secs = lib().fps_cpu_pa_ova_run(W, S, L, n1 - 1, indices.shape[1], indptr.ctypes.data, indices.ctypes.data,
+                                    values.ctypes.data, labels.ctypes.data, weights.ctypes.data, div,
+                                    {"pa": 0, "pa_i": 1, "pa_ii": 2}[variant], float(C_), int(pull_limit),
+                                    C.byref(loss), C.byref(wrong))
+    return secs, loss.value, wrong.value
+
+
+def bench_pa_ova(n_features: int = 1_000_000, n_classes: int = 100, nnz: int = 100, examples: int = 1 << 13,
+                 workers: int = 4, shards: int = 4, variant: str = "pa_i", pull_limit: int = 10_000,
+                 seed: int = 0) -> dict:
+    """BASELINE config 4 on the CPU restatement (same shapes as ``benchmarks/run_configs.py`` config 4)."""
+    rng = np.random.default_rng(seed)
+    n = examples // workers
+    div = (n_features + shards - 1) // shards
+    idx = np.sort(rng.integers(0, n_features, size=(workers, n, nnz), dtype=np.int32), axis=2).reshape(workers, -1)
+    val = rng.standard_normal((workers, n * nnz)).astype(np.float32)
+    lab = rng.integers(0, n_classes, size=(workers, n)).astype(np.int32)
+    indptr = np.tile(np.arange(0, (n + 1) * nnz, nnz, dtype=np.int64), (workers, 1))
+    w = np.zeros((shards, div, n_classes), dtype=np.float64)
+    run_pa_ova(indptr[:, : n // 8 + 1], idx[:, : (n // 8) * nnz], val[:, : (n // 8) * nnz], lab[:, : n // 8], w,
+               variant, 0.1, pull_limit)
+    secs, loss, wrong = run_pa_ova(indptr, idx, val, lab, w, variant, 0.1, pull_limit)
+    return {"impl": "cpu", "note": "C++ CPU restatement of the PS loop (not Flink), fp64", "workers": workers,
+            "shards": shards, "examples": n * workers, "seconds": secs, "examples_per_sec": n * workers / secs,
+            "row_pulls_per_sec": n * workers * nnz / secs, "row_bytes": n_classes * 8}
 
 
 def bench_pa_binary(n_features: int = 47_236, nnz: int = 75, examples: int = 1 << 17, workers: int = 4,

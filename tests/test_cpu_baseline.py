@@ -87,3 +87,34 @@ def test_cpu_pa_binary_multi_worker_learns_and_respects_limit():
     _s, _loss, wrong_first = cpu_baseline.run_pa_binary(indptr, idx.reshape(W, -1), val.reshape(W, -1), lab, w, "pa_i", 1.0, 50)
     _s, _loss, wrong_again = cpu_baseline.run_pa_binary(indptr, idx.reshape(W, -1), val.reshape(W, -1), lab, w, "pa_i", 1.0, 50)
     assert wrong_again < 0.5 * wrong_first                       # second pass over the same data: far fewer mistakes
+
+
+def test_cpu_ova_restatement_equals_the_serial_rule_at_limit_one():
+    """One worker, pull limit 1: the threaded loop is serial, so it must reproduce the host algorithm."""
+    from fps_b200.models.pa import SparseVector
+    from fps_b200.models.pa.algorithm import PassiveAggressiveOneVersusAll
+    from fps_b200.parallel import cpu_baseline
+    rng = np.random.default_rng(4)
+    F, L, n, nnz = 60, 5, 40, 6
+    idx = np.sort(np.stack([rng.choice(F, nnz, replace=False) for _ in range(n)]), axis=1).astype(np.int32)
+    val = rng.standard_normal((n, nnz)).astype(np.float32)
+    lab = rng.integers(0, L, n).astype(np.int32)
+    S = 3
+    div = (F + S - 1) // S
+    w = np.zeros((S, div, L))
+    indptr = np.arange(0, (n + 1) * nnz, nnz, dtype=np.int64)[None, :]
+    secs, loss, wrong = cpu_baseline.run_pa_ova(indptr, idx.reshape(1, -1), val.reshape(1, -1), lab[None, :], w,
+                                                "pa_i", 0.5, pull_limit=1)
+    algo = PassiveAggressiveOneVersusAll.build_pa_i(L, 0.5)
+    model = {}
+    mistakes = 0
+    for e in range(n):
+        x = SparseVector(idx[e], val[e].astype(np.float64), F)
+        sub = {int(k): model.get(int(k), np.zeros(L)) for k in idx[e]}
+        mistakes += int(algo.predict(x, sub) != lab[e])
+        for k, d in algo.delta(x, sub, int(lab[e])):
+            model[k] = model.get(k, np.zeros(L)) + d
+    flat = w.reshape(-1, L)
+    for k, v in model.items():
+        np.testing.assert_allclose(flat[k], v, rtol=1e-9, atol=1e-9)
+    assert wrong == mistakes and secs > 0

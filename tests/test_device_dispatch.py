@@ -172,3 +172,39 @@ def test_transform_binary_on_both_engines(engine):
     acc = np.mean([preds[k] == labels[k] for k in range(100)])
     assert acc >= 0.8, (engine, acc)
     assert len(last_write_wins(rights(out))) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("engine", ["host", "device"])
+def test_offline_pa_jobs_on_both_engines(engine):
+    """PABinaryClassificationOffline / the genuinely multiclass offline job: epochs over the training set, then
+    predictions for the test set, through the same public entry points on both engines."""
+    from fps_b200.models.pa import (PassiveAggressiveOneVersusAll, SparseVector, pa_binary_classification_offline,
+                                    pa_multi_classification_offline)
+    rnd = np.random.default_rng(8)
+    F = 2000
+    w_true = rnd.normal(size=F)
+    data = []
+    for _ in range(100):
+        ix = rnd.choice(F, 60, replace=False)
+        vv = rnd.normal(size=60)
+        x = SparseVector(ix, vv, F)
+        data.append((x, 1 if x.dot(w_true) > 0 else -1))
+    out = pa_binary_classification_offline(data[:80], data[80:], 3, 2, iterations=5, paf_type=1, paf_const=1.0,
+                                           pull_limit=300, iteration_wait_time=50, feature_count=F, engine=engine)
+    preds = lefts(out)
+    assert len(preds) == 20 and {p for _l, p, _v in preds} <= {1, -1}
+    assert sum(1 for label, pred, _v in preds if label == pred) / 20 >= 0.6
+    assert len(rights(out)) > 0
+    Wm = rnd.normal(size=(100, 5))
+    multi = []
+    for _ in range(420):
+        ix = rnd.choice(100, 20, replace=False)
+        vv = rnd.normal(size=20)
+        multi.append((SparseVector(ix, vv, 100), int(np.argmax(vv @ Wm[ix]))))
+    out = pa_multi_classification_offline(multi[:400], multi[400:], 2, 2, iterations=3,
+                                          method=PassiveAggressiveOneVersusAll.build_pa_i(5, 0.5),
+                                          pull_limit=500, iteration_wait_time=50, feature_count=100, engine=engine)
+    preds = lefts(out)
+    assert len(preds) == 20 and {p for _l, p, _v in preds} <= set(range(5))
+    assert sum(1 for l, p, _v in preds if l == p) / 20 >= 0.5
