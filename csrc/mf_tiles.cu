@@ -93,6 +93,27 @@ __device__ __forceinline__ void tl_bulk_g2s(void* smem_dst, const void* gmem_src
                : "memory");
 }
 
+// the same on shared-space addresses computed once per warp (a generic -> shared conversion per call was
+// 15 of the kernel's ~360 instructions per record)
+__device__ __forceinline__ void tl_expect_and_copy(uint32_t dst_s, const void* gmem_src, uint32_t bytes, uint32_t bar_s) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst_s), "l"(gmem_src), "r"(bytes), "r"(bar_s)
+               : "memory");
+}
+__device__ __forceinline__ void tl_wait_s(uint32_t bar_s, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar_s), "r"(parity)
+        : "memory");
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // phase 1: counting sort by (item & mask) into packed records
 // ---------------------------------------------------------------------------------------------
@@ -584,6 +605,7 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
   const int nvec = items.stride >> 2;
   const uint32_t row_bytes = (uint32_t)items.stride * 4u;
   WarpRing& ring = rings[w];
+  const uint32_t rows_s = smem_addr(ring.rows), bars_s = smem_addr(ring.bar);   // shared-space addresses of this warp's ring
   if (lane == 0) {
 #pragma unroll
     for (int s = 0; s < TL_RU + TL_RI; ++s) tl_mbar_init(&ring.bar[s], 1);
@@ -611,11 +633,11 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
         float* g = pack_row(users, (unsigned int)r.user);
         const int s = j % TL_RU;
         ring.gptr[s] = g;
-        tl_mbar_expect_tx(&ring.bar[s], row_bytes);
-        tl_bulk_g2s(&ring.rows[s * 128], g, row_bytes, &ring.bar[s]);
+        tl_expect_and_copy(rows_s + s * 512, g, row_bytes, bars_s + s * 8);
       }
     };
     int pi = 0, runs_issued = 0, runs_consumed = 0, p_item = -1;
+    int slot_issue = 0, slot_consume = 0;          // runs_issued % RI, runs_consumed % RI without the division
     auto pump_items = [&](int cap) {       // keep up to `cap` item rows of upcoming runs in flight
       while (runs_issued - runs_consumed < cap && pi < len) {
         const unsigned long long key = s_key[b0 + pi];
@@ -624,12 +646,12 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
           p_item = item;
           if (lane == 0) {
             float* g = pack_row(items, (unsigned int)s_rec[(unsigned int)key].pad);
-            const int s = TL_RU + runs_issued % RI;
+            const int s = TL_RU + slot_issue;
             ring.gptr[s] = g;
-            tl_mbar_expect_tx(&ring.bar[s], row_bytes);
-            tl_bulk_g2s(&ring.rows[s * 128], g, row_bytes, &ring.bar[s]);
+            tl_expect_and_copy(rows_s + s * 512, g, row_bytes, bars_s + s * 8);
           }
           ++runs_issued;
+          slot_issue = slot_issue + 1 == RI ? 0 : slot_issue + 1;
         }
         ++pi;
       }
@@ -654,7 +676,7 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
       const TileRec r = s_rec[(unsigned int)key];
       // user row
       const int su = j % TL_RU;
-      tl_mbar_wait(&ring.bar[su], (phase >> su) & 1u);
+      tl_wait_s(bars_s + su * 8, (phase >> su) & 1u);
       phase ^= 1u << su;
       float* urow = ring.gptr[su];
       float4 us[1];
@@ -673,8 +695,9 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
       if (item != cy.item) {
         if (cy.item >= 0 && cy.run_len > 0) tcarry_push<32, 1>(cy, nvec, c);
         if (runs_issued == runs_consumed) pump_items(1);     // depth 0 (tight limiter): fetch on demand
-        const int si = TL_RU + runs_consumed % RI;
-        tl_mbar_wait(&ring.bar[si], (phase >> si) & 1u);
+        const int si = TL_RU + slot_consume;
+        slot_consume = slot_consume + 1 == RI ? 0 : slot_consume + 1;
+        tl_wait_s(bars_s + si * 8, (phase >> si) & 1u);
         phase ^= 1u << si;
         cy.item = item;
         cy.row = ring.gptr[si];
@@ -742,10 +765,10 @@ int fps_mf_bucket(const int32_t* d_user_ids, const int32_t* d_item_ids, const fl
   FPS_CUDA(cudaMemsetAsync(counts, 0, (size_t)nb * sizeof(int), st));
   // one CTA per SM at most: every CTA walks all nb bins of its shared-memory histogram three times,
   // which only pays when it also owns a long range of records
-  long long blocks = (n + 16383) / 16384;
+  long long blocks = (n + 4095) / 4096;
   const long long cap = (long long)fps_num_sms();
   if (blocks > cap) blocks = cap;
-  const int threads = n >= 65536 ? 1024 : 256;
+  const int threads = n >= (1 << 20) ? 1024 : 256;
   k_bucket_count<<<(int)blocks, threads, nb * sizeof(int), st>>>(d_item_ids, n, nb, counts);
   k_bucket_scan<<<1, 1024, nb * sizeof(int), st>>>(counts, cursors, nb);
   k_bucket_scatter<<<(int)blocks, threads, 2 * nb * sizeof(int), st>>>(d_user_ids, d_item_ids, d_ratings, n, nb, cursors, out);

@@ -182,19 +182,19 @@ def test_offline_pa_jobs_on_both_engines(engine):
     from fps_b200.models.pa import (PassiveAggressiveOneVersusAll, SparseVector, pa_binary_classification_offline,
                                     pa_multi_classification_offline)
     rnd = np.random.default_rng(8)
-    F = 2000
+    F = 500
     w_true = rnd.normal(size=F)
     data = []
-    for _ in range(100):
-        ix = rnd.choice(F, 60, replace=False)
-        vv = rnd.normal(size=60)
+    for _ in range(360):
+        ix = rnd.choice(F, 40, replace=False)
+        vv = rnd.normal(size=40)
         x = SparseVector(ix, vv, F)
         data.append((x, 1 if x.dot(w_true) > 0 else -1))
-    out = pa_binary_classification_offline(data[:80], data[80:], 3, 2, iterations=5, paf_type=1, paf_const=1.0,
+    out = pa_binary_classification_offline(data[:300], data[300:], 3, 2, iterations=4, paf_type=1, paf_const=1.0,
                                            pull_limit=300, iteration_wait_time=50, feature_count=F, engine=engine)
     preds = lefts(out)
-    assert len(preds) == 20 and {p for _l, p, _v in preds} <= {1, -1}
-    assert sum(1 for label, pred, _v in preds if label == pred) / 20 >= 0.6
+    assert len(preds) == 60 and {p for _l, p, _v in preds} <= {1, -1}
+    assert sum(1 for label, pred, _v in preds if label == pred) / 60 >= 0.58      # both engines land near 0.64 on this little set
     assert len(rights(out)) > 0
     Wm = rnd.normal(size=(100, 5))
     multi = []
