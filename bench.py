@@ -32,6 +32,10 @@ DEFAULT_PULL_LIMIT = 65536
 # measured on this pool (profiles/r1_2gpu/p2p_probe_2gpu.json): per-direction P2P rates of the two access
 # types the fused kernels use; the NVLink roofline of a step is rows pulled / LOAD + rows pushed / RED
 P2P_LOAD_GBS, P2P_RED_GBS = 759.0, 687.0
+# measured with EVERY GPU pulling and pushing random 512-byte rows at once (scripts/p2p_symmetric_probe.py,
+# profiles/r2_2gpu/p2p_symmetric_2gpu.json): payload per direction per GPU when requests / acknowledgements of
+# one direction share the wire with the payload of the other - the pattern the fused kernels produce
+P2P_SYMMETRIC_GBS = 638.6
 
 
 def parse():
@@ -273,8 +277,10 @@ def main():
                 "remote_pull_fraction_of_rows": rpulls / max(pulls, 1.0),
                 "nvlink_gbs_per_dir_actual": link_bytes_dir / t_s / 1e9 if world > 1 else 0.0,
                 "nvlink_frac_of_measured_p2p": (link_roof_s / t_s) if world > 1 else None,
-                "nvlink_peaks_gbs": {"load": P2P_LOAD_GBS, "red_add": P2P_RED_GBS,
-                                     "source": "profiles/r1_2gpu/p2p_probe_2gpu.json"},
+                "nvlink_frac_of_symmetric_probe": (link_bytes_dir / t_s / 1e9 / P2P_SYMMETRIC_GBS) if world > 1 else None,
+                "nvlink_peaks_gbs": {"one_way_load": P2P_LOAD_GBS, "one_way_red_add": P2P_RED_GBS,
+                                     "all_gpus_pull_and_push": P2P_SYMMETRIC_GBS,
+                                     "source": "profiles/r1_2gpu/p2p_probe_2gpu.json, profiles/r2_2gpu/p2p_symmetric_2gpu.json"},
                 "hbm_gbs_modelled_from_counters": hbm_bytes / t_s / 1e9,
                 "hbm_frac_of_measured_copy_peak": hbm_bytes / t_s / 1e9 / hbm_peak,
                 "logical_rows_per_sec_if_uncombined": value}
