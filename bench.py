@@ -28,7 +28,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "mf_sgd_ratings_per_sec"
-DEFAULT_PULL_LIMIT = 65536
+DEFAULT_PULL_LIMIT = 262144
 # measured on this pool (profiles/r1_2gpu/p2p_probe_2gpu.json): per-direction P2P rates of the two access
 # types the fused kernels use; the NVLink roofline of a step is rows pulled / LOAD + rows pushed / RED
 P2P_LOAD_GBS, P2P_RED_GBS = 759.0, 687.0

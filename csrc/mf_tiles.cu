@@ -43,7 +43,7 @@ constexpr int TL_THREADS = 256;
 constexpr int TL_MAX_TILE = 2048;
 constexpr int TL_MAX_BUCKETS = 16384;
 constexpr int TL_BUCKET_TARGET = 256;   // average records per bucket
-constexpr int TL_RUN_FLUSH = 32;   // records of one run after which the combined delta is pushed
+constexpr int TL_RUN_FLUSH = 32;   // records of one run after which the combined delta is published (less under a limiter)
 constexpr int TL_RU = 4;           // user rows in flight per warp (staged path)
 constexpr int TL_RI = 2;           // item rows in flight per warp (staged path)
 constexpr size_t TL_HDR_BYTES = 2 * TL_MAX_BUCKETS * sizeof(int);   // counts + cursors (= bucket ends after the scatter)
@@ -438,7 +438,8 @@ __device__ __forceinline__ void tcarry_exchange(TCarry<LANES, VPL>& cy, int nvec
 // the SGD step of one record against the carried item row; `us` = user row as loaded
 template <int LANES, int VPL>
 __device__ __forceinline__ void tile_sgd(TCarry<LANES, VPL>& cy, const float4 (&us)[VPL], float* urow, float r,
-                                         bool active, int nvec, const FpsMfParams& p, TileCounters& c) {
+                                         bool active, int nvec, const FpsMfParams& p, int flush_every,
+                                         TileCounters& c) {
   const int lane = threadIdx.x % LANES;
   float dot = 0.f;
 #pragma unroll
@@ -472,7 +473,7 @@ __device__ __forceinline__ void tile_sgd(TCarry<LANES, VPL>& cy, const float4 (&
     }
   }
   if (lane == 0) c.loss += e * e;
-  if (++cy.run_len >= TL_RUN_FLUSH) tcarry_exchange<LANES, VPL>(cy, nvec, c);
+  if (++cy.run_len >= flush_every) tcarry_exchange<LANES, VPL>(cy, nvec, c);
 }
 
 // ---- register path: any rank, LANES lanes per record -----------------------------------------
@@ -480,7 +481,8 @@ template <int LANES, int VPL>
 __global__ void __launch_bounds__(TL_THREADS, (VPL == 1 ? 3 : 1))
 k_mf_tiles_reg(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
                const TileRec* __restrict__ recs, const int* __restrict__ tile_start, const FpsMfParams p, int tile_sz,
-               long long n_tiles, long long tile_mul, int active_groups, int cta_credits, FpsFlow* flow) {
+               long long n_tiles, long long tile_mul, int active_groups, int cta_credits, int flush_every,
+               FpsFlow* flow) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   TileRec* s_rec = reinterpret_cast<TileRec*>(s_raw);
   unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_raw + (size_t)tile_sz * sizeof(TileRec));
@@ -567,7 +569,7 @@ k_mf_tiles_reg(const __grid_constant__ FpsTableView items, const __grid_constant
         }
       }
       load_user(k + 1, nxt_us, nxt_urow, nxt_user);
-      tile_sgd<LANES, VPL>(cy, us, urow, r, active, nvec, p, c);
+      tile_sgd<LANES, VPL>(cy, us, urow, r, active, nvec, p, flush_every, c);
       // the row prefetched for the next record was read before this record's store: reload on a clash
       if (active && nxt_user == user && nxt_urow != nullptr) {
 #pragma unroll
@@ -595,7 +597,7 @@ __global__ void __launch_bounds__(TL_THREADS, 4)
 k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
                const TileRec* __restrict__ recs, const int* __restrict__ tile_start, const FpsMfParams p, int tile_sz,
                long long n_tiles, long long tile_mul, int item_depth, int active_warps, int cta_credits,
-               FpsFlow* flow) {
+               int flush_every, FpsFlow* flow) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   TileRec* s_rec = reinterpret_cast<TileRec*>(s_raw);
   unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_raw + (size_t)tile_sz * sizeof(TileRec));
@@ -715,7 +717,7 @@ k_mf_tiles_tma(const __grid_constant__ FpsTableView items, const __grid_constant
         ++runs_consumed;
         pump_items(item_depth);
       }
-      tile_sgd<32, 1>(cy, us, urow, r.rating, true, nvec, p, c);
+      tile_sgd<32, 1>(cy, us, urow, r.rating, true, nvec, p, flush_every, c);
     }
     if (cy.item >= 0 && cy.run_len > 0) tcarry_push<32, 1>(cy, nvec, c);
     __syncthreads();
@@ -812,29 +814,36 @@ int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, void*
   const int sms = fps_num_sms();
   const bool staged = lanes == 32 && vpl == 1 && params->unroll != 1;
   long long blocks = n_tiles;
-  // Limiter: the limit is split into per-CTA allowances.  Spread them as widely as possible (one
-  // item row outstanding per walker first, then deeper rings) - the same number of credits moves
-  // more bytes from 148 SMs than from a few.  A walker's outstanding pulls = the carried row (in
-  // compute, its push not yet issued) + the item rows its ring prefetches.
+  // Limiter.  What the reference bounds is the number of records whose pull has not been answered and
+  // processed yet (M/WorkerLogic.scala:176-225); here a record is "in flight" while the row it was computed
+  // against has not been refreshed from the owner and its delta not been published: a walker holds up to
+  // `depth` item rows (the carried one + its ring) and, inside a run, up to 2 * flush_every unpublished
+  // records (one flush period gathered, one on its way).  The limit is split evenly over the walkers of
+  // all CTAs that can be resident; each CTA takes its share from FpsFlow.in_flight once.  A small limit
+  // therefore shortens the flush period first (more push-and-refresh round trips on hot items = the
+  // feedback that keeps Hogwild stable on small hot tables), then thins the rings, then the grid.
   const int walkers_full = staged ? TL_THREADS / 32 : gpb;   // (sub-)warps per CTA that pull
   const int depth_max = staged ? TL_RI + 1 : 1;
-  int active_groups = 0, item_depth = TL_RI, cta_credits = 0;
+  int active_groups = 0, item_depth = TL_RI, cta_credits = 0, flush_every = TL_RUN_FLUSH;
   if (params->pull_limit > 0) {
     const long long limit = params->pull_limit;
-    const long long resident = (long long)sms * (2048 / TL_THREADS);   // most CTAs the hardware can keep resident
-    int walkers = walkers_full, depth = 1;
+    const long long resident = (long long)sms * 4;    // CTAs per SM the kernels' registers / shared memory allow
+    int walkers = walkers_full;
+    long long per_walker = 1;
     if (limit < walkers_full) {                       // fewer credits than walkers in one CTA
       active_groups = walkers = (int)limit;
       blocks = 1;
     } else {
-      for (depth = depth_max; depth > 1 && resident * walkers * depth > limit; --depth) {}
-      if (resident * walkers * depth > limit) {       // not even one row per walker fits: fewer, persistent CTAs
-        const long long ctas = limit / walkers;
-        if (blocks > ctas) blocks = ctas;
-      }                                               // else: the full grid - only `resident` CTAs hold credits at a time
+      long long ctas = limit / walkers;               // at least one credit per walker
+      if (ctas > resident) ctas = resident;
+      per_walker = limit / (ctas * walkers);
+      if (ctas < resident && blocks > ctas) blocks = ctas;   // else the full grid: only `resident` CTAs hold credits at a time
     }
+    if (per_walker > 2 * TL_RUN_FLUSH) per_walker = 2 * TL_RUN_FLUSH;
+    const int depth = (int)(per_walker < depth_max ? per_walker : depth_max);
+    flush_every = (int)(per_walker / 2 > 0 ? per_walker / 2 : 1);
     item_depth = depth - 1;
-    cta_credits = walkers * depth;
+    cta_credits = walkers * (int)per_walker;
   }
   const size_t smem_base = (size_t)tile_sz * (sizeof(TileRec) + 8);
   static bool attr_done[64] = {false};
@@ -858,9 +867,9 @@ int fps_mf_sgd_tiles(const FpsTableView* items, const FpsTableView* users, void*
   if (staged) {
     const size_t smem = smem_base + (TL_THREADS / 32) * sizeof(WarpRing);
     k_mf_tiles_tma<<<(int)blocks, TL_THREADS, smem, st>>>(*items, *users, recs, tile_start, *params, tile_sz, n_tiles, tile_mul,
-                                                          item_depth, active_groups, cta_credits, d_flow);
+                                                          item_depth, active_groups, cta_credits, flush_every, d_flow);
   } else {
-#define LAUNCH(L, V) k_mf_tiles_reg<L, V><<<(int)blocks, TL_THREADS, smem_base, st>>>(*items, *users, recs, tile_start, *params, tile_sz, n_tiles, tile_mul, active_groups, cta_credits, d_flow)
+#define LAUNCH(L, V) k_mf_tiles_reg<L, V><<<(int)blocks, TL_THREADS, smem_base, st>>>(*items, *users, recs, tile_start, *params, tile_sz, n_tiles, tile_mul, active_groups, cta_credits, flush_every, d_flow)
     if (vpl == 1) {
       switch (lanes) {
         case 1: LAUNCH(1, 1); break;

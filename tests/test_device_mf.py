@@ -322,7 +322,8 @@ def test_tiles_single_walker_is_the_serial_rule_even_with_repeated_users(native,
     order = np.argsort(i, kind="stable")
     U, V = serial_sgd_oracle(u[order], i[order], r[order], U0, V0, 0.05, 0.01)
     s = mf.stats()
-    assert s["records"] == n and s["pulls"] == ni and s["max_in_flight"] == 1 and s["in_flight"] == 0
+    # limit 1 = one record in flight: the lone walker publishes and refreshes after every record of a run
+    assert s["records"] == n and s["pulls"] == ni + n and s["max_in_flight"] == 1 and s["in_flight"] == 0
     np.testing.assert_allclose(mf.items.gather(torch.arange(ni)).cpu().numpy(), V, rtol=5e-4, atol=5e-5)
     np.testing.assert_allclose(mf.users.gather(torch.arange(nu)).cpu().numpy(), U, rtol=5e-4, atol=5e-5)
 
