@@ -68,6 +68,8 @@ def param_update_mode(fn: Optional[Callable]) -> Optional[str]:
     """The table update mode a ``param_update`` callable stands for, or ``None``."""
     if fn is None:
         return None
+    if isinstance(fn, str):
+        return fn if fn in UPDATE_MODES else None
     tagged = getattr(fn, "device_update_mode", None)
     if tagged in UPDATE_MODES:
         return tagged
@@ -217,3 +219,97 @@ def _ensure_builtin_runners() -> None:
                                               pull_limit=job.pull_limit, long_id=job.logic.long_id,
                                               n_shards=_n_shards(job), **job.extra)
         return out
+
+
+# ---------------------------------------------------------------------------------------------
+# generic device runtime for user logics written as tensor programs
+# ---------------------------------------------------------------------------------------------
+class TensorWorkerLogic:
+    """A user worker logic for the device engine: the per-record callbacks of ``WorkerLogic``
+    (``M/WorkerLogic.scala:23-58``) restated per *batch*, with tensors instead of messages.
+
+    For every input batch the engine (1) asks ``pull_ids(batch)`` which parameters the batch needs,
+    (2) pulls those rows from their owner shards with one gather kernel (P2P loads over NVLink for
+    remote shards; lazy ``param_init`` applies), (3) calls ``on_pull_batch(batch, ids, rows)``, any
+    torch program, which returns ``(push_ids, deltas, outputs)``, (4) applies ``param_update`` to
+    ``push_ids`` on the owner shards with one scatter kernel (``add`` = remote ``red.add``,
+    ``overwrite``, ``add_norm``) and appends ``outputs`` (a tensor or ``None``) to the worker side of
+    the output stream.  Semantics are the asynchronous ones: no barrier between ranks, every rank
+    runs its own batches; ``pull_limit`` caps the rows pulled per gather (a larger batch is pulled,
+    processed and pushed in slices)."""
+
+    def open(self, table, ctx) -> None:        # table: ops.table.ShardedTable
+        pass
+
+    def pull_ids(self, batch):
+        raise NotImplementedError
+
+    def on_pull_batch(self, batch, ids, rows):
+        raise NotImplementedError
+
+    def close(self) -> None:
+        pass
+
+
+def run_tensor_logic(batches, logic: TensorWorkerLogic, n_ids: int, dim: int, *, init_range=(0.0, 0.0),
+                     update_mode: str = "add", pull_limit: int = 0, lazy: bool = True, partition: str = "hash",
+                     seed: int = 0, n_shards=None, aux_cols: int = 0, return_table: bool = False):
+    """The device twin of ``transform`` for a ``TensorWorkerLogic``.  Returns the output stream:
+    ``Left(output tensor)`` per batch that produced one, then ``Right((id, row))`` for every live row of
+    the local shard (on-close form)."""
+    import torch
+    from ..entities import Left, Right
+    from ..ops import philox
+    from ..ops.table import ShardedTable, new_flow
+    from .device_context import get_context
+    if update_mode not in UPDATE_MODES:
+        raise ValueError(f"update_mode must be one of {UPDATE_MODES}")
+    ctx = get_context()
+    table = ShardedTable(n_ids, dim, n_shards=n_shards, partition=partition, init_range=init_range, seed=seed,
+                         stream_tag=philox.STREAM_ITEM, lazy=lazy, aux_cols=aux_cols, ctx=ctx)
+    flow = new_flow()
+    logic.open(table, ctx)
+    out = []
+    for batch in batches:
+        ids = logic.pull_ids(batch)
+        ids = ids.to(device="cuda", dtype=torch.int64)
+        step = int(pull_limit) if pull_limit and pull_limit > 0 else max(int(ids.numel()), 1)
+        for s in range(0, max(int(ids.numel()), 1), step):
+            part = ids[s:s + step]
+            sub = batch if step >= ids.numel() else _slice_batch(batch, s, s + step, ids.numel())
+            rows = table.gather(part, flow)
+            push_ids, deltas, produced = logic.on_pull_batch(sub, part, rows)
+            if push_ids is not None and push_ids.numel():
+                table.scatter(push_ids, deltas, update_mode, flow)
+            if produced is not None:
+                out.append(Left(produced))
+    logic.close()
+    torch.cuda.synchronize()
+    ctx.barrier()
+    ids, rows = table.dump()
+    rows_np = rows.cpu().numpy()
+    out.extend(Right((int(k), v)) for k, v in zip(ids.tolist(), rows_np))
+    return (out, table, flow) if return_table else out
+
+
+def _slice_batch(batch, lo: int, hi: int, n: int):
+    """Slices every tensor of a batch (tensor, tuple / list / dict of tensors) whose first dimension is
+    the batch length; anything else is passed through."""
+    import torch
+    if isinstance(batch, torch.Tensor):
+        return batch[lo:hi] if batch.dim() and batch.shape[0] == n else batch
+    if isinstance(batch, (tuple, list)):
+        return type(batch)(_slice_batch(b, lo, hi, n) for b in batch)
+    if isinstance(batch, dict):
+        return {k: _slice_batch(v, lo, hi, n) for k, v in batch.items()}
+    return batch
+
+
+@register_device_logic(TensorWorkerLogic)
+def _run_tensor_job(job: DeviceJob) -> list:
+    kw = dict(job.extra)
+    n_ids, dim = kw.pop("n_ids", None), kw.pop("dim", None)
+    if n_ids is None or dim is None:
+        raise ValueError("a TensorWorkerLogic job needs device_kw={'n_ids': ..., 'dim': ...}")
+    return run_tensor_logic(job.records, job.logic, n_ids, dim, update_mode=job.update_mode or "add",
+                            pull_limit=job.pull_limit, **kw)

@@ -208,3 +208,42 @@ def test_offline_pa_jobs_on_both_engines(engine):
     preds = lefts(out)
     assert len(preds) == 20 and {p for _l, p, _v in preds} <= set(range(5))
     assert sum(1 for l, p, _v in preds if l == p) / 20 >= 0.35          # chance is 0.2; 20 test records are noisy
+
+
+@pytest.mark.gpu
+def test_user_tensor_logic_runs_on_the_device_engine_through_transform():
+    """A user-defined logic written as a tensor program (``TensorWorkerLogic``): pull the ids of the batch,
+    push +1 to each and +10 to id 0, output the sum of the pulled rows.  Through ``transform(engine="device")``
+    with a pull limit smaller than the batch (the batch is pulled and pushed in slices)."""
+    import torch
+    from fps_b200.parallel.device_engine import TensorWorkerLogic
+
+    class Count(TensorWorkerLogic):
+        def pull_ids(self, batch):
+            return batch
+
+        def on_pull_batch(self, batch, ids, rows):
+            ones = torch.ones((ids.numel(), 3), device="cuda")
+            push_ids = torch.cat([ids, torch.zeros(1, dtype=torch.int64, device="cuda")])
+            deltas = torch.cat([ones, torch.full((1, 3), 10.0, device="cuda")])
+            return push_ids, deltas, rows[:, :3].sum(dim=0)
+
+    g = torch.Generator().manual_seed(0)
+    batches = [torch.randint(1, 50, (200,), generator=g) for _ in range(5)]
+    with warnings.catch_warnings():
+        warnings.simplefilter("error", DE.DeviceFallbackWarning)
+        out = transform(batches, add_pull_limiter(Count(), 64), None, "add", 1, 3, 10, engine="device",
+                        device_kw=dict(n_ids=50, dim=3, init_range=(0.0, 0.0), n_shards=3))
+    counts = torch.bincount(torch.cat(batches), minlength=50).numpy()
+    model = last_write_wins(rights(out))
+    slices = sum((len(b) + 63) // 64 for b in batches)
+    assert len(lefts(out)) == slices
+    for k in range(1, 50):
+        if counts[k]:
+            np.testing.assert_allclose(model[k], np.full(3, counts[k]), rtol=0, atol=1e-5)
+        else:
+            assert k not in model                    # lazy table: never touched, never dumped
+    np.testing.assert_allclose(model[0], np.full(3, 10.0 * slices), rtol=0, atol=1e-4)
+    # the worker outputs are the sums of the rows as pulled: monotone over the job
+    sums = [float(v[0]) for v in lefts(out)]
+    assert sums[0] >= 0 and sums[-1] > sums[0]
