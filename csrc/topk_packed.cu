@@ -147,6 +147,16 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t leader, uint32_t d_tmem, u
       ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(TK_IDESC), "r"(ACC ? 1u : 0u), "r"(leader)
       : "memory");
 }
+template <bool ACC>
+__device__ __forceinline__ void umma_tf32_ts_i(uint32_t leader, uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t"
+      "setp.ne.b32 e, %5, 0;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(ACC ? 1u : 0u), "r"(leader)
+      : "memory");
+}
 __device__ __forceinline__ void umma_commit_elected(uint32_t leader, uint64_t* bar) {
   asm volatile(
       "{\n\t.reg .pred e;\n\t"
@@ -208,8 +218,9 @@ __device__ __forceinline__ void select32(const float (&v)[32], float theta, int 
 // Warp-cooperative exact prune of one row-major list (c > k entries, c <= TK_CAP = 8 per lane) back to
 // its k best; returns the k-th best score.  Everything after the 16 coalesced loads runs in
 // registers: common-prefix skip, then one REDUX per remaining key bit, then a ballot compaction.
+template <int CAP = TK_CAP>
 __device__ __forceinline__ float prune_row(float* rs, int* ri, int c, int k, int lane) {
-  constexpr int PER = TK_CAP / 32;
+  constexpr int PER = CAP / 32;
   uint32_t key[PER];
   int id[PER];
 #pragma unroll
@@ -498,6 +509,336 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
   if (warp == n_sel_warps) tmem_dealloc(tmem_base, TP_TMEM_COLS);
 }
 
+// =================================================================================================
+// Wide variant: 128-item tiles (UMMA N = 128), K-block-sized pipeline stages.
+//
+// ncu of the 64-item kernel (profiles/r2_topk): the selection warps spend 34 % of their samples waiting
+// for accumulators, the MMA warp is throttled on issue, yet the tensor pipe is active only 61 % of the
+// SM-active cycles - an M128 x N64 x K8 tf32 MMA is about 35 cycles of math, too short against the fixed
+// cost of each instruction.  Doubling N doubles the math per instruction.  A 128-item tile with both
+// tf32 images is 128 KB at rank 128, so a stage is one K block of a tile ([hi | lo], 32 KB) and the
+// MMA warp accumulates over the tile's K-block stages - the K loop of a GEMM - before it commits the
+// accumulator.  TMEM: two 128-column accumulators + the 2 x 128 query columns.
+// =================================================================================================
+constexpr int W_N = 128;              // items per tile
+constexpr int W_STAGES = 6;           // shared-memory stages of one K block each (32 KB)
+constexpr int W_ACC = 2;              // TMEM accumulators of W_N columns
+constexpr int W_CAP = 512;            // candidate slots per (CTA, query): a tile may add W_N
+constexpr int W_THREADS = 6 * 32;     // 4 selection warps + producer + MMA issuer
+constexpr int W_SLAB = W_N * TK_KB;   // floats of one [128 x 128 B] image
+constexpr uint32_t W_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(W_N >> 3) << 17) | ((uint32_t)(TK_M >> 4) << 24);
+
+__global__ void __launch_bounds__(256)
+k_pack_items_wide(const float* __restrict__ items, int stride, long long n_items, int dim, int kblks,
+                  float* __restrict__ packed) {
+  const long long tile = blockIdx.x;
+  const long long i0 = tile * W_N;
+  float* out = packed + tile * 2 * (long long)kblks * W_SLAB;
+  const int chunks_per_row = kblks * 8;
+  for (int i = threadIdx.x; i < W_N * chunks_per_row; i += blockDim.x) {
+    const int r = i / chunks_per_row, cc = i - r * chunks_per_row;
+    const int kb = cc >> 3, c = cc & 7;
+    const int col = kb * TK_KB + c * 4;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i0 + r < n_items && col < dim) {
+      const float* p = items + (i0 + r) * stride + col;
+      if (col + 3 < dim) x = *reinterpret_cast<const float4*>(p);
+      else {
+        x.x = p[0];
+        if (col + 1 < dim) x.y = p[1];
+        if (col + 2 < dim) x.z = p[2];
+      }
+    }
+    float4 h, l;
+    h.x = to_tf32(x.x); h.y = to_tf32(x.y); h.z = to_tf32(x.z); h.w = to_tf32(x.w);
+    l.x = to_tf32(x.x - h.x); l.y = to_tf32(x.y - h.y); l.z = to_tf32(x.z - h.z); l.w = to_tf32(x.w - h.w);
+    // stage (tile, kb) = [hi slab | lo slab], rows swizzled like every K-major SWIZZLE_128B operand
+    const int off = kb * 2 * W_SLAB + r * TK_KB + ((c ^ (r & 7)) << 2);
+    *reinterpret_cast<float4*>(out + off) = h;
+    *reinterpret_cast<float4*>(out + off + W_SLAB) = l;
+  }
+}
+
+struct WideShared {
+  uint64_t b_full[W_STAGES];
+  uint64_t stage_free[W_STAGES];
+  uint64_t acc_full[W_ACC];
+  uint64_t acc_empty[W_ACC];
+  uint32_t tmem;
+  volatile int skip_from[4];
+  volatile int issued_final;
+  float qlen[TK_M];
+};
+
+__global__ void __launch_bounds__(W_THREADS, 1)
+k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
+                 const float* __restrict__ packed, const float* __restrict__ item_len,
+                 const int* __restrict__ item_ids, long long n_items, int dim, int kblks, int k, int n_splits,
+                 int use_pruning, TopkScratch sc, unsigned long long* __restrict__ stats) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  float* sB = (float*)base;                 // W_STAGES x [hi slab | lo slab]
+  __shared__ WideShared sh;
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int qt = blockIdx.x / n_splits, split = blockIdx.x - qt * n_splits;
+  const long long q0 = (long long)qt * TK_M;
+  const int q_valid = (int)min((long long)TK_M, n_q - q0);
+  const long long n_tiles = (n_items + W_N - 1) / W_N;
+  const int my_tiles = n_tiles > split ? (int)((n_tiles - split + n_splits - 1) / n_splits) : 0;
+  constexpr uint32_t STAGE_BYTES = 2u * W_SLAB * sizeof(float);
+  const long long tile_floats = 2ll * kblks * W_SLAB;
+
+  if (warp == 4) tmem_alloc((uint32_t*)&sh.tmem, TP_TMEM_COLS);
+  if (t == 0) {
+    for (int s = 0; s < W_STAGES; ++s) {
+      mbar_init(&sh.b_full[s], 1);
+      mbar_init(&sh.stage_free[s], 1);
+    }
+    for (int b = 0; b < W_ACC; ++b) {
+      mbar_init(&sh.acc_full[b], 1);
+      mbar_init(&sh.acc_empty[b], 4);
+    }
+    sh.issued_final = -1;
+    for (int w = 0; w < 4; ++w) sh.skip_from[w] = 0x7fffffff;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sh.tmem;
+  const uint32_t tmem_a_hi = tmem_base + TP_A_COL, tmem_a_lo = tmem_base + TP_A_COL + 128;
+
+  // ---- queries -> TMEM (thread t = lane t = query t), split into tf32 hi / lo on the way
+  if (warp < 4) {
+    const float* qp = queries + (q0 + t) * q_stride;
+    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+    float s = 0.f;
+    for (int c0 = 0; c0 < kblks * TK_KB; c0 += 32) {
+      float hi[32], lo[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int col = c0 + j;
+        const float x = (t < q_valid && col < dim) ? qp[col] : 0.f;
+        s = fmaf(x, x, s);
+        hi[j] = to_tf32(x);
+        lo[j] = to_tf32(x - hi[j]);
+      }
+      tmem_st32(tmem_a_hi + lane_off + c0, hi);
+      tmem_st32(tmem_a_lo + lane_off + c0, lo);
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    sh.qlen[t] = sqrtf(s);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+
+  if (warp == 4) {
+    // ===================== producer: one bulk copy pair per (tile, K block) =====================
+    if (lane == 0) {
+      int issued = 0;
+      long long g = 0;                                    // stage ordinal
+      for (int j = 0; j < my_tiles; ++j) {
+        if (use_pruning) {
+          bool all = true;
+          for (int sub = 0; sub < 4; ++sub) all = all && (sh.skip_from[sub] <= j);
+          if (all) break;                                                      // LEMP early exit
+        }
+        const long long tile = split + (long long)j * n_splits;
+        const float* src = packed + tile * tile_floats;
+        for (int kb = 0; kb < kblks; ++kb, ++g) {
+          const int s = (int)(g % W_STAGES);
+          const long long n = g / W_STAGES;
+          if (n > 0) mbar_wait(&sh.stage_free[s], (uint32_t)((n - 1) & 1));
+          float* dst = sB + (size_t)s * 2 * W_SLAB;
+          mbar_expect_tx(&sh.b_full[s], STAGE_BYTES);
+          tma_bulk_g2s(dst, src + (size_t)kb * 2 * W_SLAB, W_SLAB * 4, &sh.b_full[s]);
+          tma_bulk_g2s(dst + W_SLAB, src + (size_t)kb * 2 * W_SLAB + W_SLAB, W_SLAB * 4, &sh.b_full[s]);
+        }
+        issued = j + 1;
+      }
+      __threadfence_block();
+      sh.issued_final = issued;
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+    const uint32_t leader = elect_one();
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t a_hi = tb + TP_A_COL, a_lo = tb + TP_A_COL + 128;
+    long long g = 0;
+    for (int j = 0; j < my_tiles; ++j) {
+      const int b = j % W_ACC;
+      bool have = true;
+      for (int kb = 0; kb < kblks; ++kb, ++g) {
+        const int s = (int)(g % W_STAGES);
+        const uint32_t par = (uint32_t)((g / W_STAGES) & 1);
+        if (kb == 0) {
+          // the first stage of a tile may never come (the producer stopped): watch issued_final too
+          have = false;
+          while (true) {
+            if (mbar_try(&sh.b_full[s], par)) { have = true; break; }
+            const int fin = sh.issued_final;
+            if (fin >= 0 && j >= fin) break;
+          }
+          have = __shfl_sync(0xffffffffu, have ? 1 : 0, 0) != 0;
+          if (!have) break;
+          if (j >= W_ACC) mbar_wait(&sh.acc_empty[b], (uint32_t)(((j / W_ACC) - 1) & 1));   // accumulator drained
+        } else {
+          mbar_wait(&sh.b_full[s], par);
+        }
+        tc_fence_after();
+        const uint32_t acc_addr = tb + (uint32_t)b * W_N;
+        const uint64_t d0 = make_desc(smem_u32(sB + (size_t)s * 2 * W_SLAB));
+        constexpr uint64_t LO_OFF = ((uint64_t)W_SLAB * 4) >> 4;
+#pragma unroll
+        for (int ks = 0; ks < TK_KB / 8; ++ks) {
+          const uint32_t a_col = (uint32_t)(kb * TK_KB + ks * 8);
+          const uint64_t bh = d0 + (uint64_t)(ks * 2), bl = bh + LO_OFF;
+          if (kb == 0 && ks == 0) umma_tf32_ts_i<false>(leader, acc_addr, a_lo + a_col, bh, W_IDESC);   // small terms first
+          else umma_tf32_ts_i<true>(leader, acc_addr, a_lo + a_col, bh, W_IDESC);
+          umma_tf32_ts_i<true>(leader, acc_addr, a_hi + a_col, bl, W_IDESC);
+          umma_tf32_ts_i<true>(leader, acc_addr, a_hi + a_col, bh, W_IDESC);
+        }
+        umma_commit_elected(leader, &sh.stage_free[s]);
+      }
+      if (!have) break;
+      umma_commit_elected(leader, &sh.acc_full[b]);
+    }
+  } else {
+    // ===================== selection warps: thread = TMEM lane = query =====================
+    const int sub = warp & 3;
+    const int tq = sub * 32 + lane;
+    const size_t row0 = ((size_t)blockIdx.x * TK_M + sub * 32) * W_CAP;       // this warp's 32 lists
+    float* const rs_w = sc.cand_s + row0;
+    int* const ri_w = sc.cand_i + row0;
+    float* const rs = rs_w + (size_t)lane * W_CAP;
+    int* const ri = ri_w + (size_t)lane * W_CAP;
+    volatile uint32_t* theta_g = sc.theta + q0 + tq;
+    const bool q_ok = tq < q_valid;
+    const float qlen = sh.qlen[tq];
+    int cnt = 0;
+    float theta = q_ok ? -INFINITY : INFINITY;           // padding queries never accept anything
+    unsigned long long tiles_done = 0, accepted = 0, prunes = 0;
+    for (int j = 0; j < my_tiles; ++j) {
+      const int b = j % W_ACC;
+      const uint32_t theta_key = *theta_g;
+      bool have = false;
+      while (true) {
+        if (mbar_try(&sh.acc_full[b], (uint32_t)((j / W_ACC) & 1))) { have = true; break; }
+        const int fin = sh.issued_final;
+        if (fin >= 0 && j >= fin) break;
+      }
+      if (!have) break;
+      tc_fence_after();
+      const long long tile = split + (long long)j * n_splits;
+      const long long i0 = tile * W_N;
+      const int i_valid = (int)min((long long)W_N, n_items - i0);
+      float v[4][32];
+      const uint32_t lane_addr = tmem_base + ((uint32_t)(sub * 32) << 16) + (uint32_t)b * W_N;
+#pragma unroll
+      for (int h = 0; h < 4; ++h) tmem_ld32(lane_addr + 32 * h, v[h]);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sh.acc_empty[b]);       // the MMAs of tile j + 2 may overwrite it now
+      if (q_ok) theta = fmaxf(theta, key2f(theta_key));
+      if (i_valid < W_N) {                                 // ragged last tile
+#pragma unroll
+        for (int h = 0; h < 4; ++h)
+#pragma unroll
+          for (int jj = 0; jj < 32; ++jj)
+            if (32 * h + jj >= i_valid) v[h][jj] = -INFINITY;
+      }
+      const int before = cnt;
+#pragma unroll
+      for (int h = 0; h < 4; ++h) select32(v[h], theta, (int)i0 + 32 * h, rs, ri, cnt);
+      accepted += (unsigned)(cnt - before);
+      if (__any_sync(0xffffffffu, cnt > W_CAP - W_N)) {
+        __syncwarp();
+        for (int src = 0; src < 32; ++src) {
+          const int c = __shfl_sync(0xffffffffu, cnt, src);
+          if (c > k) {
+            const float th = prune_row<W_CAP>(rs_w + (size_t)src * W_CAP, ri_w + (size_t)src * W_CAP, c, k, lane);
+            if (lane == src) {
+              cnt = k;
+              theta = fmaxf(theta, th);
+              ++prunes;
+              atomicMax((uint32_t*)theta_g, f2key(theta));
+            }
+          }
+        }
+        __syncwarp();
+      }
+      ++tiles_done;
+      if (use_pruning && j + 1 < my_tiles) {
+        const long long nxt = (split + (long long)(j + 1) * n_splits) * W_N;
+        const bool can_skip = !q_ok || (theta > -INFINITY && qlen * item_len[nxt] <= theta);
+        if (__all_sync(0xffffffffu, can_skip) && lane == 0 && sh.skip_from[warp] == 0x7fffffff) sh.skip_from[warp] = j + 1;
+      }
+    }
+    // final prune + partial list of (query, split), one list at a time by the whole warp
+    __syncwarp();
+    for (int src = 0; src < 32; ++src) {
+      const int qi = sub * 32 + src;
+      if (qi >= q_valid) break;                          // warp-uniform
+      int c = __shfl_sync(0xffffffffu, cnt, src);
+      float* r_s = rs_w + (size_t)src * W_CAP;
+      int* r_i = ri_w + (size_t)src * W_CAP;
+      if (c > k) {
+        prune_row<W_CAP>(r_s, r_i, c, k, lane);
+        c = k;
+        __syncwarp();
+      }
+      const size_t part = ((size_t)(q0 + qi) * n_splits + (size_t)split) * k;
+      for (int jj = lane; jj < k; jj += 32) {
+        const bool in = jj < c;
+        const int slot = in ? r_i[jj] : -1;
+        sc.part_s[part + jj] = in ? r_s[jj] : -INFINITY;
+        sc.part_i[part + jj] = in ? (item_ids ? item_ids[slot] : slot) : -1;
+      }
+    }
+    if (stats != nullptr) {
+      if (tq == 0) {
+        atomicAdd(&stats[0], tiles_done);
+        atomicAdd(&stats[1], (unsigned long long)my_tiles);
+      }
+      if (q_ok) atomicAdd(&stats[2], accepted);
+      if (prunes) atomicAdd(&stats[3], prunes);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem_base, TP_TMEM_COLS);
+}
+
+// scratch plan of the wide kernel: as make_plan, with 128-item tiles, W_CAP slots per list, one group
+Plan make_plan_wide(long long n_q, int k, long long n_items, int dim) {
+  Plan p;
+  p.n_q_tiles = (int)((n_q + TK_M - 1) / TK_M);
+  const long long n_tiles = (n_items + W_N - 1) / W_N;
+  const int sms = fps_num_sms();
+  long long splits = sms / (p.n_q_tiles > 0 ? p.n_q_tiles : 1);
+  if (splits < 1) splits = 1;
+  if (splits > 16) splits = 16;
+  if (splits > n_tiles) splits = n_tiles > 0 ? n_tiles : 1;
+  p.n_splits = (int)splits;
+  p.n_ctas = p.n_q_tiles * p.n_splits;
+  p.kblks = (dim + TK_KB - 1) / TK_KB;
+  auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  size_t o = 0;
+  o = align(o + (size_t)p.n_ctas * W_CAP * TK_M * sizeof(float));
+  p.off_cand_i = o;
+  o = align(o + (size_t)p.n_ctas * W_CAP * TK_M * sizeof(int));
+  p.off_theta = o;
+  o = align(o + (size_t)p.n_q_tiles * TK_M * sizeof(uint32_t));
+  p.off_part_s = o;
+  o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * k * sizeof(float));
+  p.off_part_i = o;
+  o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * k * sizeof(int));
+  p.total = o;
+  return p;
+}
+
 int packed_groups() {
   static int g = -1;
   if (g < 0) {
@@ -594,6 +935,58 @@ int fps_lemp_topk_packed(const float* d_queries, int32_t q_stride, int64_t n_q, 
                                                                     (unsigned long long*)d_stats);
   FPS_LAUNCH_CHECK();
   return launch_merge(sc.part_s, sc.part_i, p.n_splits * groups, n_q, k, k, nullptr, 0, d_out_scores, d_out_ids, st);
+}
+
+/* ---- wide variant (128-item tiles) ------------------------------------------------------------- */
+size_t fps_topk_wide_packed_bytes(int64_t n_items, int32_t dim) {
+  if (n_items <= 0 || dim <= 0 || dim > 128) return 0;
+  const int kblks = (dim + TK_KB - 1) / TK_KB;
+  const size_t n_tiles = (size_t)((n_items + W_N - 1) / W_N);
+  return n_tiles * 2 * (size_t)kblks * W_SLAB * sizeof(float);
+}
+
+size_t fps_topk_wide_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items) {
+  if (n_q <= 0 || k <= 0 || n_items <= 0) return 0;
+  return make_plan_wide(n_q, k, n_items, 128).total;
+}
+
+int fps_topk_pack_items_wide(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim, void* d_packed,
+                             void* stream) {
+  FPS_REQUIRE(d_items && d_packed && n_items > 0 && dim > 0 && dim <= 128 && item_stride % 4 == 0, FPS_E_INVALID,
+              "fps_topk_pack_items_wide: bad arguments (rank must be <= 128, stride a multiple of 4)");
+  const int kblks = (dim + TK_KB - 1) / TK_KB;
+  const long long n_tiles = (n_items + W_N - 1) / W_N;
+  k_pack_items_wide<<<(unsigned)n_tiles, 256, 0, (cudaStream_t)stream>>>(d_items, item_stride, n_items, dim, kblks, (float*)d_packed);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int fps_lemp_topk_wide(const float* d_queries, int32_t q_stride, int64_t n_q, const void* d_packed,
+                       const float* d_item_len, const int32_t* d_item_ids, int64_t n_items, int32_t dim,
+                       int32_t k, int32_t use_pruning, void* d_scratch, size_t scratch_bytes,
+                       float* d_out_scores, int32_t* d_out_ids, uint64_t* d_stats, void* stream) {
+  FPS_REQUIRE(n_q > 0 && n_items > 0 && dim > 0, FPS_E_INVALID, "fps_lemp_topk_wide: empty problem");
+  FPS_REQUIRE(k >= 1 && k <= TK_MAX_K, FPS_E_TOO_LARGE, "fps_lemp_topk_wide: k = %d outside [1, %d]", k, TK_MAX_K);
+  FPS_REQUIRE(dim <= 128 && q_stride % 4 == 0, FPS_E_UNSUPPORTED, "fps_lemp_topk_wide: rank <= 128 and q_stride %% 4 == 0 required");
+  FPS_REQUIRE(!use_pruning || d_item_len != nullptr, FPS_E_INVALID, "fps_lemp_topk_wide: pruning needs item lengths");
+  cudaStream_t st = (cudaStream_t)stream;
+  const Plan p = make_plan_wide(n_q, k, n_items, dim);
+  FPS_REQUIRE(scratch_bytes >= p.total, FPS_E_INVALID, "fps_lemp_topk_wide: scratch too small (%zu < %zu)", scratch_bytes, p.total);
+  uint8_t* sb = (uint8_t*)d_scratch;
+  TopkScratch sc;
+  sc.cand_s = (float*)sb;
+  sc.cand_i = (int*)(sb + p.off_cand_i);
+  sc.theta = (uint32_t*)(sb + p.off_theta);
+  sc.part_s = (float*)(sb + p.off_part_s);
+  sc.part_i = (int*)(sb + p.off_part_i);
+  FPS_CUDA(cudaMemsetAsync(sc.theta, 0, (size_t)p.n_q_tiles * TK_M * sizeof(uint32_t), st));
+  const size_t smem = 1024 + (size_t)W_STAGES * 2 * W_SLAB * sizeof(float);
+  FPS_CUDA(cudaFuncSetAttribute(k_lemp_topk_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_lemp_topk_wide<<<p.n_ctas, W_THREADS, smem, st>>>(d_queries, q_stride, n_q, (const float*)d_packed, d_item_len,
+                                                      d_item_ids, n_items, dim, p.kblks, k, p.n_splits, use_pruning,
+                                                      sc, (unsigned long long*)d_stats);
+  FPS_LAUNCH_CHECK();
+  return launch_merge(sc.part_s, sc.part_i, p.n_splits, n_q, k, k, nullptr, 0, d_out_scores, d_out_ids, st);
 }
 
 }  // extern "C"

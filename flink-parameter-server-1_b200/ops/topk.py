@@ -76,16 +76,21 @@ class PackedItems:
     tensor cores read.  Built once per model refresh (``fps_topk_pack_items``), then streamed by
     the TMA engine on every query batch (``lemp_topk_packed``).  Costs 2x the fp32 item bytes."""
 
-    def __init__(self, items_sorted, item_len=None, item_ids=None):
+    def __init__(self, items_sorted, item_len=None, item_ids=None, wide=None):
+        """``wide``: 128-item tiles for the wide kernel (default; ``FPS_TOPK_WIDE=0`` or ``wide=False`` =
+        the 64-item layout of ``fps_lemp_topk_packed``)."""
+        import os
         import torch
         it = _pad4(items_sorted.float())
         self.n_items, self.dim = it.shape[0], items_sorted.shape[1]
-        nbytes = int(N.lib().fps_topk_packed_bytes(self.n_items, self.dim))
+        self.wide = (os.environ.get("FPS_TOPK_WIDE", "1") != "0") if wide is None else bool(wide)
+        L = N.lib()
+        nbytes = int((L.fps_topk_wide_packed_bytes if self.wide else L.fps_topk_packed_bytes)(self.n_items, self.dim))
         if nbytes == 0:
             raise ValueError("packed top-K supports ranks up to 128")
         self.data = torch.empty(nbytes, device="cuda", dtype=torch.uint8)
-        N.check(N.lib().fps_topk_pack_items(N.ptr(it), it.shape[1], self.n_items, self.dim, N.ptr(self.data),
-                                            N.current_stream()), "fps_topk_pack_items")
+        N.check((L.fps_topk_pack_items_wide if self.wide else L.fps_topk_pack_items)(
+            N.ptr(it), it.shape[1], self.n_items, self.dim, N.ptr(self.data), N.current_stream()), "fps_topk_pack_items")
         self.item_len = (torch.linalg.vector_norm(items_sorted.float(), dim=1) if item_len is None else item_len).contiguous()
         self.item_ids = None if item_ids is None else item_ids.int().contiguous()
 
@@ -97,13 +102,15 @@ def lemp_topk_packed(queries, packed: PackedItems, k: int, *, use_pruning: bool 
     assert queries.shape[1] == packed.dim
     q = _pad4(queries.float())
     n_q = q.shape[0]
-    if scratch is None:      # room for every selection group's candidate lists (a smaller caller buffer = fewer groups)
-        scratch = torch.empty(int(N.lib().fps_topk_packed_scratch_bytes(n_q, k, packed.n_items)), device="cuda",
-                              dtype=torch.uint8)
+    wide = getattr(packed, "wide", False)
+    need = int((N.lib().fps_topk_wide_scratch_bytes if wide else N.lib().fps_topk_packed_scratch_bytes)(n_q, k, packed.n_items))
+    if scratch is None or (wide and scratch.numel() < need):
+        # room for every selection group's candidate lists (a smaller caller buffer = fewer groups, 64-item path)
+        scratch = torch.empty(need, device="cuda", dtype=torch.uint8)
     out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
     out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
     with nvtx_range("fps.topk.packed"):
-        N.check(N.lib().fps_lemp_topk_packed(N.ptr(q), q.shape[1], n_q, N.ptr(packed.data), N.ptr(packed.item_len),
+        N.check((N.lib().fps_lemp_topk_wide if wide else N.lib().fps_lemp_topk_packed)(N.ptr(q), q.shape[1], n_q, N.ptr(packed.data), N.ptr(packed.item_len),
                                              N.ptr(packed.item_ids), packed.n_items, packed.dim, k, int(use_pruning),
                                              N.ptr(scratch), scratch.numel(), N.ptr(out_s), N.ptr(out_i),
                                              N.ptr(stats), N.current_stream()), "fps_lemp_topk_packed")

@@ -321,6 +321,18 @@ int fps_lemp_topk_packed(const float* d_queries, int32_t q_stride, int64_t n_q, 
                          int32_t dim, int32_t k, int32_t use_pruning, void* d_scratch,
                          size_t scratch_bytes, float* d_out_scores, int32_t* d_out_ids,
                          uint64_t* d_stats, void* stream);
+/* Wide variant of the packed path: 128-item tiles (one tcgen05.mma covers N = 128, twice the math per
+ * instruction), shared-memory stages of one K block, two TMEM accumulators.  Own packed layout
+ * (fps_topk_pack_items_wide), own scratch size; same results and arguments as fps_lemp_topk_packed.   */
+size_t fps_topk_wide_packed_bytes(int64_t n_items, int32_t dim);
+size_t fps_topk_wide_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items);
+int fps_topk_pack_items_wide(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim,
+                             void* d_packed, void* stream);
+int fps_lemp_topk_wide(const float* d_queries, int32_t q_stride, int64_t n_q, const void* d_packed,
+                       const float* d_item_len, const int32_t* d_item_ids, int64_t n_items,
+                       int32_t dim, int32_t k, int32_t use_pruning, void* d_scratch,
+                       size_t scratch_bytes, float* d_out_scores, int32_t* d_out_ids,
+                       uint64_t* d_stats, void* stream);
 /* fps_lemp_topk for callers that cannot allocate device memory - no counterpart in the reference.
  * Meant for request paths where a cudaMalloc may fail (all device memory is already spoken for by
  * a training job or another allocator) or would stall (it synchronises the device).  The scratch

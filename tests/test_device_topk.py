@@ -53,9 +53,10 @@ def test_tensor_core_topk_matches_reference(dim, n_q, n_items, k):
     assert stats[0].item() == stats[1].item()
 
 
+@pytest.mark.parametrize("wide", [False, True])
 @pytest.mark.parametrize("dim,n_q,n_items,k", [(10, 37, 1000, 10), (64, 200, 5000, 75), (128, 300, 20011, 100),
                                                 (96, 129, 70, 5), (128, 1024, 100_000, 50)])
-def test_packed_tma_pipeline_matches_reference(dim, n_q, n_items, k):
+def test_packed_tma_pipeline_matches_reference(dim, n_q, n_items, k, wide):
     """Pre-packed tiles + TMA + warp-specialised tcgen05 pipeline: same answers as the reference,
     with and without the LEMP early exit."""
     from fps_b200.ops.topk import PackedItems, lemp_topk_packed, sort_items_by_length
@@ -63,7 +64,7 @@ def test_packed_tma_pipeline_matches_reference(dim, n_q, n_items, k):
     q = torch.randn(n_q, dim, device="cuda", generator=g)
     items = torch.randn(n_items, dim, device="cuda", generator=g) * (0.2 + 2.0 * torch.rand(n_items, 1, device="cuda", generator=g) ** 3)
     it_s, len_s, ids_s = sort_items_by_length(items)
-    packed = PackedItems(it_s, len_s, ids_s)
+    packed = PackedItems(it_s, len_s, ids_s, wide=wide)      # 64-item tiles / 128-item tiles with K-block stages
     stats = torch.zeros(4, device="cuda", dtype=torch.int64)
     for pruning in (True, False):
         stats.zero_()
