@@ -287,6 +287,10 @@ int fps_mf_sgd_combine(const FpsTableView* items, const FpsTableView* users, con
     q.variant = 0;
     return fps_mf_sgd_step(items, users, d_uid, d_iid, d_rating, n, &q, flow, (void*)st);
   }
+  // Round-1 path, kept for A/B runs: its sort scratch is one grow-only buffer per device owned by the
+  // library (cudaMalloc on first use / growth), so only ONE stream per device may use this variant at a
+  // time; the tile path (mf_tiles.cu) takes caller-owned scratch instead.
+  FPS_REQUIRE(n <= 0x7fffffffll, FPS_E_TOO_LARGE, "fps_mf_sgd_combine: at most 2^31-1 ratings per step");
   auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
   const size_t nb = align((size_t)n * 4);
   size_t cub_bytes = 0;

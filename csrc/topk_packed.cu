@@ -570,24 +570,36 @@ struct WideShared {
   float qlen[TK_M];
 };
 
+// Work split of the wide kernel.  Every query tile is cut into V "virtual splits" (virtual split v of a
+// query tile = item tiles v, v + V, v + 2V, ... - interleaved so that each sees the long items first),
+// and CTA c takes the `share` consecutive virtual splits [c * share, (c + 1) * share) of the whole list
+// (query tile major).  share = 1, V = n_splits is the classic "one CTA per (query tile, split)" plan;
+// V = 37, share = 8 puts 32 query tiles on exactly 148 SMs (37 * 32 = 148 * 8) instead of leaving 20 idle.
+// A CTA whose range crosses a query-tile boundary works in SEGMENTS: it finishes its part of one query
+// tile (partial list written to its slot), re-stages the next tile's queries in TMEM and goes on; the
+// barrier / accumulator / stage ordinals simply keep counting.
+struct WideSplit {
+  int V, share, n_slots;
+};
+
 __global__ void __launch_bounds__(W_THREADS, 1)
 k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
                  const float* __restrict__ packed, const float* __restrict__ item_len,
-                 const int* __restrict__ item_ids, long long n_items, int dim, int kblks, int k, int n_splits,
-                 int use_pruning, TopkScratch sc, unsigned long long* __restrict__ stats) {
+                 const int* __restrict__ item_ids, long long n_items, int dim, int kblks, int k,
+                 const WideSplit ws, int n_q_tiles, int use_pruning, TopkScratch sc,
+                 unsigned long long* __restrict__ stats) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   float* sB = (float*)base;                 // W_STAGES x [hi slab | lo slab]
   __shared__ WideShared sh;
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-  const int qt = blockIdx.x / n_splits, split = blockIdx.x - qt * n_splits;
-  const long long q0 = (long long)qt * TK_M;
-  const int q_valid = (int)min((long long)TK_M, n_q - q0);
   const long long n_tiles = (n_items + W_N - 1) / W_N;
-  const int my_tiles = n_tiles > split ? (int)((n_tiles - split + n_splits - 1) / n_splits) : 0;
   constexpr uint32_t STAGE_BYTES = 2u * W_SLAB * sizeof(float);
   const long long tile_floats = 2ll * kblks * W_SLAB;
+  const long long v_total = (long long)n_q_tiles * ws.V;
+  long long v_cur = (long long)blockIdx.x * ws.share;
+  const long long v_end = min(v_total, v_cur + ws.share);
 
   if (warp == 4) tmem_alloc((uint32_t*)&sh.tmem, TP_TMEM_COLS);
   if (t == 0) {
@@ -599,8 +611,6 @@ k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
       mbar_init(&sh.acc_full[b], 1);
       mbar_init(&sh.acc_empty[b], 4);
     }
-    sh.issued_final = -1;
-    for (int w = 0; w < 4; ++w) sh.skip_from[w] = 0x7fffffff;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   tc_fence_before();
@@ -608,221 +618,285 @@ k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
   tc_fence_after();
   const uint32_t tmem_base = sh.tmem;
   const uint32_t tmem_a_hi = tmem_base + TP_A_COL, tmem_a_lo = tmem_base + TP_A_COL + 128;
+  long long g_base = 0;                     // stages issued by the segments before this one
+  long long a_base = 0;                     // tiles (accumulator uses) of the segments before this one
+  unsigned long long tiles_done = 0, accepted = 0, prunes = 0, tiles_planned = 0;
 
-  // ---- queries -> TMEM (thread t = lane t = query t), split into tf32 hi / lo on the way
-  if (warp < 4) {
-    const float* qp = queries + (q0 + t) * q_stride;
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-    float s = 0.f;
-    for (int c0 = 0; c0 < kblks * TK_KB; c0 += 32) {
-      float hi[32], lo[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int col = c0 + j;
-        const float x = (t < q_valid && col < dim) ? qp[col] : 0.f;
-        s = fmaf(x, x, s);
-        hi[j] = to_tf32(x);
-        lo[j] = to_tf32(x - hi[j]);
-      }
-      tmem_st32(tmem_a_hi + lane_off + c0, hi);
-      tmem_st32(tmem_a_lo + lane_off + c0, lo);
+  while (v_cur < v_end) {
+    // ---- this segment: virtual splits [lv0, lv0 + nv) of query tile qt -----------------------------
+    const int qt = (int)(v_cur / ws.V);
+    const int lv0 = (int)(v_cur - (long long)qt * ws.V);
+    const int nv = (int)min((long long)ws.V - lv0, v_end - v_cur);
+    const long long q0 = (long long)qt * TK_M;
+    const int q_valid = (int)min((long long)TK_M, n_q - q0);
+    const int rows = (int)((n_tiles + ws.V - 1) / ws.V);            // item tiles of the longest virtual split
+    int my_tiles = 0;
+    if (rows > 0) {
+      const long long last = n_tiles - (long long)(rows - 1) * ws.V - lv0;     // valid ones in the last row
+      my_tiles = (rows - 1) * nv + (int)max(0ll, min((long long)nv, last));
     }
-    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-    sh.qlen[t] = sqrtf(s);
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
+    // ordinal m of the segment -> item tile (row major: all of the segment's virtual splits, then the next row)
+    auto tile_of = [&](int m) -> long long { return lv0 + (m % nv) + (long long)(m / nv) * ws.V; };
+    const int slot = (int)(blockIdx.x - ((long long)qt * ws.V) / ws.share);     // which partial list of the query tile
+    const bool last_of_qt = lv0 + nv == ws.V;
 
-  if (warp == 4) {
-    // ===================== producer: one bulk copy pair per (tile, K block) =====================
-    if (lane == 0) {
-      int issued = 0;
-      long long g = 0;                                    // stage ordinal
-      for (int j = 0; j < my_tiles; ++j) {
-        if (use_pruning) {
-          bool all = true;
-          for (int sub = 0; sub < 4; ++sub) all = all && (sh.skip_from[sub] <= j);
-          if (all) break;                                                      // LEMP early exit
+    if (t == 0) {
+      sh.issued_final = -1;
+      for (int w = 0; w < 4; ++w) sh.skip_from[w] = 0x7fffffff;
+    }
+    // queries -> TMEM (thread t = lane t = query t), split into tf32 hi / lo on the way
+    if (warp < 4) {
+      const float* qp = queries + (q0 + t) * q_stride;
+      const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+      float s = 0.f;
+      for (int c0 = 0; c0 < kblks * TK_KB; c0 += 32) {
+        float hi[32], lo[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int col = c0 + j;
+          const float x = (t < q_valid && col < dim) ? qp[col] : 0.f;
+          s = fmaf(x, x, s);
+          hi[j] = to_tf32(x);
+          lo[j] = to_tf32(x - hi[j]);
         }
-        const long long tile = split + (long long)j * n_splits;
-        const float* src = packed + tile * tile_floats;
+        tmem_st32(tmem_a_hi + lane_off + c0, hi);
+        tmem_st32(tmem_a_lo + lane_off + c0, lo);
+      }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      sh.qlen[t] = sqrtf(s);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+
+    if (warp == 4) {
+      // ===================== producer: one bulk copy pair per (tile, K block) =====================
+      if (lane == 0) {
+        int issued = 0;
+        long long g = g_base;
+        for (int j = 0; j < my_tiles; ++j) {
+          if (use_pruning) {
+            bool all = true;
+            for (int sub = 0; sub < 4; ++sub) all = all && (sh.skip_from[sub] <= j);
+            if (all) break;                                                      // LEMP early exit
+          }
+          const float* src = packed + tile_of(j) * tile_floats;
+          for (int kb = 0; kb < kblks; ++kb, ++g) {
+            const int s = (int)(g % W_STAGES);
+            const long long n = g / W_STAGES;
+            if (n > 0) mbar_wait(&sh.stage_free[s], (uint32_t)((n - 1) & 1));
+            float* dst = sB + (size_t)s * 2 * W_SLAB;
+            mbar_expect_tx(&sh.b_full[s], STAGE_BYTES);
+            tma_bulk_g2s(dst, src + (size_t)kb * 2 * W_SLAB, W_SLAB * 4, &sh.b_full[s]);
+            tma_bulk_g2s(dst + W_SLAB, src + (size_t)kb * 2 * W_SLAB + W_SLAB, W_SLAB * 4, &sh.b_full[s]);
+          }
+          issued = j + 1;
+        }
+        __threadfence_block();
+        sh.issued_final = issued;
+      }
+    } else if (warp == 5) {
+      // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+      const uint32_t leader = elect_one();
+      const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t a_hi = tb + TP_A_COL, a_lo = tb + TP_A_COL + 128;
+      long long g = g_base;
+      for (int j = 0; j < my_tiles; ++j) {
+        const long long a = a_base + j;
+        const int b = (int)(a % W_ACC);
+        bool have = true;
         for (int kb = 0; kb < kblks; ++kb, ++g) {
           const int s = (int)(g % W_STAGES);
-          const long long n = g / W_STAGES;
-          if (n > 0) mbar_wait(&sh.stage_free[s], (uint32_t)((n - 1) & 1));
-          float* dst = sB + (size_t)s * 2 * W_SLAB;
-          mbar_expect_tx(&sh.b_full[s], STAGE_BYTES);
-          tma_bulk_g2s(dst, src + (size_t)kb * 2 * W_SLAB, W_SLAB * 4, &sh.b_full[s]);
-          tma_bulk_g2s(dst + W_SLAB, src + (size_t)kb * 2 * W_SLAB + W_SLAB, W_SLAB * 4, &sh.b_full[s]);
-        }
-        issued = j + 1;
-      }
-      __threadfence_block();
-      sh.issued_final = issued;
-    }
-  } else if (warp == 5) {
-    // ===================== MMA issuer (converged warp, one elected lane issues) =====================
-    const uint32_t leader = elect_one();
-    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint32_t a_hi = tb + TP_A_COL, a_lo = tb + TP_A_COL + 128;
-    long long g = 0;
-    for (int j = 0; j < my_tiles; ++j) {
-      const int b = j % W_ACC;
-      bool have = true;
-      for (int kb = 0; kb < kblks; ++kb, ++g) {
-        const int s = (int)(g % W_STAGES);
-        const uint32_t par = (uint32_t)((g / W_STAGES) & 1);
-        if (kb == 0) {
-          // the first stage of a tile may never come (the producer stopped): watch issued_final too
-          have = false;
-          while (true) {
-            if (mbar_try(&sh.b_full[s], par)) { have = true; break; }
-            const int fin = sh.issued_final;
-            if (fin >= 0 && j >= fin) break;
+          const uint32_t par = (uint32_t)((g / W_STAGES) & 1);
+          if (kb == 0) {
+            // the first stage of a tile may never come (the producer stopped): watch issued_final too
+            have = false;
+            while (true) {
+              if (mbar_try(&sh.b_full[s], par)) { have = true; break; }
+              const int fin = sh.issued_final;
+              if (fin >= 0 && j >= fin) break;
+            }
+            have = __shfl_sync(0xffffffffu, have ? 1 : 0, 0) != 0;
+            if (!have) break;
+            if (a >= W_ACC) mbar_wait(&sh.acc_empty[b], (uint32_t)(((a / W_ACC) - 1) & 1));   // accumulator drained
+          } else {
+            mbar_wait(&sh.b_full[s], par);
           }
-          have = __shfl_sync(0xffffffffu, have ? 1 : 0, 0) != 0;
-          if (!have) break;
-          if (j >= W_ACC) mbar_wait(&sh.acc_empty[b], (uint32_t)(((j / W_ACC) - 1) & 1));   // accumulator drained
-        } else {
-          mbar_wait(&sh.b_full[s], par);
+          tc_fence_after();
+          const uint32_t acc_addr = tb + (uint32_t)b * W_N;
+          const uint64_t d0 = make_desc(smem_u32(sB + (size_t)s * 2 * W_SLAB));
+          constexpr uint64_t LO_OFF = ((uint64_t)W_SLAB * 4) >> 4;
+#pragma unroll
+          for (int ks = 0; ks < TK_KB / 8; ++ks) {
+            const uint32_t a_col = (uint32_t)(kb * TK_KB + ks * 8);
+            const uint64_t bh = d0 + (uint64_t)(ks * 2), bl = bh + LO_OFF;
+            if (kb == 0 && ks == 0) umma_tf32_ts_i<false>(leader, acc_addr, a_lo + a_col, bh, W_IDESC);   // small terms first
+            else umma_tf32_ts_i<true>(leader, acc_addr, a_lo + a_col, bh, W_IDESC);
+            umma_tf32_ts_i<true>(leader, acc_addr, a_hi + a_col, bl, W_IDESC);
+            umma_tf32_ts_i<true>(leader, acc_addr, a_hi + a_col, bh, W_IDESC);
+          }
+          umma_commit_elected(leader, &sh.stage_free[s]);
         }
+        if (!have) break;
+        umma_commit_elected(leader, &sh.acc_full[b]);
+      }
+    } else {
+      // ===================== selection warps: thread = TMEM lane = query =====================
+      const int sub = warp & 3;
+      const int tq = sub * 32 + lane;
+      const size_t row0 = ((size_t)blockIdx.x * TK_M + sub * 32) * W_CAP;       // this warp's 32 lists
+      float* const rs_w = sc.cand_s + row0;
+      int* const ri_w = sc.cand_i + row0;
+      float* const rs = rs_w + (size_t)lane * W_CAP;
+      int* const ri = ri_w + (size_t)lane * W_CAP;
+      volatile uint32_t* theta_g = sc.theta + q0 + tq;
+      const bool q_ok = tq < q_valid;
+      const float qlen = sh.qlen[tq];
+      int cnt = 0;
+      float theta = q_ok ? -INFINITY : INFINITY;           // padding queries never accept anything
+      for (int j = 0; j < my_tiles; ++j) {
+        const long long a = a_base + j;
+        const int b = (int)(a % W_ACC);
+        const uint32_t theta_key = *theta_g;
+        bool have = false;
+        while (true) {
+          if (mbar_try(&sh.acc_full[b], (uint32_t)((a / W_ACC) & 1))) { have = true; break; }
+          const int fin = sh.issued_final;
+          if (fin >= 0 && j >= fin) break;
+        }
+        if (!have) break;
         tc_fence_after();
-        const uint32_t acc_addr = tb + (uint32_t)b * W_N;
-        const uint64_t d0 = make_desc(smem_u32(sB + (size_t)s * 2 * W_SLAB));
-        constexpr uint64_t LO_OFF = ((uint64_t)W_SLAB * 4) >> 4;
+        const long long i0 = tile_of(j) * W_N;
+        const int i_valid = (int)min((long long)W_N, n_items - i0);
+        float v[4][32];
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(sub * 32) << 16) + (uint32_t)b * W_N;
 #pragma unroll
-        for (int ks = 0; ks < TK_KB / 8; ++ks) {
-          const uint32_t a_col = (uint32_t)(kb * TK_KB + ks * 8);
-          const uint64_t bh = d0 + (uint64_t)(ks * 2), bl = bh + LO_OFF;
-          if (kb == 0 && ks == 0) umma_tf32_ts_i<false>(leader, acc_addr, a_lo + a_col, bh, W_IDESC);   // small terms first
-          else umma_tf32_ts_i<true>(leader, acc_addr, a_lo + a_col, bh, W_IDESC);
-          umma_tf32_ts_i<true>(leader, acc_addr, a_hi + a_col, bl, W_IDESC);
-          umma_tf32_ts_i<true>(leader, acc_addr, a_hi + a_col, bh, W_IDESC);
-        }
-        umma_commit_elected(leader, &sh.stage_free[s]);
-      }
-      if (!have) break;
-      umma_commit_elected(leader, &sh.acc_full[b]);
-    }
-  } else {
-    // ===================== selection warps: thread = TMEM lane = query =====================
-    const int sub = warp & 3;
-    const int tq = sub * 32 + lane;
-    const size_t row0 = ((size_t)blockIdx.x * TK_M + sub * 32) * W_CAP;       // this warp's 32 lists
-    float* const rs_w = sc.cand_s + row0;
-    int* const ri_w = sc.cand_i + row0;
-    float* const rs = rs_w + (size_t)lane * W_CAP;
-    int* const ri = ri_w + (size_t)lane * W_CAP;
-    volatile uint32_t* theta_g = sc.theta + q0 + tq;
-    const bool q_ok = tq < q_valid;
-    const float qlen = sh.qlen[tq];
-    int cnt = 0;
-    float theta = q_ok ? -INFINITY : INFINITY;           // padding queries never accept anything
-    unsigned long long tiles_done = 0, accepted = 0, prunes = 0;
-    for (int j = 0; j < my_tiles; ++j) {
-      const int b = j % W_ACC;
-      const uint32_t theta_key = *theta_g;
-      bool have = false;
-      while (true) {
-        if (mbar_try(&sh.acc_full[b], (uint32_t)((j / W_ACC) & 1))) { have = true; break; }
-        const int fin = sh.issued_final;
-        if (fin >= 0 && j >= fin) break;
-      }
-      if (!have) break;
-      tc_fence_after();
-      const long long tile = split + (long long)j * n_splits;
-      const long long i0 = tile * W_N;
-      const int i_valid = (int)min((long long)W_N, n_items - i0);
-      float v[4][32];
-      const uint32_t lane_addr = tmem_base + ((uint32_t)(sub * 32) << 16) + (uint32_t)b * W_N;
-#pragma unroll
-      for (int h = 0; h < 4; ++h) tmem_ld32(lane_addr + 32 * h, v[h]);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&sh.acc_empty[b]);       // the MMAs of tile j + 2 may overwrite it now
-      if (q_ok) theta = fmaxf(theta, key2f(theta_key));
-      if (i_valid < W_N) {                                 // ragged last tile
-#pragma unroll
-        for (int h = 0; h < 4; ++h)
-#pragma unroll
-          for (int jj = 0; jj < 32; ++jj)
-            if (32 * h + jj >= i_valid) v[h][jj] = -INFINITY;
-      }
-      const int before = cnt;
-#pragma unroll
-      for (int h = 0; h < 4; ++h) select32(v[h], theta, (int)i0 + 32 * h, rs, ri, cnt);
-      accepted += (unsigned)(cnt - before);
-      if (__any_sync(0xffffffffu, cnt > W_CAP - W_N)) {
+        for (int h = 0; h < 4; ++h) tmem_ld32(lane_addr + 32 * h, v[h]);
+        tc_fence_before();
         __syncwarp();
-        for (int src = 0; src < 32; ++src) {
-          const int c = __shfl_sync(0xffffffffu, cnt, src);
-          if (c > k) {
-            const float th = prune_row<W_CAP>(rs_w + (size_t)src * W_CAP, ri_w + (size_t)src * W_CAP, c, k, lane);
-            if (lane == src) {
-              cnt = k;
-              theta = fmaxf(theta, th);
-              ++prunes;
-              atomicMax((uint32_t*)theta_g, f2key(theta));
+        if (lane == 0) mbar_arrive(&sh.acc_empty[b]);       // the MMAs of the tile after next may overwrite it now
+        if (q_ok) theta = fmaxf(theta, key2f(theta_key));
+        if (i_valid < W_N) {                                 // ragged last tile
+#pragma unroll
+          for (int h = 0; h < 4; ++h)
+#pragma unroll
+            for (int jj = 0; jj < 32; ++jj)
+              if (32 * h + jj >= i_valid) v[h][jj] = -INFINITY;
+        }
+        const int before = cnt;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) select32(v[h], theta, (int)i0 + 32 * h, rs, ri, cnt);
+        accepted += (unsigned)(cnt - before);
+        if (__any_sync(0xffffffffu, cnt > W_CAP - W_N)) {
+          __syncwarp();
+          for (int src = 0; src < 32; ++src) {
+            const int c = __shfl_sync(0xffffffffu, cnt, src);
+            if (c > k) {
+              const float th = prune_row<W_CAP>(rs_w + (size_t)src * W_CAP, ri_w + (size_t)src * W_CAP, c, k, lane);
+              if (lane == src) {
+                cnt = k;
+                theta = fmaxf(theta, th);
+                ++prunes;
+                atomicMax((uint32_t*)theta_g, f2key(theta));
+              }
             }
           }
+          __syncwarp();
         }
-        __syncwarp();
+        if (tq == 0) ++tiles_done;
+        if (use_pruning && j + 1 < my_tiles) {
+          const long long nxt = tile_of(j + 1) * W_N;
+          const bool can_skip = !q_ok || (theta > -INFINITY && qlen * item_len[nxt] <= theta);
+          if (__all_sync(0xffffffffu, can_skip) && lane == 0 && sh.skip_from[warp] == 0x7fffffff) sh.skip_from[warp] = j + 1;
+        }
       }
-      ++tiles_done;
-      if (use_pruning && j + 1 < my_tiles) {
-        const long long nxt = (split + (long long)(j + 1) * n_splits) * W_N;
-        const bool can_skip = !q_ok || (theta > -INFINITY && qlen * item_len[nxt] <= theta);
-        if (__all_sync(0xffffffffu, can_skip) && lane == 0 && sh.skip_from[warp] == 0x7fffffff) sh.skip_from[warp] = j + 1;
+      // final prune + partial list of (query, slot), one list at a time by the whole warp; the CTA that
+      // holds the last part of a query tile also blanks the slots nobody owns
+      __syncwarp();
+      for (int src = 0; src < 32; ++src) {
+        const int qi = sub * 32 + src;
+        if (qi >= q_valid) break;                          // warp-uniform
+        int c = __shfl_sync(0xffffffffu, cnt, src);
+        float* r_s = rs_w + (size_t)src * W_CAP;
+        int* r_i = ri_w + (size_t)src * W_CAP;
+        if (c > k) {
+          prune_row<W_CAP>(r_s, r_i, c, k, lane);
+          c = k;
+          __syncwarp();
+        }
+        const size_t part = ((size_t)(q0 + qi) * ws.n_slots + (size_t)slot) * k;
+        for (int jj = lane; jj < k; jj += 32) {
+          const bool in = jj < c;
+          const int it = in ? r_i[jj] : -1;
+          sc.part_s[part + jj] = in ? r_s[jj] : -INFINITY;
+          sc.part_i[part + jj] = in ? (item_ids ? item_ids[it] : it) : -1;
+        }
+        if (last_of_qt) {
+          for (int e = lane + (slot + 1) * k; e < ws.n_slots * k; e += 32) {
+            sc.part_s[(size_t)(q0 + qi) * ws.n_slots * k + e] = -INFINITY;
+            sc.part_i[(size_t)(q0 + qi) * ws.n_slots * k + e] = -1;
+          }
+        }
       }
+      if (tq == 0) tiles_planned += (unsigned long long)my_tiles;
     }
-    // final prune + partial list of (query, split), one list at a time by the whole warp
-    __syncwarp();
-    for (int src = 0; src < 32; ++src) {
-      const int qi = sub * 32 + src;
-      if (qi >= q_valid) break;                          // warp-uniform
-      int c = __shfl_sync(0xffffffffu, cnt, src);
-      float* r_s = rs_w + (size_t)src * W_CAP;
-      int* r_i = ri_w + (size_t)src * W_CAP;
-      if (c > k) {
-        prune_row<W_CAP>(r_s, r_i, c, k, lane);
-        c = k;
-        __syncwarp();
-      }
-      const size_t part = ((size_t)(q0 + qi) * n_splits + (size_t)split) * k;
-      for (int jj = lane; jj < k; jj += 32) {
-        const bool in = jj < c;
-        const int slot = in ? r_i[jj] : -1;
-        sc.part_s[part + jj] = in ? r_s[jj] : -INFINITY;
-        sc.part_i[part + jj] = in ? (item_ids ? item_ids[slot] : slot) : -1;
-      }
+    // ---- end of segment: everybody agrees on how far the pipeline got, then the next query tile ----
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const int fin = sh.issued_final;
+    g_base += (long long)fin * kblks;
+    a_base += fin;
+    v_cur += nv;
+    __syncthreads();                                       // nobody may reset issued_final before all have read it
+  }
+  if (stats != nullptr && warp < 4) {
+    if (t == 0) {
+      atomicAdd(&stats[0], tiles_done);
+      atomicAdd(&stats[1], tiles_planned);
     }
-    if (stats != nullptr) {
-      if (tq == 0) {
-        atomicAdd(&stats[0], tiles_done);
-        atomicAdd(&stats[1], (unsigned long long)my_tiles);
-      }
-      if (q_ok) atomicAdd(&stats[2], accepted);
-      if (prunes) atomicAdd(&stats[3], prunes);
-    }
+    if (accepted) atomicAdd(&stats[2], accepted);
+    if (prunes) atomicAdd(&stats[3], prunes);
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 4) tmem_dealloc(tmem_base, TP_TMEM_COLS);
 }
 
-// scratch plan of the wide kernel: as make_plan, with 128-item tiles, W_CAP slots per list, one group
-Plan make_plan_wide(long long n_q, int k, long long n_items, int dim) {
+// Scratch plan of the wide kernel: 128-item tiles, W_CAP slots per list, one selection group.  With ten
+// or more query tiles that do not divide the SMs evenly, the virtual-split scheme above fills every SM.
+struct WidePlan {
   Plan p;
+  WideSplit ws;
+};
+WidePlan make_plan_wide(long long n_q, int k, long long n_items, int dim) {
+  WidePlan wp;
+  Plan& p = wp.p;
   p.n_q_tiles = (int)((n_q + TK_M - 1) / TK_M);
   const long long n_tiles = (n_items + W_N - 1) / W_N;
   const int sms = fps_num_sms();
-  long long splits = sms / (p.n_q_tiles > 0 ? p.n_q_tiles : 1);
+  const int qt = p.n_q_tiles > 0 ? p.n_q_tiles : 1;
+  long long splits = sms / qt;
   if (splits < 1) splits = 1;
   if (splits > 16) splits = 16;
   if (splits > n_tiles) splits = n_tiles > 0 ? n_tiles : 1;
-  p.n_splits = (int)splits;
-  p.n_ctas = p.n_q_tiles * p.n_splits;
+  wp.ws = WideSplit{(int)splits, 1, (int)splits};
+  p.n_ctas = qt * (int)splits;
+  // opt-in (FPS_TOPK_FILL=1): measured on config 6, 148 CTAs of 8/37 of a query tile take 5.85 ms against
+  // 5.85 ms for 128 CTAs of 1/4 (3.45 vs 3.32 ms pruned).  The SM clock sits at 1.77 of 1.97 GHz during the
+  // kernel (ncu): the tensor work is power-limited, more busy SMs only lower the clock further.
+  static const bool fill = []() { const char* e = getenv("FPS_TOPK_FILL"); return e && e[0] == '1'; }();
+  if (fill && qt >= 10 && qt < sms && sms % qt != 0) {
+    auto gcd = [](long long a, long long b) { while (b) { const long long t = a % b; a = b; b = t; } return a; };
+    const long long V = sms / gcd(sms, qt);               // qt * V is a multiple of the SM count
+    const long long share = (long long)qt * V / sms;
+    const long long slots = (V + share - 1) / share + 1;  // CTAs that can touch one query tile
+    if (V <= n_tiles && slots * k <= 8192 && slots <= 16) {
+      wp.ws = WideSplit{(int)V, (int)share, (int)slots};
+      p.n_ctas = sms;
+    }
+  }
+  p.n_splits = wp.ws.n_slots;
   p.kblks = (dim + TK_KB - 1) / TK_KB;
   auto align = [](size_t x) { return (x + 255) & ~(size_t)255; };
   size_t o = 0;
@@ -836,7 +910,7 @@ Plan make_plan_wide(long long n_q, int k, long long n_items, int dim) {
   p.off_part_i = o;
   o = align(o + (size_t)p.n_q_tiles * TK_M * p.n_splits * k * sizeof(int));
   p.total = o;
-  return p;
+  return wp;
 }
 
 int packed_groups() {
@@ -947,7 +1021,7 @@ size_t fps_topk_wide_packed_bytes(int64_t n_items, int32_t dim) {
 
 size_t fps_topk_wide_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items) {
   if (n_q <= 0 || k <= 0 || n_items <= 0) return 0;
-  return make_plan_wide(n_q, k, n_items, 128).total;
+  return make_plan_wide(n_q, k, n_items, 128).p.total;
 }
 
 int fps_topk_pack_items_wide(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim, void* d_packed,
@@ -970,7 +1044,8 @@ int fps_lemp_topk_wide(const float* d_queries, int32_t q_stride, int64_t n_q, co
   FPS_REQUIRE(dim <= 128 && q_stride % 4 == 0, FPS_E_UNSUPPORTED, "fps_lemp_topk_wide: rank <= 128 and q_stride %% 4 == 0 required");
   FPS_REQUIRE(!use_pruning || d_item_len != nullptr, FPS_E_INVALID, "fps_lemp_topk_wide: pruning needs item lengths");
   cudaStream_t st = (cudaStream_t)stream;
-  const Plan p = make_plan_wide(n_q, k, n_items, dim);
+  const WidePlan wp = make_plan_wide(n_q, k, n_items, dim);
+  const Plan& p = wp.p;
   FPS_REQUIRE(scratch_bytes >= p.total, FPS_E_INVALID, "fps_lemp_topk_wide: scratch too small (%zu < %zu)", scratch_bytes, p.total);
   uint8_t* sb = (uint8_t*)d_scratch;
   TopkScratch sc;
@@ -983,8 +1058,8 @@ int fps_lemp_topk_wide(const float* d_queries, int32_t q_stride, int64_t n_q, co
   const size_t smem = 1024 + (size_t)W_STAGES * 2 * W_SLAB * sizeof(float);
   FPS_CUDA(cudaFuncSetAttribute(k_lemp_topk_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   k_lemp_topk_wide<<<p.n_ctas, W_THREADS, smem, st>>>(d_queries, q_stride, n_q, (const float*)d_packed, d_item_len,
-                                                      d_item_ids, n_items, dim, p.kblks, k, p.n_splits, use_pruning,
-                                                      sc, (unsigned long long*)d_stats);
+                                                      d_item_ids, n_items, dim, p.kblks, k, wp.ws, p.n_q_tiles,
+                                                      use_pruning, sc, (unsigned long long*)d_stats);
   FPS_LAUNCH_CHECK();
   return launch_merge(sc.part_s, sc.part_i, p.n_splits, n_q, k, k, nullptr, 0, d_out_scores, d_out_ids, st);
 }

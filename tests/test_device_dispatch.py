@@ -247,3 +247,39 @@ def test_user_tensor_logic_runs_on_the_device_engine_through_transform():
     # the worker outputs are the sums of the rows as pulled: monotone over the job
     sums = [float(v[0]) for v in lefts(out)]
     assert sums[0] >= 0 and sums[-1] > sums[0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("engine", ["host", "device"])
+def test_ps_top_k_generator_on_both_engines(engine):
+    """psTopKGenerator through the public entry point: the same model stream and queries, brute-force truth."""
+    from fps_b200.models.mf import attach_length, ps_top_k_generator
+    from fps_b200.models.mf.pruning import LENGTH
+    rng = np.random.default_rng(5)
+    k, n_items, n_users = 8, 400, 12
+    items = rng.normal(size=(n_items, k)).astype(np.float32)
+    users = rng.normal(size=(n_users, k)).astype(np.float32)
+    model = ([Left((u, attach_length(users[u]))) for u in range(n_users)] +
+             [Right((i, attach_length(items[i]))) for i in range(n_items)])
+    queries = [Rating(u, 0, 1.0, 100 + u) for u in range(n_users)]
+    res = ps_top_k_generator(queries, model, num_factors=k, K=5, worker_k=5, user_memory=-1,
+                             pruning_algorithm=LENGTH(), worker_parallelism=2, ps_parallelism=2,
+                             iteration_wait_time=10, engine=engine)
+    by_ts = {ts: topk for (_item, ts, topk) in res}
+    for u in range(n_users):
+        want = np.argsort(-(items.astype(np.float64) @ users[u].astype(np.float64)))[:5]
+        got = [i for _s, i in by_ts[100 + u]]
+        assert got[0] == want[0] and len(set(got) & set(want.tolist())) >= 4, (engine, u, got, want)
+
+
+@pytest.mark.gpu
+def test_learner_generator_entry_point_dispatches_and_announces_pruning():
+    from fps_b200.models.mf import ps_online_learner_and_generator
+    rnd = random.Random(2)
+    stream = [Rating(u := rnd.randrange(40), (u % 4) * 10 + rnd.randrange(10), 1.0, t) for t in range(1500)]
+    with pytest.warns(DE.DeviceFallbackWarning, match="LENGTH bucket bound"):      # default strategy is LI(5, 2.5)
+        out = ps_online_learner_and_generator(stream, num_factors=8, range_min=-0.1, range_max=0.1, learning_rate=0.1,
+                                              negative_sample_rate=3, user_memory=4, K=10, worker_k=10, pull_limit=500,
+                                              engine="device", n_users=40, n_items=40, batch_size=50)
+    assert len(out) == len(stream)
+    assert out.hit_rate(1000) > out.hit_rate(0) - 0.05 and out.hit_rate(1000) > 0.3      # 10 of 40 items = 0.25 by chance

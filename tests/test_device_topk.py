@@ -159,3 +159,30 @@ def test_in_place_table_scoring_masks_dead_slots():
     # nothing live at all -> empty lists
     s0, i0, _ = lemp_topk_table(q, table, dim, k, torch.full_like(live, -1))
     assert (i0 == -1).all() and torch.isinf(s0).all()
+
+
+def test_wide_kernel_fill_plan_covers_query_tile_boundaries(monkeypatch):
+    """FPS_TOPK_FILL=1: CTAs take equal shares of virtual splits and work in segments across query-tile
+    boundaries (re-staging queries in TMEM); the static plan flag is read once per process, so this runs the
+    check in a child process."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, torch; sys.path.insert(0, %r)\n"
+        "from fps_b200.ops.topk import PackedItems, lemp_topk_packed, sort_items_by_length\n"
+        "g = torch.Generator(device='cuda').manual_seed(3)\n"
+        "for n_q in (1500, 4000):\n"
+        "    q = torch.randn(n_q, 96, device='cuda', generator=g)\n"
+        "    items = torch.randn(60000, 96, device='cuda', generator=g) * (0.2 + 2 * torch.rand(60000, 1, device='cuda', generator=g) ** 3)\n"
+        "    it_s, len_s, ids_s = sort_items_by_length(items)\n"
+        "    packed = PackedItems(it_s, len_s, ids_s, wide=True)\n"
+        "    ref = (q.double() @ items.double().T).topk(50, dim=1)\n"
+        "    for prune in (False, True):\n"
+        "        s, i = lemp_topk_packed(q, packed, 50, use_pruning=prune)\n"
+        "        torch.cuda.synchronize()\n"
+        "        assert torch.allclose(s.double(), ref.values, rtol=2e-5, atol=2e-5)\n"
+        "        assert (i.long() == ref.indices).float().mean() > 0.99\n"
+        "print('FILL_OK')\n" % root)
+    env = dict(os.environ, FPS_TOPK_FILL="1")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=200, env=env)
+    assert r.returncode == 0 and "FILL_OK" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
