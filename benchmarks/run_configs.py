@@ -123,9 +123,13 @@ def config2(ctx):
         u = u - ((u - rank) % W)
         batches.append((u.int().cuda(), zipf_items(B, ni, g).int().cuda(), (torch.rand(B, generator=g) * 0.8 + 0.2).cuda()))   # stars / 5: the 1..5 scale diverges at lr 0.01 with 1M-rating launches
     k = [0]
+    torch.cuda.synchronize()
+    ready = torch.cuda.Event()
+    ready.record()                      # the resident batches are valid from here on: the tile path may group
+                                        # batch k + 1 on its side stream while step k runs
 
     def step():
-        mf.step(*batches[k[0] % 4])
+        mf.step(*batches[k[0] % 4], ready_event=ready)
         k[0] += 1
     ms = timed(step, 3, 20)
     st = mf.stats(check_nan=False)      # a diverged model would skip its updates and look fast: report it
