@@ -41,8 +41,8 @@ P2P_SYMMETRIC_GBS = 638.6
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "nccl_a2a", "cpu", "reference"])
     ap.add_argument("--batch", type=int, default=1 << 22, help="ratings per GPU per step")
     ap.add_argument("--users", type=int, default=100_000_000)
@@ -361,7 +361,7 @@ def cpu_arm(a, torch):
         avail = psutil.virtual_memory().available
     except Exception:
         avail = 64 << 30
-    budget = int(avail * 0.5)
+    budget = min(int(avail * 0.5), 32 << 30)      # the single-threaded table fill takes ~1 s per GB
     row = a.rank * 8
     users = min(a.users, max(1_000_000, budget * 10 // 11 // row))
     items = min(a.items, max(100_000, budget // 11 // row))
@@ -376,7 +376,7 @@ def cpu_arm(a, torch):
                       "config": {"model": f"mf_sgd_rank{a.rank}_{users}x{items}", "global_batch": batch,
                                  "parallelism": f"w{threads // 2}xps{threads // 2} threads",
                                  "host_cpus": os.cpu_count(), "host_mem_available_gb": round(avail / 2 ** 30, 1),
-                                 "note": "tables sized to half of the host's free memory; per-record work identical"},
+                                 "note": "tables sized to half of the host's free memory, at most 32 GB; per-record work identical"},
                       "gpu_launches": 0}))
     return 0
 

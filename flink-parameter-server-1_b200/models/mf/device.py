@@ -169,7 +169,7 @@ class DeviceMF:
         if side is not main:
             s["ready"].record(side)
             main.wait_event(s["ready"])
-        self.kernel_launches += 3
+        self.kernel_launches += 3                 # k_bucket_count, k_bucket_scan, k_bucket_scatter
         return s
 
     def _run_tiles(self, s, n: int) -> None:
@@ -179,7 +179,7 @@ class DeviceMF:
                 "fps_mf_sgd_tiles")
         s["free"].record(torch.cuda.current_stream())
         s["used"] = True
-        self.kernel_launches += 1
+        self.kernel_launches += 2                 # k_tile_bounds + k_mf_tiles_tma / k_mf_tiles_reg
 
     # -- training ------------------------------------------------------------------------------
     def step(self, users, items, ratings, ready_event=None) -> None:
