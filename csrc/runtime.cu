@@ -253,7 +253,28 @@ probe_mixed_rows(float* remote, float* local, long long span_rows, long long n_r
       if (flags & 32) *reinterpret_cast<float4*>(lr) = d; else st_row4(lr, d);
     }
     if (flags & 16) red_add4(lr, d);
-    if ((flags & 2) && !(flags & 64)) red_add4(rr, d);
+    if ((flags & 2) && !(flags & 64) && !(flags & 256)) red_add4(rr, d);
+    if ((flags & 2) && (flags & 256)) {
+      // push as ONE bulk reduction of the whole 512-byte row from shared memory (TMA reduce) instead of
+      // 32 x 16-byte red.add: does the wire carry it better?
+      __shared__ __align__(128) float s_row[8][2][128];
+      const int w = threadIdx.x >> 5;
+      const int slot = (int)((r / n_warps) & 1);
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the copy that used this slot two rows ago
+      __syncwarp();
+      *reinterpret_cast<float4*>(&s_row[w][slot][lane * 4]) = d;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) {
+        asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], 512;"
+                     ::"l"(rr - lane * 4), "r"((uint32_t)__cvta_generic_to_shared(&s_row[w][slot][0])) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+  }
+  if (flags & 256) {
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    __syncwarp();
   }
   if (acc == 123.456f) sink[0] = acc;
 }

@@ -117,7 +117,8 @@ int fps_p2p_probe(float* d_dst, const float* d_src, size_t bytes, int mode, int 
  * floats at random offsets within span_rows rows of d_table (local or peer-mapped); mode as above;
  * `unroll` rows in flight per warp, blocks_per_sm CTAs per SM.  The mixed probe interleaves peer loads,
  * peer red.adds, local loads and local stores as selected by the bits of `flags` (1, 2, 4, 8; 128 = all
- * four on one row index) - the mix the fused MF kernel issues.  Elapsed ms of `iters` launches in *ms.  */
+ * four on one row index; 256 = the peer push as one 512-byte cp.reduce.async.bulk per row instead of
+ * 32 red.add.v4) - the mix the fused MF kernel issues.  Elapsed ms of `iters` launches in *ms.          */
 int fps_p2p_probe_random(float* d_table, int64_t span_rows, int row_floats, int64_t n_rows, int mode,
                          int unroll, int blocks_per_sm, int iters, float* ms, void* stream);
 int fps_p2p_probe_mixed(float* d_remote, float* d_local, int64_t span_rows, int64_t n_rows, int flags,

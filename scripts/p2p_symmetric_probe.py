@@ -30,7 +30,8 @@ def main():
     peer = t._view.rows[(rank + 1) % world]
     n = 1 << 22
     res = {}
-    for label, flags in (("pull_only", 1), ("push_only", 2), ("pull+push", 3), ("pull+push+local_rw", 3 | 4 | 8)):
+    for label, flags in (("pull_only", 1), ("push_only", 2), ("pull+push", 3), ("pull+push+local_rw", 3 | 4 | 8),
+                         ("push_only_bulk_reduce", 2 | 256), ("pull+push_bulk_reduce", 3 | 256)):
         torch.cuda.synchronize()
         ctx.barrier()
         ms = C.c_float()
