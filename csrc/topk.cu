@@ -118,7 +118,7 @@ k_lemp_topk(const float* __restrict__ queries, int q_stride, long long n_q,
         }
         umma_commit(&s_bar);
       }
-      mbar_wait(&s_bar, phase);
+      mbar_wait_warp(&s_bar, phase);      // every thread of the CTA waits here
       phase ^= 1;
       tc_fence_after();
       const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);

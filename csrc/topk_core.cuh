@@ -44,6 +44,24 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
   }
 }
+// The same wait for call sites where ALL 32 lanes of a warp poll one barrier.  When every operand of the poll
+// is provably uniform, ptxas takes the result for warp-uniform and emits no reconvergence point behind the
+// loop (seen in SASS: the loop branch is followed directly by uniform-datapath updates of phase bits and
+// counters, and a __syncwarp() placed there is compiled to a NOP).  Whether the hardware always answers the
+// 32 lanes of one poll alike is not documented, so the exit is made uniform in fact with a vote; a completed
+// phase stays completed until the waiters have moved on.  Measured cost: none (config 6 unchanged).
+__device__ __forceinline__ void mbar_wait_warp(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!__all_sync(0xffffffffu, done));
+}
 // D[tmem] (+)= A[smem] * B[smem]^T, tf32 inputs, fp32 accumulate, issued by one thread
 __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                           uint32_t accumulate) {

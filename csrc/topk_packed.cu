@@ -57,6 +57,10 @@ __device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
       : "memory");
   return done != 0;
 }
+// one poll by all 32 lanes of a warp, with a warp-uniform answer (see mbar_wait_warp)
+__device__ __forceinline__ bool mbar_try_warp(uint64_t* bar, uint32_t parity) {
+  return __all_sync(0xffffffffu, mbar_try(bar, parity)) != 0;
+}
 // global -> shared bulk copy executed by the TMA engine; completes `bytes` on `bar`
 __device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -372,14 +376,14 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
       const int s = j % TP_STAGES, n = j / TP_STAGES;
       bool have = false;
       while (true) {
-        if (mbar_try(&sh.b_full[s], n & 1)) { have = true; break; }
+        if (mbar_try_warp(&sh.b_full[s], n & 1)) { have = true; break; }
         const int fin = sh.issued_final;
-        if (fin >= 0 && j >= fin) break;
+        if (__any_sync(0xffffffffu, fin >= 0 && j >= fin)) break;
       }
       have = __shfl_sync(0xffffffffu, have ? 1 : 0, 0) != 0;
       if (!have) break;
       const int b = j % TP_ACC;
-      if (j >= TP_ACC) mbar_wait(&sh.acc_empty[b], ((j / TP_ACC) - 1) & 1);      // accumulator drained
+      if (j >= TP_ACC) mbar_wait_warp(&sh.acc_empty[b], ((j / TP_ACC) - 1) & 1);      // accumulator drained
       tc_fence_after();
       const uint32_t acc_addr = tb + (uint32_t)b * TK_N;
       const uint64_t d0 = make_desc(smem_u32(sB + (size_t)s * stage_floats));
@@ -418,9 +422,9 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
       // wait for tile j, or learn that the producer stopped before it
       bool have = false;
       while (true) {
-        if (mbar_try(&sh.acc_full[b], (j / TP_ACC) & 1)) { have = true; break; }
+        if (mbar_try_warp(&sh.acc_full[b], (j / TP_ACC) & 1)) { have = true; break; }
         const int fin = sh.issued_final;
-        if (fin >= 0 && j >= fin) break;
+        if (__any_sync(0xffffffffu, fin >= 0 && j >= fin)) break;
       }
       if (!have) break;
       tc_fence_after();
@@ -712,15 +716,15 @@ k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
             // the first stage of a tile may never come (the producer stopped): watch issued_final too
             have = false;
             while (true) {
-              if (mbar_try(&sh.b_full[s], par)) { have = true; break; }
+              if (mbar_try_warp(&sh.b_full[s], par)) { have = true; break; }
               const int fin = sh.issued_final;
-              if (fin >= 0 && j >= fin) break;
+              if (__any_sync(0xffffffffu, fin >= 0 && j >= fin)) break;
             }
             have = __shfl_sync(0xffffffffu, have ? 1 : 0, 0) != 0;
             if (!have) break;
-            if (a >= W_ACC) mbar_wait(&sh.acc_empty[b], (uint32_t)(((a / W_ACC) - 1) & 1));   // accumulator drained
+            if (a >= W_ACC) mbar_wait_warp(&sh.acc_empty[b], (uint32_t)(((a / W_ACC) - 1) & 1));   // accumulator drained
           } else {
-            mbar_wait(&sh.b_full[s], par);
+            mbar_wait_warp(&sh.b_full[s], par);
           }
           tc_fence_after();
           const uint32_t acc_addr = tb + (uint32_t)b * W_N;
@@ -760,9 +764,9 @@ k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
         const uint32_t theta_key = *theta_g;
         bool have = false;
         while (true) {
-          if (mbar_try(&sh.acc_full[b], (uint32_t)((a / W_ACC) & 1))) { have = true; break; }
+          if (mbar_try_warp(&sh.acc_full[b], (uint32_t)((a / W_ACC) & 1))) { have = true; break; }
           const int fin = sh.issued_final;
-          if (fin >= 0 && j >= fin) break;
+          if (__any_sync(0xffffffffu, fin >= 0 && j >= fin)) break;
         }
         if (!have) break;
         tc_fence_after();
