@@ -139,7 +139,8 @@ k_pa_binary(const __grid_constant__ FpsTableView t, const long long* __restrict_
 // Warps split the active features, lanes split the class columns (float4 each); the decision
 // vector d = W^T x is reduced across warps in shared memory, tau/y per class is computed once,
 // then every warp scatters its features' row deltas.
-__global__ void __launch_bounds__(PA_THREADS)
+// 4 CTAs per SM (64 registers): measured on config 4 against 3 (72 registers) and 2 (92): 0.722 / 0.931 / 1.135 ms
+__global__ void __launch_bounds__(PA_THREADS, 4)
 k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__ indptr,
            const int* __restrict__ indices, const float* __restrict__ values,
            const int* __restrict__ labels, long long n, const FpsPaParams p,
@@ -161,50 +162,58 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
   for (long long e = blockIdx.x; e < n; e += gridDim.x) {
     const long long b = indptr[e], end = indptr[e + 1];
     // ---- pull + decision vector
+    // Features are dealt to the pulling warps round-robin.  Lane u of a warp fetches the id / value of the
+    // warp's u-th feature and resolves its row ONCE (32 features per warp and pass), then the warp walks
+    // them with shuffles, pull_u (<= PULL_U) rows in flight at a time.  (Before: every lane re-read the id and
+    // re-derived the row for each feature, and a dependent id -> row load chain per two features.)
+    constexpr int PULL_U = 4;
     float n2 = 0.f;
     for (int v0 = 0; v0 < nvec; v0 += 32) {
       const int vb = v0 + lane;
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      // PULL_U features of this warp in flight at once: ids first, then all row loads, then the FMAs
-      // (one feature per iteration left the warp waiting on a dependent id -> row load chain)
-      constexpr int PULL_U = 2;
-      for (long long k0 = b + warp; k0 < end && warp < warps_pulling; k0 += (long long)warps_pulling * PULL_U) {
-        long long id[PULL_U];
-        float x[PULL_U];
-        RowRef r[PULL_U];
-        bool ok[PULL_U];
-        float4 w[PULL_U];
-#pragma unroll
-        for (int u = 0; u < PULL_U; ++u) {
-          const long long k = k0 + (long long)u * warps_pulling;
-          const bool have = k < end && u < pull_u;
-          id[u] = have ? (long long)indices[k] : 0;
-          x[u] = have ? values[k] : 0.f;
-          r[u] = locate(t, id[u]);
-          ok[u] = have && in_table(t, id[u], r[u]);
-          if (have && !ok[u] && lane == 0 && v0 == 0) ++c.bad;
+      for (long long base = b; base < end && warp < warps_pulling; base += 32ll * warps_pulling) {
+        const long long mk = base + warp + (long long)lane * warps_pulling;
+        const bool mhave = mk < end;
+        const long long mid = mhave ? (long long)indices[mk] : 0;
+        const float mx = mhave ? values[mk] : 0.f;
+        const RowRef mr = locate(t, mid);
+        const bool mok = mhave && in_table(t, mid, mr);
+        if (mhave && !mok && v0 == 0) ++c.bad;
+        const unsigned okmask = __ballot_sync(0xffffffffu, mok);
+        const int rem = (int)min(end - base, 32ll * warps_pulling) - warp;       // features of this warp in this pass
+        const int nfeat = rem > 0 ? (rem + warps_pulling - 1) / warps_pulling : 0;
+        if (v0 == 0 && mok) {
+          n2 = fmaf(mx, mx, n2);
+          ++c.pulls;
+          if (mr.owner != p.local_shard) ++c.remote;
         }
+        for (int u0 = 0; u0 < nfeat; u0 += pull_u) {
+          float4 w[PULL_U];
+          float x[PULL_U];
 #pragma unroll
-        for (int u = 0; u < PULL_U; ++u) {
-          w[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (ok[u] && vb < nvec) w[u] = ld_row4(t.rows[r[u].owner] + r[u].slot * t.stride + vb * 4);
-        }
-#pragma unroll
-        for (int u = 0; u < PULL_U; ++u) {
-          if (!ok[u]) continue;
-          if (v0 == 0 && lane == 0) {
-            n2 = fmaf(x[u], x[u], n2);
-            ++c.pulls;
-            if (r[u].owner != p.local_shard) ++c.remote;
-          }
-          if (vb < nvec) {
-            if (t.lazy) {
-              const int s = touch_state(t.state[r[u].owner], r[u].slot, FPS_ROW_PULLED);
-              if (s == FPS_ROW_PULLED && !(t.init_lo == 0.f && t.init_hi == 0.f)) {
-                const float4 i4 = init_block(t, id[u], vb);
-                w[u].x += i4.x; w[u].y += i4.y; w[u].z += i4.z; w[u].w += i4.w;
+          for (int u = 0; u < PULL_U; ++u) {
+            const int src = min(u0 + u, 31);
+            const int owner = __shfl_sync(0xffffffffu, mr.owner, src);
+            const long long slot = __shfl_sync(0xffffffffu, mr.slot, src);
+            x[u] = __shfl_sync(0xffffffffu, mx, src);
+            long long fid = 0;
+            if (t.lazy) fid = __shfl_sync(0xffffffffu, mid, src);
+            const bool ok = u < pull_u && u0 + u < nfeat && ((okmask >> src) & 1u);
+            if (!ok) x[u] = 0.f;
+            w[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok && vb < nvec) {
+              w[u] = ld_row4(t.rows[owner] + slot * t.stride + vb * 4);
+              if (t.lazy) {
+                const int st = touch_state(t.state[owner], slot, FPS_ROW_PULLED);
+                if (st == FPS_ROW_PULLED && !(t.init_lo == 0.f && t.init_hi == 0.f)) {
+                  const float4 i4 = init_block(t, fid, vb);
+                  w[u].x += i4.x; w[u].y += i4.y; w[u].z += i4.z; w[u].w += i4.w;
+                }
               }
             }
+          }
+#pragma unroll
+          for (int u = 0; u < PULL_U; ++u) {
             acc.x = fmaf(x[u], w[u].x, acc.x); acc.y = fmaf(x[u], w[u].y, acc.y);
             acc.z = fmaf(x[u], w[u].z, acc.z); acc.w = fmaf(x[u], w[u].w, acc.w);
           }
@@ -212,6 +221,8 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
       }
       if (vb < nvec) *reinterpret_cast<float4*>(s_part + warp * t.stride + vb * 4) = acc;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, o);
     if (lane == 0) s_n2[warp] = n2;
     __syncthreads();
     for (int j = threadIdx.x; j < t.stride; j += PA_THREADS) {
@@ -275,18 +286,33 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
         any = true;   // rows of all-zero multipliers are rare (every class already separated)
       }
       if (p.multiclass == 1 && any) {
-        for (long long k = b + warp; k < end; k += WPB) {
-          const long long id = indices[k];
-          const float x = values[k];
-          const RowRef r = locate(t, id);
-          if (!in_table(t, id, r)) continue;
-          const long long row = r.slot * t.stride;
-          if (t.lazy && lane == 0) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
-          for (int vb = lane; vb < nvec; vb += 32) {
-            const float4 m4 = *reinterpret_cast<const float4*>(s_d + vb * 4);
-            push_add4(t, r.owner, row + vb * 4, make_float4(x * m4.x, x * m4.y, x * m4.z, x * m4.w));
+        // same dealing as the pull: lane u resolves the warp's u-th feature, the warp walks them with shuffles
+        const float4 m0 = lane < nvec ? *reinterpret_cast<const float4*>(s_d + lane * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (long long base = b; base < end; base += 32ll * WPB) {
+          const long long mk = base + warp + (long long)lane * WPB;
+          const bool mhave = mk < end;
+          const long long mid = mhave ? (long long)indices[mk] : 0;
+          const float mx = mhave ? values[mk] : 0.f;
+          const RowRef mr = locate(t, mid);
+          const bool mok = mhave && in_table(t, mid, mr);
+          if (mok) {
+            if (t.lazy) touch_state(t.state[mr.owner], mr.slot, FPS_ROW_PUSHED);
+            ++c.pushes;
           }
-          if (lane == 0) ++c.pushes;
+          const unsigned okmask = __ballot_sync(0xffffffffu, mok);
+          const int rem = (int)min(end - base, 32ll * WPB) - warp;
+          const int nfeat = rem > 0 ? (rem + WPB - 1) / WPB : 0;
+          for (int u = 0; u < nfeat; ++u) {
+            const int owner = __shfl_sync(0xffffffffu, mr.owner, u);
+            const long long row = __shfl_sync(0xffffffffu, mr.slot, u) * t.stride;
+            const float x = __shfl_sync(0xffffffffu, mx, u);
+            if (!((okmask >> u) & 1u)) continue;
+            if (lane < nvec) push_add4(t, owner, row + lane * 4, make_float4(x * m0.x, x * m0.y, x * m0.z, x * m0.w));
+            for (int vb = lane + 32; vb < nvec; vb += 32) {
+              const float4 m4 = *reinterpret_cast<const float4*>(s_d + vb * 4);
+              push_add4(t, owner, row + vb * 4, make_float4(x * m4.x, x * m4.y, x * m4.z, x * m4.w));
+            }
+          }
         }
       } else if (p.multiclass >= 2 && s_q != y) {
         const float tau = s_tau;
@@ -352,11 +378,11 @@ extern "C" int fps_pa_step_cost(const FpsTableView* weights, const int64_t* d_in
     if (smem > 48 * 1024) FPS_CUDA(cudaFuncSetAttribute(k_pa_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long blocks = n_examples;
     if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
-    int warps_pulling = PA_THREADS / 32, pull_u = 2;
+    int warps_pulling = PA_THREADS / 32, pull_u = 4;        // = PULL_U of the kernel
     if (params->pull_limit > 0) {
       const long long limit = params->pull_limit;
-      if (limit < 2) { pull_u = 1; warps_pulling = 1; }
-      else if (limit < 2 * (PA_THREADS / 32)) warps_pulling = (int)(limit / 2);
+      if (limit < 4) { pull_u = (int)limit; warps_pulling = 1; }
+      else if (limit < 4 * (PA_THREADS / 32)) warps_pulling = (int)(limit / 4);
       const long long fit = limit / (warps_pulling * pull_u);
       if (fit < (long long)sms * 8 && blocks > fit) blocks = fit > 0 ? fit : 1;
     }
