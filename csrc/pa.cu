@@ -9,6 +9,9 @@
 namespace {
 
 constexpr int PA_THREADS = 256;
+// multiclass kernel: one CTA per example; measured on config 4 (no limiter / limit 10 000): 256 threads 0.722 /
+// 1.157 ms, 128 threads 0.674 / 0.885 ms, 64 threads 0.728 / 0.879 ms
+constexpr int PM_THREADS = 128;
 
 __device__ __forceinline__ float scalar_init(const FpsTableView& t, long long id) {
   if (t.init_lo == 0.f && t.init_hi == 0.f) return 0.f;
@@ -37,9 +40,10 @@ struct PaCounters {
   unsigned int records, pulls, pushes, remote, bad;
 };
 
+template <int THREADS = PA_THREADS>
 __device__ __forceinline__ void pa_flush(PaCounters c, FpsFlow* flow) {
-  __shared__ float s_loss[PA_THREADS / 32];
-  __shared__ unsigned int s_cnt[PA_THREADS / 32][5];
+  __shared__ float s_loss[THREADS / 32];
+  __shared__ unsigned int s_cnt[THREADS / 32][5];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     c.loss += __shfl_xor_sync(0xffffffffu, c.loss, o);
@@ -58,7 +62,7 @@ __device__ __forceinline__ void pa_flush(PaCounters c, FpsFlow* flow) {
   if (threadIdx.x == 0) {
     double L = 0.0;
     unsigned long long a[5] = {0, 0, 0, 0, 0};
-    for (int i = 0; i < PA_THREADS / 32; ++i) {
+    for (int i = 0; i < THREADS / 32; ++i) {
       L += s_loss[i];
       for (int k = 0; k < 5; ++k) a[k] += s_cnt[i][k];
     }
@@ -139,13 +143,13 @@ k_pa_binary(const __grid_constant__ FpsTableView t, const long long* __restrict_
 // Warps split the active features, lanes split the class columns (float4 each); the decision
 // vector d = W^T x is reduced across warps in shared memory, tau/y per class is computed once,
 // then every warp scatters its features' row deltas.
-// 4 CTAs per SM (64 registers): measured on config 4 against 3 (72 registers) and 2 (92): 0.722 / 0.931 / 1.135 ms
-__global__ void __launch_bounds__(PA_THREADS, 4)
+// 64 registers (1024 threads per SM): with 256-thread CTAs measured against 72 and 92 registers: 0.722 / 0.931 / 1.135 ms
+__global__ void __launch_bounds__(PM_THREADS, 1024 / PM_THREADS)
 k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__ indptr,
            const int* __restrict__ indices, const float* __restrict__ values,
            const int* __restrict__ labels, long long n, const FpsPaParams p,
            const float* __restrict__ cost, int* __restrict__ pred, int warps_pulling, int pull_u, FpsFlow* flow) {
-  constexpr int WPB = PA_THREADS / 32;
+  constexpr int WPB = PM_THREADS / 32;
   extern __shared__ __align__(16) float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nvec = t.stride >> 2, L = p.n_classes;
@@ -225,7 +229,7 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
     for (int o = 16; o > 0; o >>= 1) n2 += __shfl_xor_sync(0xffffffffu, n2, o);
     if (lane == 0) s_n2[warp] = n2;
     __syncthreads();
-    for (int j = threadIdx.x; j < t.stride; j += PA_THREADS) {
+    for (int j = threadIdx.x; j < t.stride; j += PM_THREADS) {
       float d = 0.f;
 #pragma unroll
       for (int w = 0; w < WPB; ++w) d += s_part[w * t.stride + j];
@@ -271,7 +275,7 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
       if (p.multiclass == 1) {
         // one-vs-all: per-class multiplier tau_c * y_c, written over s_d
         float lsum = 0.f;
-        for (int j = threadIdx.x; j < t.stride; j += PA_THREADS) {
+        for (int j = threadIdx.x; j < t.stride; j += PM_THREADS) {
           float mult = 0.f;
           if (j < L) {
             const float yc = (j == y) ? 1.f : -1.f;
@@ -317,7 +321,7 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
       } else if (p.multiclass >= 2 && s_q != y) {
         const float tau = s_tau;
         const int q = s_q;
-        for (long long k = b + threadIdx.x; k < end; k += PA_THREADS) {
+        for (long long k = b + threadIdx.x; k < end; k += PM_THREADS) {
           const long long id = indices[k];
           const float x = values[k];
           const RowRef r = locate(t, id);
@@ -333,7 +337,7 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
     __syncthreads();
   }
   if (p.pull_limit > 0) flow_release(flow, credits);
-  pa_flush(c, flow);
+  pa_flush<PM_THREADS>(c, flow);
 }
 
 }  // namespace
@@ -373,20 +377,22 @@ extern "C" int fps_pa_step_cost(const FpsTableView* weights, const int64_t* d_in
   } else {
     FPS_REQUIRE(weights->stride % 4 == 0 && weights->dim == params->n_classes, FPS_E_INVALID,
                 "fps_pa_step: multiclass table must have dim == n_classes (%d vs %d)", weights->dim, params->n_classes);
-    const size_t smem = (size_t)(PA_THREADS / 32 + 1) * weights->stride * sizeof(float);
+    constexpr int PMT = PM_THREADS;
+    const size_t smem = (size_t)(PMT / 32 + 1) * weights->stride * sizeof(float);
     FPS_REQUIRE(smem <= 200 * 1024, FPS_E_UNSUPPORTED, "fps_pa_step: too many classes (%d)", params->n_classes);
     if (smem > 48 * 1024) FPS_CUDA(cudaFuncSetAttribute(k_pa_multi, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long blocks = n_examples;
-    if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
-    int warps_pulling = PA_THREADS / 32, pull_u = 4;        // = PULL_U of the kernel
+    if (blocks > (long long)sms * (2048 / PMT)) blocks = (long long)sms * (2048 / PMT);
+    int warps_pulling = PMT / 32, pull_u = 4;        // = PULL_U of the kernel
     if (params->pull_limit > 0) {
       const long long limit = params->pull_limit;
       if (limit < 4) { pull_u = (int)limit; warps_pulling = 1; }
-      else if (limit < 4 * (PA_THREADS / 32)) warps_pulling = (int)(limit / 4);
+      else if (limit < 4 * (PMT / 32)) warps_pulling = (int)(limit / 4);
       const long long fit = limit / (warps_pulling * pull_u);
-      if (fit < (long long)sms * 8 && blocks > fit) blocks = fit > 0 ? fit : 1;
+      // CTAs beyond the resident ones (64 registers: 1024 threads per SM) hold no credits until they start
+      if (fit < (long long)sms * (1024 / PMT) && blocks > fit) blocks = fit > 0 ? fit : 1;
     }
-    k_pa_multi<<<(int)blocks, PA_THREADS, smem, st>>>(*weights, (const long long*)d_indptr, d_indices, d_values,
+    k_pa_multi<<<(int)blocks, PMT, smem, st>>>(*weights, (const long long*)d_indptr, d_indices, d_values,
                                                       d_labels, n_examples, *params, d_cost, d_pred, warps_pulling,
                                                       pull_u, d_flow);
   }
