@@ -205,6 +205,56 @@ __device__ __forceinline__ int prune_candidates(float* cs, int* ci, int cnt, int
   return w;
 }
 
+// Warp-cooperative exact prune of one row-major list (c > k entries, c <= TK_CAP = 8 per lane) back to
+// its k best; returns the k-th best score.  Everything after the 16 coalesced loads runs in
+// registers: common-prefix skip, then one REDUX per remaining key bit, then a ballot compaction.
+template <int CAP = TK_CAP>
+__device__ __forceinline__ float prune_row(float* rs, int* ri, int c, int k, int lane) {
+  constexpr int PER = CAP / 32;
+  uint32_t key[PER];
+  int id[PER];
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int idx = lane + 32 * i;
+    const bool valid = idx < c;
+    key[i] = valid ? f2key(rs[idx]) : 0u;      // 0 sorts below every real score
+    id[i] = valid ? ri[idx] : -1;
+  }
+  const uint32_t key0 = __shfl_sync(0xffffffffu, key[0], 0);
+  uint32_t diff = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) diff |= (lane + 32 * i < c) ? (key[i] ^ key0) : 0u;
+  diff = __reduce_or_sync(0xffffffffu, diff);
+  const int hb = diff ? 31 - __clz(diff) : -1;
+  uint32_t T = hb >= 0 ? (key0 & ~((2u << hb) - 1u)) : key0;
+  for (int b = hb; b >= 0; --b) {
+    const uint32_t trial = T | (1u << b);
+    int n = 0;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) n += (key[i] >= trial);
+    n = __reduce_add_sync(0xffffffffu, n);
+    if (n >= k) T = trial;
+  }
+  int n_above = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) n_above += (key[i] > T);
+  n_above = __reduce_add_sync(0xffffffffu, n_above);
+  const int ties_left = k - n_above;
+  const uint32_t lt = (1u << lane) - 1u;
+  int base_a = 0, base_t = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const bool a = key[i] > T, t = key[i] == T && (lane + 32 * i < c);
+    const uint32_t ma = __ballot_sync(0xffffffffu, a), mt = __ballot_sync(0xffffffffu, t);
+    const int pa = base_a + __popc(ma & lt), pt = base_t + __popc(mt & lt);
+    if (a) { rs[pa] = key2f(key[i]); ri[pa] = id[i]; }
+    else if (t && pt < ties_left) { rs[n_above + pt] = key2f(key[i]); ri[n_above + pt] = id[i]; }
+    base_a += __popc(ma);
+    base_t += __popc(mt);
+  }
+  return key2f(T);
+}
+
 // ---- N7: merge partial lists (one CTA per query, bitonic sort in shared memory) ------------------
 __global__ void __launch_bounds__(256)
 k_topk_merge(const float* __restrict__ part_s, const int* __restrict__ part_i, int n_parts, long long n_q,

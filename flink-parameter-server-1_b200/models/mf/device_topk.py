@@ -26,7 +26,7 @@ import numpy as np
 from ...ops import _native as N
 from ...ops import philox
 from ...ops.table import ShardedTable, new_flow, read_flow
-from ...ops.topk import (PackedItems, lemp_topk, lemp_topk_packed, lemp_topk_table, sort_items_by_length,
+from ...ops.topk import (PackedItems, lemp_topk, lemp_topk_filtered, lemp_topk_packed, lemp_topk_table, sort_items_by_length,
                          topk_merge)
 from ...utils.observability import nvtx_range
 
@@ -48,7 +48,9 @@ class _LocalItems:
             # one-time split + swizzle so that every query batch streams the tiles with TMA
             self.packed = PackedItems(self.rows, self.lens, self.ids)
 
-    def topk(self, q, k: int, use_pruning: bool):
+    def topk(self, q, k: int, use_pruning: bool, filters=None):
+        if filters is not None:          # (strategy, bucket_size): the reference's loop with its candidate filters
+            return lemp_topk_filtered(q, self.rows, self.lens, k, filters[0], filters[1], item_ids=self.ids)
         if getattr(self, "packed", None) is not None:
             return lemp_topk_packed(q, self.packed, k, use_pruning=use_pruning)
         return lemp_topk(q, self.rows, k, item_len=self.lens, item_ids=self.ids, use_pruning=use_pruning)
@@ -101,10 +103,15 @@ class _SeenMemory:
 
 class DeviceTopK:
     def __init__(self, n_users: int, n_items: int, num_factors: int, *, K: int = 100, worker_k: int = 75,
-                 user_memory: int = 0, use_pruning: bool = True, ctx=None):
+                 user_memory: int = 0, use_pruning: bool = True, ctx=None, candidate_filters=None,
+                 bucket_size: int = 100):
+        """``candidate_filters``: a ``LEMPPruningStrategy`` to run the reference's bucket loop with its
+        per-candidate filters on CUDA cores (``csrc/lemp_filters.cu``) instead of the tensor-core tile
+        kernel with the bucket-level LENGTH bound - same results, the reference's pruning behaviour."""
         from ...parallel.device_context import get_context
         self.ctx = ctx or get_context()
         self.K, self.worker_k, self.use_pruning = K, min(worker_k, 128), use_pruning
+        self.filters = None if candidate_filters is None else (candidate_filters, int(bucket_size))
         self.dim = num_factors
         # PS side: users; zero rows = unknown user (the reference's invalid param (-1, []))
         self.users = ShardedTable(n_users, num_factors, partition="hash", init_range=(0.0, 0.0), ctx=self.ctx)
@@ -141,7 +148,7 @@ class DeviceTopK:
         if self.items.empty:
             return (torch.full((n_q, self.worker_k), -float("inf"), device="cuda"),
                     torch.full((n_q, self.worker_k), -1, device="cuda", dtype=torch.int32))
-        return self.items.topk(q, min(self.worker_k, 128), self.use_pruning)
+        return self.items.topk(q, min(self.worker_k, 128), self.use_pruning, self.filters)
 
     def query(self, user_ids: List[int], apply_seen: bool = True):
         """Every rank calls this with the same ``user_ids``.  Returns ``(scores, item_ids)``
@@ -233,7 +240,10 @@ class DeviceLearnerGenerator:
                  range_max: float = 0.001, learning_rate: float = 0.01, negative_sample_rate: int = 0,
                  user_memory: int = 65535, K: int = 100, worker_k: int = 75, pull_limit: int = 500,
                  seed: int = 0, use_pruning: bool = True, ctx=None, dense_catalog: int = 1 << 18,
-                 refresh_every: int = 8, max_ring: int = 512):
+                 refresh_every: int = 8, max_ring: int = 512, candidate_filters=None, bucket_size: int = 100):
+        """``candidate_filters`` (a ``LEMPPruningStrategy``): score with the reference's bucket loop and the
+        strategy's per-candidate filters (``ops.topk.lemp_topk_filtered``) on a length-sorted snapshot refreshed
+        every batch, instead of the tensor-core kernels."""
         import torch
         from ...parallel.device_context import get_context
         self.ctx = ctx or get_context()
@@ -271,7 +281,10 @@ class DeviceLearnerGenerator:
         st.user_memory, st.rate, st.local_shard, st.n_rings = self.mem, int(negative_sample_rate), -2, n_users
         self._sampler = st
         self._tag = 0
-        self.dense = self.items.rows_per_shard <= dense_catalog and num_factors <= 128
+        self.filters = None if candidate_filters is None else (candidate_filters, int(bucket_size))
+        self.dense = self.filters is None and self.items.rows_per_shard <= dense_catalog and num_factors <= 128
+        if self.filters is not None:
+            refresh_every = 1          # the filters need exact lengths: no stale snapshot
         self.refresh_every = max(1, int(refresh_every))
         self.local = _LocalItems()
         self._since_refresh = 1 << 30
@@ -296,7 +309,7 @@ class DeviceLearnerGenerator:
         if self.local.empty:
             return (torch.full((n_q, self.worker_k), -float("inf"), device="cuda"),
                     torch.full((n_q, self.worker_k), -1, device="cuda", dtype=torch.int32))
-        return self.local.topk(q, self.worker_k, self.use_pruning)
+        return self.local.topk(q, self.worker_k, self.use_pruning, self.filters)
 
     def step_tensors(self, users, items, ratings):
         """``users`` / ``items`` int32, ``ratings`` fp32 device tensors - the same batch on every rank.
@@ -358,14 +371,15 @@ class DeviceLearnerGenerator:
 
 
 def ps_top_k_generator_device(src, model, num_factors: int = 10, user_memory: int = 0, K: int = 100,
-                              worker_k: int = 75, n_users: Optional[int] = None, use_pruning: bool = True):
+                              worker_k: int = 75, n_users: Optional[int] = None, use_pruning: bool = True,
+                              candidate_filters=None, bucket_size: int = 100):
     """Device twin of ``ps_top_k_generator``."""
     model = list(model)
     ratings = list(src)
     n_users = n_users or (max([e.value[0] for e in model if e.is_left] + [r.user for r in ratings]) + 1)
     n_items = max(e.value[0] for e in model if e.is_right) + 1
     gen = DeviceTopK(n_users, n_items, num_factors, K=K, worker_k=worker_k, user_memory=user_memory,
-                     use_pruning=use_pruning)
+                     use_pruning=use_pruning, candidate_filters=candidate_filters, bucket_size=bucket_size)
     gen.load_model(model)
     return gen.recommend(ratings)
 

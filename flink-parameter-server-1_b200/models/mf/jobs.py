@@ -99,21 +99,25 @@ def _device_shards(ps_parallelism: int):
     return None if get_context().distributed else max(1, min(int(ps_parallelism), 16))
 
 
-def device_pruning(strategy: LEMPPruningStrategy) -> bool:
-    """What the device top-K kernel does with a ``LEMPPruningStrategy``
-    (``pruning/LEMPPruningStrategy.scala:6-50``).  The kernel scores whole 64-item tiles on the tensor
+def device_pruning(strategy: LEMPPruningStrategy, candidate_filters: bool = False) -> bool:
+    """What the device top-K does with a ``LEMPPruningStrategy``
+    (``pruning/LEMPPruningStrategy.scala:6-50``).  The default kernel scores whole item tiles on the tensor
     cores and applies the LENGTH bound per bucket (skip every later tile once ``max|p| * |q| <= theta``).
     COORD and INCR are *per-candidate* filters that only avoid scalar dot products of items that cannot
-    enter the top-K - they never change the result, and a tile's MMA is issued for all 64 items anyway.
-    So every strategy returns exactly what the reference's would; for the ones with a COORD / INCR part
-    a ``DeviceFallbackWarning``-class note says that this part is not executed."""
+    enter the top-K - they never change the result, and a tile's MMA is issued for all its items anyway.
+    So every strategy returns exactly what the reference's would; for the ones with a COORD / INCR part a
+    ``DeviceFallbackWarning``-class note says that this part is not executed on that path.
+    ``candidate_filters=True`` (an ``engine="device"`` keyword of the front-ends) runs the reference's own
+    bucket loop with the chosen strategy's filters on CUDA cores instead (``csrc/lemp_filters.cu``,
+    ``ops.topk.lemp_topk_filtered``): same results, the reference's pruned / scored counts, not the fast path."""
     from .pruning import LENGTH
-    if not isinstance(strategy, LENGTH):
+    if not candidate_filters and not isinstance(strategy, LENGTH):
         import warnings
         from ...parallel.device_engine import DeviceFallbackWarning
         warnings.warn(f"engine='device': pruning strategy {strategy!r} runs as the LENGTH bucket bound; its "
                       "COORD / INCR candidate filters do not change results and are not executed on the "
-                      "tensor-core path", DeviceFallbackWarning, stacklevel=3)
+                      "tensor-core path (candidate_filters=True runs them on CUDA cores)", DeviceFallbackWarning,
+                      stacklevel=3)
     return True
 
 
@@ -138,8 +142,11 @@ def ps_top_k_generator(src, model, num_factors: int = 10, user_memory: int = 0, 
     Returns ``[(item, timestamp, [(score, item), ...]), ...]``."""
     if _use_device(engine):
         from .device_topk import ps_top_k_generator_device
+        filters = bool(engine_kw.pop("candidate_filters", False))
         return ps_top_k_generator_device(src, model, num_factors, user_memory, K, worker_k,
-                                         use_pruning=device_pruning(pruning_algorithm), **engine_kw)
+                                         use_pruning=device_pruning(pruning_algorithm, filters),
+                                         candidate_filters=pruning_algorithm if filters else None,
+                                         bucket_size=bucket_size, **engine_kw)
     invalid = (-1, np.zeros(0))
     worker = PSTopKGeneratorWorker(worker_k, bucket_size, worker_parallelism, pruning_algorithm)
     logic = add_pull_limiter(worker, pull_limit)
@@ -164,10 +171,12 @@ def ps_online_learner_and_generator(src, num_factors: int = 10, range_min: float
     ``engine="device"`` needs ``n_users`` and ``n_items`` (table sizes) among the keyword arguments."""
     if _use_device(engine):
         from .device_topk import ps_online_learner_and_generator_device
+        filters = bool(engine_kw.pop("candidate_filters", False))
         out, _lg = ps_online_learner_and_generator_device(
             src, num_factors=num_factors, range_min=range_min, range_max=range_max, learning_rate=learning_rate,
             negative_sample_rate=negative_sample_rate, user_memory=user_memory, K=K, worker_k=worker_k,
-            pull_limit=pull_limit, seed=seed, use_pruning=device_pruning(pruning_algorithm), **engine_kw)
+            pull_limit=pull_limit, seed=seed, use_pruning=device_pruning(pruning_algorithm, filters),
+            candidate_filters=pruning_algorithm if filters else None, bucket_size=bucket_size, **engine_kw)
         return out
     item_desc = RangedRandomFactorInitializerDescriptor(num_factors, range_min, range_max, seed,
                                                         philox.STREAM_ITEM)

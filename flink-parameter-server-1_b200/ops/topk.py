@@ -121,6 +121,68 @@ def topk_simt(queries, items, k: int, *, item_ids=None, scratch=None):
     return _run("simt", queries, items, k, None, item_ids, False, scratch, None)
 
 
+def _strategy_code(strategy):
+    """``LEMPPruningStrategy`` (or its string form) -> ``(code, n_focus, switch_threshold)`` of the C ABI."""
+    from ..models.mf import pruning as P
+    if isinstance(strategy, str):
+        strategy = P.from_string(strategy)
+    if isinstance(strategy, P.LENGTH):
+        return 0, 0, 0.0
+    if isinstance(strategy, P.COORD):
+        return 1, 0, 0.0
+    if isinstance(strategy, P.INCR):
+        return 2, int(strategy.num_focus_coordinates), 0.0
+    if isinstance(strategy, P.LC):
+        return 3, 0, float(strategy.algorithm_switch_threshold)
+    if isinstance(strategy, P.LI):
+        return 4, int(strategy.num_focus_coordinates), float(strategy.algorithm_switch_threshold)
+    raise TypeError(f"not a LEMP pruning strategy: {strategy!r}")
+
+
+def lemp_keep_mask(queries, items_sorted, item_len, theta, strategy, bucket_size: int):
+    """``keep[q, i]`` (bool): does item ``i`` pass the predicate its bucket gets under ``strategy`` for query
+    ``q`` at threshold ``theta[q]`` - the device twins of ``lengthPruning`` / ``coordPruning`` /
+    ``incrPruning`` (``pruning/LEMPPruningFunctions.scala:10-90``) chosen per bucket as in
+    ``PSTopKGeneratorWorker.scala:82-96``.  Items sorted by length descending."""
+    import torch
+    code, n_focus, thr = _strategy_code(strategy)
+    q = _pad4(queries.float())
+    it = _pad4(items_sorted.float())
+    n_q, n_items, dim = q.shape[0], it.shape[0], queries.shape[1]
+    keep = torch.empty((n_q, n_items), device="cuda", dtype=torch.uint8)
+    th = theta.float().contiguous()
+    ln = item_len.float().contiguous()
+    N.check(N.lib().fps_lemp_keep_mask(N.ptr(q), q.shape[1], n_q, N.ptr(it), it.shape[1], N.ptr(ln), n_items, dim,
+                                       N.ptr(th), int(bucket_size), code, n_focus, thr, N.ptr(keep),
+                                       N.current_stream()), "fps_lemp_keep_mask")
+    return keep.bool()
+
+
+def lemp_topk_filtered(queries, items_sorted, item_len, k: int, strategy, bucket_size: int, *, item_ids=None,
+                       stats=None):
+    """The reference's bucketed LEMP retrieval with its candidate filters executed on the device
+    (``PSTopKGeneratorWorker.scala:49-111``; one warp per query, CUDA cores).  Exact like every other path;
+    ``stats`` (uint64[4], accumulated): candidates seen, pruned, scored, buckets skipped - the numbers the
+    host engine's ``lemp_top_k(..., stats=)`` counts.  The parity path: ``lemp_topk_packed`` is the fast one."""
+    import torch
+    code, n_focus, thr = _strategy_code(strategy)
+    q = _pad4(queries.float())
+    it = _pad4(items_sorted.float())
+    n_q, n_items, dim = q.shape[0], it.shape[0], queries.shape[1]
+    ln = item_len.float().contiguous()
+    part_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
+    part_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
+    out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
+    out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
+    ids = None if item_ids is None else item_ids.int().contiguous()
+    with nvtx_range("fps.topk.filtered"):
+        N.check(N.lib().fps_lemp_topk_filtered(N.ptr(q), q.shape[1], n_q, N.ptr(it), it.shape[1], N.ptr(ln), N.ptr(ids),
+                                               n_items, dim, int(k), int(bucket_size), code, n_focus, thr,
+                                               N.ptr(part_s), N.ptr(part_i), N.ptr(out_s), N.ptr(out_i),
+                                               N.ptr(stats), N.current_stream()), "fps_lemp_topk_filtered")
+    return out_s, out_i
+
+
 def topk_merge(part_scores, part_ids, k_out: int, seen=None):
     """``part_scores`` / ``part_ids``: ``[n_q, n_parts, k_in]``.  ``seen``: ``[n_q, m]`` int32 item ids
     to drop (-1 padded)."""

@@ -353,6 +353,26 @@ int fps_topk_simt(const float* d_queries, int32_t q_stride, int64_t n_q,
                   const float* d_items, int32_t item_stride, const int32_t* d_item_ids,
                   int64_t n_items, int32_t dim, int32_t k, void* d_scratch, size_t scratch_bytes,
                   float* d_out_scores, int32_t* d_out_ids, void* stream);
+/* LEMP candidate filters executed on the device (E11 / E12; csrc/lemp_filters.cu).  strategy: 0 LENGTH,
+ * 1 COORD, 2 INCR(n_focus), 3 LC(switch_threshold), 4 LI(n_focus, switch_threshold)
+ * (pruning/LEMPPruningStrategy.scala:6-50); n_focus <= 16.  Items sorted by length descending, cut into
+ * buckets of bucket_size; a bucket's predicate is chosen and parameterised as in
+ * PSTopKGeneratorWorker.scala:82-96.
+ * fps_lemp_keep_mask: d_keep[q, i] = 1 if item i passes its bucket's predicate for query q at d_theta[q].
+ * fps_lemp_topk_filtered: the reference's whole retrieval loop, one warp per query, scalar fp32 dot
+ *   products for the survivors - the parity path of the tensor-core kernels above, which apply only the
+ *   bucket-level LENGTH bound.  d_part_scores / d_part_ids: [n_q, k] scratch; d_stats (optional, 4 x
+ *   uint64, accumulated): candidates seen, candidates pruned, dot products, buckets skipped.          */
+int fps_lemp_keep_mask(const float* d_queries, int32_t q_stride, int64_t n_q, const float* d_items,
+                       int32_t item_stride, const float* d_item_len, int64_t n_items, int32_t dim,
+                       const float* d_theta, int32_t bucket_size, int32_t strategy, int32_t n_focus,
+                       float switch_threshold, uint8_t* d_keep, void* stream);
+int fps_lemp_topk_filtered(const float* d_queries, int32_t q_stride, int64_t n_q, const float* d_items,
+                           int32_t item_stride, const float* d_item_len, const int32_t* d_item_ids,
+                           int64_t n_items, int32_t dim, int32_t k, int32_t bucket_size, int32_t strategy,
+                           int32_t n_focus, float switch_threshold, float* d_part_scores,
+                           int32_t* d_part_ids, float* d_out_scores, int32_t* d_out_ids, uint64_t* d_stats,
+                           void* stream);
 /* Merge n_parts partial top-k lists per query (X8: CollectTopKFromEachWorker.scala:40-48) with an
  * optional per-query seen-set filter (d_seen: [n_q, seen_stride] item ids, -1 padded).            */
 int fps_topk_merge(const float* d_part_scores, const int32_t* d_part_ids, int32_t n_parts,

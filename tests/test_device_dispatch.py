@@ -273,6 +273,33 @@ def test_ps_top_k_generator_on_both_engines(engine):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("strategy", ["coord", "li:3:1.5"])
+def test_ps_top_k_generator_device_with_candidate_filters(strategy):
+    """engine="device", candidate_filters=True: the reference's bucket loop with the strategy's own filters on
+    the device (no LENGTH-only note), same answers as brute force."""
+    import warnings
+    from fps_b200.models.mf import attach_length, ps_top_k_generator
+    from fps_b200.models.mf.pruning import from_string
+    rng = np.random.default_rng(6)
+    k, n_items, n_users = 8, 500, 10
+    items = (rng.normal(size=(n_items, k)) * rng.uniform(0.1, 3.0, size=(n_items, 1))).astype(np.float32)
+    users = rng.normal(size=(n_users, k)).astype(np.float32)
+    model = ([Left((u, attach_length(users[u]))) for u in range(n_users)] +
+             [Right((i, attach_length(items[i]))) for i in range(n_items)])
+    queries = [Rating(u, 0, 1.0, 100 + u) for u in range(n_users)]
+    with warnings.catch_warnings():
+        warnings.simplefilter("error", DE.DeviceFallbackWarning)
+        res = ps_top_k_generator(queries, model, num_factors=k, K=5, worker_k=5, user_memory=-1, bucket_size=40,
+                                 pruning_algorithm=from_string(strategy), worker_parallelism=2, ps_parallelism=2,
+                                 iteration_wait_time=10, engine="device", candidate_filters=True)
+    by_ts = {ts: topk for (_item, ts, topk) in res}
+    for u in range(n_users):
+        want = np.argsort(-(items.astype(np.float64) @ users[u].astype(np.float64)))[:5]
+        got = [i for _s, i in by_ts[100 + u]]
+        assert got[0] == want[0] and len(set(got) & set(want.tolist())) >= 4, (strategy, u, got, want)
+
+
+@pytest.mark.gpu
 def test_learner_generator_entry_point_dispatches_and_announces_pruning():
     from fps_b200.models.mf import ps_online_learner_and_generator
     rnd = random.Random(2)
@@ -283,3 +310,19 @@ def test_learner_generator_entry_point_dispatches_and_announces_pruning():
                                               engine="device", n_users=40, n_items=40, batch_size=50)
     assert len(out) == len(stream)
     assert out.hit_rate(1000) > out.hit_rate(0) - 0.05 and out.hit_rate(1000) > 0.3      # 10 of 40 items = 0.25 by chance
+
+
+@pytest.mark.gpu
+def test_learner_generator_with_candidate_filters_runs_the_strategy_on_the_device():
+    import warnings
+    from fps_b200.models.mf import ps_online_learner_and_generator
+    rnd = random.Random(2)
+    stream = [Rating(u := rnd.randrange(40), (u % 4) * 10 + rnd.randrange(10), 1.0, t) for t in range(1200)]
+    with warnings.catch_warnings():
+        warnings.simplefilter("error", DE.DeviceFallbackWarning)            # LI(5, 2.5) is executed, not announced
+        out = ps_online_learner_and_generator(stream, num_factors=8, range_min=-0.1, range_max=0.1, learning_rate=0.1,
+                                              negative_sample_rate=3, user_memory=4, K=10, worker_k=10, pull_limit=500,
+                                              bucket_size=8, engine="device", candidate_filters=True, n_users=40,
+                                              n_items=40, batch_size=50)
+    assert len(out) == len(stream)
+    assert out.hit_rate(800) > 0.3

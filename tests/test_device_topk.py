@@ -186,3 +186,73 @@ def test_wide_kernel_fill_plan_covers_query_tile_boundaries(monkeypatch):
     env = dict(os.environ, FPS_TOPK_FILL="1")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=200, env=env)
     assert r.returncode == 0 and "FILL_OK" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+def _skewed_problem(n_q, n_items, dim, seed):
+    torch = pytest.importorskip("torch")
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    q = torch.randn(n_q, dim, device="cuda", generator=g)
+    lens = torch.rand(n_items, 1, device="cuda", generator=g) ** 3 * 4 + 0.05
+    items = torch.nn.functional.normalize(torch.randn(n_items, dim, device="cuda", generator=g), dim=1) * lens
+    from fps_b200.ops.topk import sort_items_by_length
+    return (q,) + sort_items_by_length(items)
+
+
+@pytest.mark.parametrize("strategy", ["length", "coord", "incr:3", "lc:1.3", "li:3:1.3"])
+def test_device_candidate_filters_match_host_predicates(strategy):
+    """lengthPruning / coordPruning / incrPruning on the device against the host restatement
+    (LEMPPruningFunctions.scala:10-90), bucket by bucket as PSTopKGeneratorWorker.scala:82-96 picks them."""
+    torch = pytest.importorskip("torch")
+    from fps_b200.models.mf import pruning as P
+    from fps_b200.ops.topk import lemp_keep_mask
+    n_q, n_items, dim, bucket = 6, 400, 16, 48
+    q, it, ln, ids = _skewed_problem(n_q, n_items, dim, 11)
+    scores = q.double() @ it.double().T
+    theta = scores.topk(40, dim=1).values[:, -1].float()          # the 40th best score of every query
+    keep = lemp_keep_mask(q, it, ln, theta, strategy, bucket).cpu().numpy()
+    strat = P.from_string(strategy)
+    qn, itn, lnn = q.double().cpu().numpy(), it.double().cpu().numpy(), ln.double().cpu().numpy()
+    want = np.zeros_like(keep)
+    for a in range(n_q):
+        user = (float(np.linalg.norm(qn[a])), qn[a])
+        focus, fset = P.focus_coordinate(qn[a]), P.focus_set(qn[a], strat.num_focus)
+        for b0 in range(0, n_items, bucket):
+            b1 = min(n_items, b0 + bucket)
+            pred = P.bucket_filter(strat, user, float(theta[a]), lnn[b0], lnn[b1 - 1], focus, fset)
+            for i in range(b0, b1):
+                want[a, i] = pred((i, (lnn[i], itn[i])))
+    mism = int((keep != want).sum())
+    assert mism <= max(2, keep.size // 500), f"{strategy}: {mism} of {keep.size} predicates differ"
+    if strategy != "length":
+        assert 0 < want.sum() < want.size              # the filter does prune and does keep
+    # safe filters: nothing that beats theta is ever dropped
+    beats = (scores.cpu().numpy() > theta.cpu().numpy()[:, None] * (1 + 1e-6) + 1e-6)
+    assert not (beats & ~keep).any()
+
+
+@pytest.mark.parametrize("strategy", ["length", "coord", "incr:4", "lc:1.5", "li:5:2.5"])
+def test_filtered_retrieval_is_exact_and_counts_like_the_host(strategy):
+    torch = pytest.importorskip("torch")
+    from fps_b200.models.mf import pruning as P
+    from fps_b200.models.mf.workers import lemp_top_k
+    from fps_b200.ops.topk import lemp_topk_filtered
+    n_q, n_items, dim, k, bucket = 24, 3000, 24, 20, 64
+    q, it, ln, ids = _skewed_problem(n_q, n_items, dim, 12)
+    stats = torch.zeros(4, device="cuda", dtype=torch.int64)
+    s, i = lemp_topk_filtered(q, it, ln, k, strategy, bucket, item_ids=ids, stats=stats)
+    ref = (q.double() @ it.double().T).topk(k, dim=1)
+    assert torch.equal(ids[ref.indices].sort(dim=1).values.int(), i.sort(dim=1).values)
+    assert torch.allclose(s, ref.values.float(), rtol=1e-5, atol=1e-5)
+    seen, pruned, scored, skipped = stats.tolist()
+    assert seen == pruned + scored and scored < n_q * n_items            # the search stops early / prunes
+    # the host engine's loop over the same buckets
+    strat = P.from_string(strategy)
+    itn, lnn, idn = it.double().cpu().numpy(), ln.double().cpu().numpy(), ids.cpu().numpy()
+    model = {int(idn[j]): (float(lnn[j]), itn[j]) for j in range(n_items)}
+    desc = [(float(lnn[j]), int(idn[j])) for j in range(n_items)]
+    host = {}
+    for a in range(n_q):
+        qa = q[a].double().cpu().numpy()
+        lemp_top_k((float(np.linalg.norm(qa)), qa), desc, model, k, bucket, strat, stats=host)
+    assert abs(host.get("scored", 0) - scored) <= 0.03 * host["scored"] + 64, (host, stats.tolist())
+    assert abs(host.get("pruned", 0) - pruned) <= 0.03 * max(host.get("pruned", 0), 1) + 64, (host, stats.tolist())
