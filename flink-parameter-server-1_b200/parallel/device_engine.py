@@ -251,12 +251,56 @@ class TensorWorkerLogic:
         pass
 
 
+def conflict_free_rounds(ids):
+    """The device form of the per-key lock of ``LockPSLogicA`` (``M/server/LockPSLogicA.scala:13-46``): a
+    pull of a key that is locked waits until the push of the pull before it has been applied.  For a batch of
+    pulls that is a schedule in rounds - record ``j`` runs in round ``r`` if ``r`` earlier records of the
+    batch asked for the same key - and inside a round no key occurs twice, so gather -> program -> scatter of
+    a round is a set of independent read-modify-write cycles.  Returns the list of index tensors (positions in
+    arrival order) of the rounds, computed on the device (stable sort + run starts)."""
+    import torch
+    n = int(ids.numel())
+    if n == 0:
+        return []
+    order = torch.argsort(ids, stable=True)
+    s = ids[order]
+    idx = torch.arange(n, device=ids.device)
+    start = torch.ones(n, dtype=torch.bool, device=ids.device)
+    start[1:] = s[1:] != s[:-1]
+    first = torch.cummax(torch.where(start, idx, torch.zeros_like(idx)), 0).values
+    rank = torch.empty_like(idx)
+    rank[order] = idx - first
+    n_rounds = int(rank.max().item()) + 1
+    if n_rounds == 1:
+        return [idx]
+    return [torch.nonzero(rank == r).flatten() for r in range(n_rounds)]
+
+
+def _index_batch(batch, index, n: int):
+    """``_slice_batch`` with an index tensor."""
+    import torch
+    if isinstance(batch, torch.Tensor):
+        return batch[index.to(batch.device)] if batch.dim() and batch.shape[0] == n else batch
+    if isinstance(batch, (tuple, list)):
+        return type(batch)(_index_batch(b, index, n) for b in batch)
+    if isinstance(batch, dict):
+        return {k: _index_batch(v, index, n) for k, v in batch.items()}
+    return batch
+
+
 def run_tensor_logic(batches, logic: TensorWorkerLogic, n_ids: int, dim: int, *, init_range=(0.0, 0.0),
                      update_mode: str = "add", pull_limit: int = 0, lazy: bool = True, partition: str = "hash",
-                     seed: int = 0, n_shards=None, aux_cols: int = 0, return_table: bool = False):
+                     seed: int = 0, n_shards=None, aux_cols: int = 0, return_table: bool = False,
+                     locking: bool = False):
     """The device twin of ``transform`` for a ``TensorWorkerLogic``.  Returns the output stream:
     ``Left(output tensor)`` per batch that produced one, then ``Right((id, row))`` for every live row of
-    the local shard (on-close form)."""
+    the local shard (on-close form).
+
+    ``locking=True`` is the device twin of ``LockPSLogicA`` / ``LockPSLogicB``: every batch is run in
+    conflict-free rounds (``conflict_free_rounds``), so the read-modify-write cycles on one key happen one
+    after the other in arrival order and the result of a rank's stream is the sequential one - whatever
+    ``param_update`` is.  The lock is the rank's: cycles of different ranks on one key still interleave
+    (asynchronous semantics), as they do between the reference's workers whenever the lock is free."""
     import torch
     from ..entities import Left, Right
     from ..ops import philox
@@ -270,9 +314,7 @@ def run_tensor_logic(batches, logic: TensorWorkerLogic, n_ids: int, dim: int, *,
     flow = new_flow()
     logic.open(table, ctx)
     out = []
-    for batch in batches:
-        ids = logic.pull_ids(batch)
-        ids = ids.to(device="cuda", dtype=torch.int64)
+    def run_part(batch, ids):
         step = int(pull_limit) if pull_limit and pull_limit > 0 else max(int(ids.numel()), 1)
         for s in range(0, max(int(ids.numel()), 1), step):
             part = ids[s:s + step]
@@ -283,6 +325,19 @@ def run_tensor_logic(batches, logic: TensorWorkerLogic, n_ids: int, dim: int, *,
                 table.scatter(push_ids, deltas, update_mode, flow)
             if produced is not None:
                 out.append(Left(produced))
+
+    for batch in batches:
+        ids = logic.pull_ids(batch)
+        ids = ids.to(device="cuda", dtype=torch.int64)
+        if not locking:
+            run_part(batch, ids)
+            continue
+        rounds = conflict_free_rounds(ids)
+        for index in rounds:
+            if len(rounds) == 1:
+                run_part(batch, ids)
+            else:
+                run_part(_index_batch(batch, index, int(ids.numel())), ids[index])
     logic.close()
     torch.cuda.synchronize()
     ctx.barrier()
@@ -311,5 +366,8 @@ def _run_tensor_job(job: DeviceJob) -> list:
     n_ids, dim = kw.pop("n_ids", None), kw.pop("dim", None)
     if n_ids is None or dim is None:
         raise ValueError("a TensorWorkerLogic job needs device_kw={'n_ids': ..., 'dim': ...}")
+    if "locking" not in kw:           # a lock logic on the server side asks for the lock schedule
+        from ..server.logics import LockPSLogicA
+        kw["locking"] = isinstance(job.ps_logic, LockPSLogicA)
     return run_tensor_logic(job.records, job.logic, n_ids, dim, update_mode=job.update_mode or "add",
                             pull_limit=job.pull_limit, **kw)

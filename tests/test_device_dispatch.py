@@ -326,3 +326,88 @@ def test_learner_generator_with_candidate_filters_runs_the_strategy_on_the_devic
                                               n_items=40, batch_size=50)
     assert len(out) == len(stream)
     assert out.hit_rate(800) > 0.3
+
+
+@pytest.mark.gpu
+def test_lock_logic_on_the_device_is_the_sequential_read_modify_write():
+    """LockPSLogicA on both engines (LockPSLogicA.scala:13-46): x <- 0.5 * x + v per record with an overwriting
+    update.  With the lock, the cycles on one key run one after the other in arrival order (device: conflict-free
+    rounds), so both engines give the sequential result; without it the device loses the earlier of two
+    updates of a key in one batch."""
+    import torch
+    from collections import defaultdict, deque
+    from fps_b200.api import WorkerLogic
+    from fps_b200.parallel.device_engine import TensorWorkerLogic, conflict_free_rounds
+    from fps_b200.server.logics import LockPSLogicA
+
+    rng = np.random.default_rng(3)
+    n_keys, n = 12, 300
+    keys = rng.integers(0, n_keys, size=n)
+    vals = rng.normal(size=n).astype(np.float32)
+    want = np.zeros(n_keys)
+    for k, v in zip(keys, vals):
+        want[k] = 0.5 * want[k] + v
+
+    # the rounds themselves: no key twice in a round, arrival order kept per key
+    rounds = conflict_free_rounds(torch.from_numpy(keys).cuda())
+    seen_upto = defaultdict(lambda: -1)
+    for r in rounds:
+        ks = keys[r.cpu().numpy()]
+        assert len(set(ks.tolist())) == len(ks)
+        for pos, k in zip(r.cpu().numpy().tolist(), ks.tolist()):
+            assert pos > seen_upto[k]
+            seen_upto[k] = pos
+    assert sum(int(r.numel()) for r in rounds) == n
+
+    overwrite = lambda old, new: new                                     # noqa: E731
+    DE.register_param_update(overwrite, "overwrite")
+
+    class Decay(TensorWorkerLogic):
+        def pull_ids(self, batch):
+            return batch[0]
+
+        def on_pull_batch(self, batch, ids, rows):
+            return ids, 0.5 * rows[:, :1] + batch[1][:, None], None
+
+    batches = [(torch.from_numpy(keys[s:s + 100]).cuda(), torch.from_numpy(vals[s:s + 100]).cuda())
+               for s in range(0, n, 100)]
+    kw = dict(n_ids=n_keys, dim=1, init_range=(0.0, 0.0), n_shards=2)
+    out = transform(batches, Decay(), ps_logic=LockPSLogicA(lambda _k: 0.0, overwrite), worker_parallelism=1,
+                    ps_parallelism=2, iteration_wait_time=10, engine="device", device_kw=kw)
+    got = last_write_wins(rights(out))
+    np.testing.assert_allclose([float(got[k][0]) for k in range(n_keys)], want, rtol=1e-5, atol=1e-6)
+
+    out_free = transform(batches, Decay(), ps_logic=LockPSLogicA(lambda _k: 0.0, overwrite), worker_parallelism=1,
+                         ps_parallelism=2, iteration_wait_time=10, engine="device", device_kw=dict(kw, locking=False))
+    free = last_write_wins(rights(out_free))
+    assert max(abs(float(free[k][0]) - want[k]) for k in range(n_keys)) > 1e-2        # lost updates
+
+    # host engine, the reference's per-record logic under the same lock logic
+    class DecayHost(WorkerLogic):
+        def __init__(self):
+            self.pending = defaultdict(deque)
+
+        def on_recv(self, data, ps):
+            self.pending[data[0]].append(data[1])
+            ps.pull(data[0])
+
+        def on_pull_recv(self, param_id, value, ps):
+            ps.push(param_id, 0.5 * value + self.pending[param_id].popleft())
+
+    host = transform(list(zip(keys.tolist(), vals.tolist())), DecayHost(),
+                     ps_logic=LockPSLogicA(lambda _k: 0.0, overwrite), worker_parallelism=1, ps_parallelism=2,
+                     iteration_wait_time=10, engine="host")
+    hostm = last_write_wins(rights(host))
+    np.testing.assert_allclose([float(hostm[k]) for k in range(n_keys)], want, rtol=1e-5, atol=1e-6)
+
+
+def test_conflict_free_rounds_schedule():
+    """The lock schedule of the device engine (CPU tensors work too): round r holds the records that r earlier
+    records of the batch share their key with."""
+    import torch
+    from fps_b200.parallel.device_engine import conflict_free_rounds
+    rounds = conflict_free_rounds(torch.tensor([3, 1, 3, 3, 2, 1, 0]))
+    assert [r.tolist() for r in rounds] == [[0, 1, 4, 6], [2, 5], [3]]
+    assert conflict_free_rounds(torch.tensor([], dtype=torch.int64)) == []
+    one = conflict_free_rounds(torch.tensor([5, 6, 7]))
+    assert len(one) == 1 and one[0].tolist() == [0, 1, 2]
