@@ -312,6 +312,62 @@ k_flush_delta(const __grid_constant__ FpsTableView t, long long n_floats) {
   }
 }
 
+// ---- N13: per-row lock word, system-scope CAS (LockPSLogicA.scala:13-46 on the device) ---------------------
+// x <- alpha * x + delta as a LOCKED read-modify-write: the reference's lock logic answers a pull only when
+// the push of the pull before it has been applied, which makes a worker's pull -> compute -> push an
+// exclusive cycle per key.  Here the cycle is one warp's: lane 0 takes the row's lock word (an int32 living
+// in an auxiliary column of the row itself, so it is in the owner's memory and reachable over NVLink like
+// the row), the warp reads the row, applies the update, writes it back, and lane 0 releases the lock.  A warp
+// holds at most one lock, so there is no cycle of waiters; waiters back off with __nanosleep.
+// `use_lock == 0` runs the same read-modify-write unprotected (what an overwriting param_update does without
+// the lock logic: updates get lost) - kept for the test that shows the difference.
+__global__ void __launch_bounds__(256)
+k_table_locked_axpby(const __grid_constant__ FpsTableView t, const long long* __restrict__ ids, long long n,
+                     float alpha, const float* __restrict__ deltas, int delta_stride, int lock_col, int use_lock,
+                     FpsFlow* flow) {
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+  unsigned long long spins = 0, done = 0, bad = 0;
+  for (long long k = warp0; k < n; k += n_warps) {
+    const long long id = ids[k];
+    const RowRef r = locate(t, id);
+    if (!in_table(t, id, r)) { if (lane == 0) ++bad; continue; }
+    float* row = t.rows[r.owner] + r.slot * t.stride;
+    int* lock = reinterpret_cast<int*>(row + lock_col);
+    if (use_lock) {
+      if (lane == 0) {
+        unsigned ns = 32;
+        while (atomicCAS_system(lock, 0, 1) != 0) {
+          __nanosleep(ns);
+          if (ns < 2048) ns <<= 1;
+          ++spins;
+        }
+        __threadfence_system();                 // acquire: the row reads below come after the lock
+      }
+      __syncwarp();
+    }
+    if (t.lazy && lane == 0) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
+    for (int c = lane; c < t.dim; c += 32) {
+      float x;
+      asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(x) : "l"(row + c) : "memory");
+      x = fmaf(alpha, x, deltas[k * delta_stride + c]);
+      asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(row + c), "f"(x) : "memory");
+    }
+    if (use_lock) {
+      __threadfence_system();                   // release: the row is written before the lock opens
+      __syncwarp();
+      if (lane == 0) atomicExch_system(lock, 0);
+    }
+    if (lane == 0) ++done;
+  }
+  if (flow != nullptr && lane == 0) {
+    if (done) { atomicAdd((unsigned long long*)&flow->pushes, done); atomicAdd((unsigned long long*)&flow->pulls, done); }
+    if (bad) atomicAdd((unsigned long long*)&flow->bad_ids, bad);
+    if (spins) atomicAdd((unsigned long long*)&flow->limiter_stalls, spins);
+  }
+}
+
 }  // namespace
 
 int fps_check_view(const FpsTableView* v, const char* who) { return check_view(v, who); }
@@ -444,6 +500,27 @@ int fps_table_dump_shard(const FpsTableView* view, int shard, int64_t n_rows, in
                          int64_t* d_out_ids, float* d_out_rows, int64_t capacity, int64_t* d_count,
                          void* stream) {
   return fps_table_dump_range(view, shard, 0, n_rows, n_ids_total, d_out_ids, d_out_rows, capacity, d_count, stream);
+}
+
+int fps_table_locked_axpby(const FpsTableView* view, const int64_t* d_ids, int64_t n, float alpha,
+                           const float* d_deltas, int32_t delta_stride, int32_t lock_col, int32_t use_lock,
+                           FpsFlow* d_flow, void* stream) {
+  if (int e = check_view(view, "fps_table_locked_axpby")) return e;
+  FPS_REQUIRE(d_ids && d_deltas && delta_stride >= view->dim, FPS_E_INVALID, "fps_table_locked_axpby: ids, deltas (stride >= dim) required");
+  FPS_REQUIRE(view->n_replicas <= 1, FPS_E_UNSUPPORTED, "fps_table_locked_axpby: sharded tables only (a replica has no single owner to lock)");
+  FPS_REQUIRE(lock_col >= view->dim && lock_col < view->stride, FPS_E_INVALID,
+              "fps_table_locked_axpby: the lock word lives in an auxiliary column: dim <= lock_col < stride (%d, %d, %d)",
+              view->dim, lock_col, view->stride);
+  FPS_REQUIRE(!view->lazy || (view->init_lo == 0.f && view->init_hi == 0.f), FPS_E_UNSUPPORTED,
+              "fps_table_locked_axpby: lazy tables need a zero initialiser");
+  if (n <= 0) return 0;
+  long long blocks = (n + 7) / 8;
+  const long long cap = (long long)fps_num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  k_table_locked_axpby<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(*view, (const long long*)d_ids, n, alpha, d_deltas,
+                                                                      delta_stride, lock_col, use_lock, d_flow);
+  FPS_LAUNCH_CHECK();
+  return 0;
 }
 
 }  // extern "C"

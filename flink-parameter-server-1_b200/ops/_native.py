@@ -158,6 +158,7 @@ def lib() -> C.CDLL:
         "fps_table_init_shard": (C.c_int, [P(FpsTableView), C.c_int, i64, vp]),
         "fps_table_gather": (C.c_int, [P(FpsTableView), vp, i64, vp, C.c_int, vp, vp]),
         "fps_table_scatter": (C.c_int, [P(FpsTableView), vp, i64, vp, C.c_int, C.c_int, vp, vp]),
+        "fps_table_locked_axpby": (C.c_int, [P(FpsTableView), vp, i64, C.c_float, vp, i32, i32, i32, vp, vp]),
         "fps_table_dump_shard": (C.c_int, [P(FpsTableView), C.c_int, i64, i64, vp, vp, i64, vp, vp]),
         "fps_table_dump_range": (C.c_int, [P(FpsTableView), C.c_int, i64, i64, i64, vp, vp, i64, vp, vp]),
         "fps_mf_sgd_step": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, vp, i64, P(FpsMfParams), vp, vp]),

@@ -227,6 +227,23 @@ class ShardedTable:
         if m == 0:
             self.flush_deltas()
 
+    def locked_axpby(self, ids, alpha: float, deltas, *, lock_col: Optional[int] = None, use_lock: bool = True,
+                     flow=None) -> None:
+        """``row <- alpha * row + delta`` as a locked read-modify-write per record (the device form of
+        ``LockPSLogicA``: a cycle on a key excludes every other cycle on it, on this GPU and on the peers).
+        The lock word lives in an auxiliary column of the row (``aux_cols >= 1``; default: the last one)."""
+        import torch
+        if self.aux_cols < 1 or self.stride == 1:
+            raise ValueError("locked_axpby needs a vector table with aux_cols >= 1 (the lock word's column)")
+        col = self.dim + self.aux_cols - 1 if lock_col is None else int(lock_col)
+        ids = ids.to(device="cuda", dtype=torch.int64).contiguous()
+        deltas = deltas.to(device="cuda", dtype=torch.float32).contiguous()
+        if deltas.dim() == 1:
+            deltas = deltas[:, None]
+        N.check(N.lib().fps_table_locked_axpby(C.byref(self._view), N.ptr(ids), ids.numel(), float(alpha), N.ptr(deltas),
+                                               deltas.shape[1], col, int(bool(use_lock)), N.ptr(flow),
+                                               N.current_stream()), "fps_table_locked_axpby")
+
     def flush_deltas(self) -> None:
         """Replicated table with deferred pushes: forward the deltas accumulated since the last
         flush to the other replicas (no-op for every other kind of table)."""

@@ -131,6 +131,15 @@ int fps_table_init_shard(const FpsTableView* view, int shard, int64_t n_rows, vo
 /* Gather rows by id (pull without compute): out[i, :dim] = value(ids[i]).  ids may be remote.    */
 int fps_table_gather(const FpsTableView* view, const int64_t* d_ids, int64_t n, float* d_out,
                      int out_stride, FpsFlow* d_flow, void* stream);
+/* Locked read-modify-write (N13; M/server/LockPSLogicA.scala:13-46 on the device): row <- alpha * row +
+ * delta with the row's lock word held - an int32 in auxiliary column `lock_col` of the row itself
+ * (dim <= lock_col < stride; auxiliary columns start as zero = unlocked), taken with a system-scope CAS
+ * by one lane of the warp that runs the cycle, so it also excludes warps on other GPUs.  Sharded tables
+ * only; lazy tables need the zero initialiser.  use_lock = 0 runs the same cycle unprotected (for tests).
+ * d_flow (optional): pulls / pushes += cycles, limiter_stalls += lock retries.                        */
+int fps_table_locked_axpby(const FpsTableView* view, const int64_t* d_ids, int64_t n, float alpha,
+                           const float* d_deltas, int32_t delta_stride, int32_t lock_col, int32_t use_lock,
+                           FpsFlow* d_flow, void* stream);
 /* Push rows: mode 0 = add (vectorSum), 1 = overwrite, 2 = add then store the new L2 norm in
  * column `dim` (LengthAndVector tables, stride > dim).  value semantics of SimplePSLogic
  * (M/server/SimplePSLogic.scala:16-25): an untouched row becomes exactly the pushed value.       */

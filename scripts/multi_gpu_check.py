@@ -47,6 +47,22 @@ def main():
     ok &= ok2
     print(f"[rank {rank}] remote red.add from all ranks landed: {ok2}", flush=True)
 
+    # 2b. locked read-modify-write from every rank on the same few keys (N13: lock word in the row, system-scope
+    #     CAS): non-atomic read - add 1 - write cycles; every cycle of every rank must count
+    lt = ShardedTable(29, 6, init_range=(0.0, 0.0), aux_cols=1, ctx=ctx)
+    n_cyc = 50_000
+    lids = torch.randint(0, 29, (n_cyc,), generator=torch.Generator().manual_seed(100 + rank))
+    all_counts = sum(torch.bincount(torch.randint(0, 29, (n_cyc,), generator=torch.Generator().manual_seed(100 + r)),
+                                    minlength=29) for r in range(world)).float()
+    ctx.barrier()
+    lt.locked_axpby(lids, 1.0, torch.ones((n_cyc, 6)))
+    torch.cuda.synchronize()
+    ctx.barrier()
+    lrows = lt.gather(torch.arange(29)).cpu()
+    ok2b = bool(torch.equal(lrows[:, :6], all_counts[:, None].expand(29, 6))) and bool(torch.all(lrows[:, 6] == 0))
+    ok &= ok2b
+    print(f"[rank {rank}] locked read-modify-write cycles of all ranks all counted: {ok2b}", flush=True)
+
     # 3. fused MF across ranks
     n_users, n_items, dim = 200_000, 50_000, 64
     mf = DeviceMF(n_users, n_items, dim, 0.0, 0.2, 0.05, pull_limit=1600, seed=1, ctx=ctx, replicate_items=False)

@@ -169,3 +169,45 @@ def test_every_update_stream_folds_to_the_on_close_dump():
         np.testing.assert_array_equal(items_f[k], items_c[k])
     (uu, _), (ii, _) = mf.drain_updates()
     assert len(uu) == 0 and len(ii) == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("lazy", [False, True])
+def test_locked_read_modify_write_loses_no_update(lazy):
+    """N13, the device form of LockPSLogicA (per-row lock word, system-scope CAS): 200 000 non-atomic
+    read - add 1 - write cycles on 37 keys spread over 3 shards.  Under the lock every cycle counts; the same
+    kernel without the lock loses updates, which is what the lock logic exists to prevent."""
+    import torch
+    from fps_b200.ops.table import ShardedTable, new_flow, read_flow
+    n_keys, n, dim = 37, 200_000, 5
+    g = torch.Generator().manual_seed(9)
+    ids = torch.randint(0, n_keys, (n,), generator=g)
+    ones = torch.ones((n, dim))
+    counts = torch.bincount(ids, minlength=n_keys).float()
+
+    t = ShardedTable(n_keys, dim, n_shards=3, partition="hash", init_range=(0.0, 0.0), aux_cols=1, lazy=lazy)
+    flow = new_flow()
+    t.locked_axpby(ids, 1.0, ones, flow=flow)
+    torch.cuda.synchronize()
+    rows = t.gather(torch.arange(n_keys))
+    assert torch.equal(rows[:, :dim].cpu(), counts[:, None].expand(n_keys, dim))
+    assert torch.all(rows[:, dim] == 0)                         # every lock word released
+    st = read_flow(flow)
+    assert st["pushes"] == n and st["bad_ids"] == 0
+    if lazy:
+        live, _ = t.dump()
+        assert sorted(live.tolist()) == sorted(torch.nonzero(counts).flatten().tolist())
+
+    # a decaying update is order dependent, but bounded: x <- 0.5 x + 1 stays in [1, 2)
+    t.locked_axpby(ids[:5000], 0.5, ones[:5000])
+    x = t.gather(torch.arange(n_keys))[:, :dim]
+    assert torch.all((x >= 1.0) & (x < counts.max() + 1))
+
+    free = ShardedTable(n_keys, dim, n_shards=3, partition="hash", init_range=(0.0, 0.0), aux_cols=1)
+    free.locked_axpby(ids, 1.0, ones, use_lock=False)
+    torch.cuda.synchronize()
+    lost = counts.sum() - free.gather(torch.arange(n_keys))[:, 0].cpu().sum()
+    assert lost > 0, "the unprotected cycle was expected to lose updates under this contention"
+
+    with pytest.raises(ValueError):
+        ShardedTable(8, 4, n_shards=1).locked_axpby(ids[:4] % 8, 1.0, ones[:4, :4])        # no aux column for the lock
