@@ -273,19 +273,18 @@ def config7(ctx):
     res = {"config": 7, "what": "prequential learner+generator, 69K events / 12.5K users / 19K items, rank 10, K=100, 9 negatives"}
     ps_online_learner_and_generator_device(stream[:4096], n_users=n_users, n_items=n_items, batch_size=2048,
                                            user_memory=128, **kw)          # warm-up (module load, allocator)
-    for bs in (256, 2048, 8192):
+    for bs, graph in ((64, False), (64, True), (256, False), (256, True), (2048, False), (8192, False), (8192, True)):
         torch.cuda.synchronize()
         t0 = time.time()
         out, lg = ps_online_learner_and_generator_device(stream, n_users=n_users, n_items=n_items, batch_size=bs,
-                                                         user_memory=128, **kw)
+                                                         user_memory=128, cuda_graph=graph, **kw)
         torch.cuda.synchronize()
         dt = time.time() - t0
         s = lg.stats()
-        res[f"device_batch{bs}"] = {"events_per_sec": n_events / dt, "seconds": dt,
-                                    "ndcg_last20k": out.ndcg(n_events - 20000),
-                                    "hit_rate_last20k": out.hit_rate(n_events - 20000),
-                                    "sgd_records": s["records"], "nan_count": s["nan_count"],
-                                    "max_in_flight": s["max_in_flight"]}
+        res[f"device_batch{bs}" + ("_cuda_graph" if graph else "")] = {
+            "events_per_sec": n_events / dt, "seconds": dt, "ndcg_last20k": out.ndcg(n_events - 20000),
+            "hit_rate_last20k": out.hit_rate(n_events - 20000), "sgd_records": s["records"],
+            "nan_count": s["nan_count"], "max_in_flight": s["max_in_flight"], "cuda_graph": graph}
     n_host = 3000
     t0 = time.time()
     out_h = ps_online_learner_and_generator(stream[:n_host], user_memory=128, worker_parallelism=4, ps_parallelism=4,

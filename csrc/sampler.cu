@@ -55,7 +55,9 @@ k_neg_register(const __grid_constant__ FpsTableView users, const FpsNegSampler s
 __global__ void __launch_bounds__(256)
 k_neg_draw(const __grid_constant__ FpsTableView users, const FpsNegSampler s, const int* __restrict__ uid,
            const int* __restrict__ iid, const float* __restrict__ rating, long long n, unsigned long long tag,
-           int* __restrict__ out_u, int* __restrict__ out_i, float* __restrict__ out_r) {
+           const unsigned long long* __restrict__ d_tag, int* __restrict__ out_u, int* __restrict__ out_i,
+           float* __restrict__ out_r) {
+  if (d_tag != nullptr) tag = *d_tag;          // the step tag lives on the device (launches replayed from a CUDA graph)
   const int per = s.rate + 1;
   const long long total = n * per;
   const int pool_n = *s.pool_count;
@@ -158,9 +160,10 @@ int fps_mark_live_items(const FpsTableView* items, int32_t local_shard, const in
   return 0;
 }
 
-int fps_mf_sample_negatives(const FpsTableView* users, const FpsNegSampler* sampler, const int32_t* d_user_ids,
+static int sample_negatives(const FpsTableView* users, const FpsNegSampler* sampler, const int32_t* d_user_ids,
                             const int32_t* d_item_ids, const float* d_ratings, int64_t n, uint64_t step_tag,
-                            int32_t* d_out_users, int32_t* d_out_items, float* d_out_ratings, void* stream) {
+                            const uint64_t* d_step_tag, int32_t* d_out_users, int32_t* d_out_items,
+                            float* d_out_ratings, void* stream) {
   if (int e = fps_check_view(users, "fps_mf_sample_negatives")) return e;
   FPS_REQUIRE(sampler != nullptr && sampler->seen && sampler->seen_count && sampler->item_bitmap &&
                   sampler->item_pool && sampler->pool_count,
@@ -175,10 +178,26 @@ int fps_mf_sample_negatives(const FpsTableView* users, const FpsNegSampler* samp
   if (b1 > sms * 16) b1 = sms * 16;
   if (b2 > sms * 32) b2 = sms * 32;
   k_neg_register<<<(int)b1, 256, 0, st>>>(*users, *sampler, d_user_ids, d_item_ids, n);
-  k_neg_draw<<<(int)b2, 256, 0, st>>>(*users, *sampler, d_user_ids, d_item_ids, d_ratings, n, step_tag, d_out_users,
-                                       d_out_items, d_out_ratings);
+  k_neg_draw<<<(int)b2, 256, 0, st>>>(*users, *sampler, d_user_ids, d_item_ids, d_ratings, n, step_tag,
+                                       (const unsigned long long*)d_step_tag, d_out_users, d_out_items, d_out_ratings);
   FPS_LAUNCH_CHECK();
   return 0;
+}
+
+int fps_mf_sample_negatives(const FpsTableView* users, const FpsNegSampler* sampler, const int32_t* d_user_ids,
+                            const int32_t* d_item_ids, const float* d_ratings, int64_t n, uint64_t step_tag,
+                            int32_t* d_out_users, int32_t* d_out_items, float* d_out_ratings, void* stream) {
+  return sample_negatives(users, sampler, d_user_ids, d_item_ids, d_ratings, n, step_tag, nullptr, d_out_users,
+                          d_out_items, d_out_ratings, stream);
+}
+
+int fps_mf_sample_negatives_dtag(const FpsTableView* users, const FpsNegSampler* sampler, const int32_t* d_user_ids,
+                                 const int32_t* d_item_ids, const float* d_ratings, int64_t n,
+                                 const uint64_t* d_step_tag, int32_t* d_out_users, int32_t* d_out_items,
+                                 float* d_out_ratings, void* stream) {
+  FPS_REQUIRE(d_step_tag != nullptr, FPS_E_INVALID, "fps_mf_sample_negatives_dtag: the device step tag is required");
+  return sample_negatives(users, sampler, d_user_ids, d_item_ids, d_ratings, n, 0, d_step_tag, d_out_users,
+                          d_out_items, d_out_ratings, stream);
 }
 
 }  // extern "C"

@@ -166,45 +166,6 @@ struct TopkScratch {
   int* part_i;
 };
 
-// prune the candidate list of this thread's query back to its k best; returns new count and theta
-__device__ __forceinline__ int prune_candidates(float* cs, int* ci, int cnt, int k, float& theta) {
-  if (cnt <= k) {
-    if (cnt == k) {   // theta = min of the list
-      float m = INFINITY;
-      for (int j = 0; j < cnt; ++j) m = fminf(m, cs[j * TK_M]);
-      theta = fmaxf(theta, m);
-    }
-    return cnt;
-  }
-  // the keys of one list share their leading bits (scores of similar magnitude): one pass finds the
-  // highest bit in which any two differ, the bitwise search starts there instead of at bit 31
-  const uint32_t key0 = f2key(cs[0]);
-  uint32_t diff = 0;
-  for (int j = 1; j < cnt; ++j) diff |= f2key(cs[j * TK_M]) ^ key0;
-  const int hb = diff ? 31 - __clz(diff) : -1;
-  uint32_t T = hb >= 0 ? (key0 & ~((2u << hb) - 1u)) : key0;
-  for (int b = hb; b >= 0; --b) {
-    const uint32_t trial = T | (1u << b);
-    int n = 0;
-    for (int j = 0; j < cnt; ++j) n += (f2key(cs[j * TK_M]) >= trial);
-    if (n >= k) T = trial;
-  }
-  // keep everything above T, then fill with keys equal to T up to k
-  int w = 0, above = 0;
-  for (int j = 0; j < cnt; ++j) above += (f2key(cs[j * TK_M]) > T);
-  int ties_left = k - above;
-  for (int j = 0; j < cnt; ++j) {
-    const float s = cs[j * TK_M];
-    const int id = ci[j * TK_M];
-    const uint32_t key = f2key(s);
-    bool keep = key > T;
-    if (!keep && key == T && ties_left > 0) { keep = true; --ties_left; }
-    if (keep) { cs[w * TK_M] = s; ci[w * TK_M] = id; ++w; }
-  }
-  theta = fmaxf(theta, key2f(T));
-  return w;
-}
-
 // Warp-cooperative exact prune of one row-major list (c > k entries, c <= TK_CAP = 8 per lane) back to
 // its k best; returns the k-th best score.  Everything after the 16 coalesced loads runs in
 // registers: common-prefix skip, then one REDUX per remaining key bit, then a ballot compaction.
@@ -319,7 +280,7 @@ struct Plan {
 // = 128 CTAs leave 20 of 148 SMs idle, 9 splits = 288 CTAs run as 1.95 waves); later CTAs start with
 // the theta the earlier ones published, so the extra lists cost little.  `forced_splits` > 0 overrides.
 Plan make_plan(long long n_q, int k, long long n_items, int dim, int groups = 1, int multi_wave = 0,
-               int forced_splits = 0) {
+               int forced_splits = 0, int max_splits = 16) {
   Plan p;
   p.n_q_tiles = (int)((n_q + TK_M - 1) / TK_M);
   const long long n_tiles = (n_items + TK_N - 1) / TK_N;
@@ -327,7 +288,11 @@ Plan make_plan(long long n_q, int k, long long n_items, int dim, int groups = 1,
   const int qt = p.n_q_tiles > 0 ? p.n_q_tiles : 1;
   long long splits = sms / qt;
   if (splits < 1) splits = 1;
-  if (splits > 16) splits = 16;
+  if (splits > max_splits) splits = max_splits;
+  // more than 16 splits only while the merge of their lists stays a 2048-element sort per query: measured on
+  // 256 queries x 19K items, k = 75 (ms per learner+generator step): 16 splits 0.565, 24 0.507, 32 (4096-sort)
+  // 0.550, 48 0.495, 64 (8192-sort) 0.684
+  while (splits > 16 && splits * groups * k > 2048) --splits;
   if (multi_wave) {
     auto eff = [&](long long s) { return (double)(qt * s) / (double)(((qt * s + sms - 1) / sms) * sms); };
     long long best = splits;
@@ -335,7 +300,7 @@ Plan make_plan(long long n_q, int k, long long n_items, int dim, int groups = 1,
       if (s * groups * k <= 8192 && eff(s) > eff(best) + 0.03) best = s;
     splits = best;
   }
-  if (forced_splits > 0) splits = forced_splits > 16 ? 16 : forced_splits;
+  if (forced_splits > 0) splits = forced_splits > max_splits ? max_splits : forced_splits;
   if (splits > n_tiles) splits = n_tiles > 0 ? n_tiles : 1;
   p.n_splits = (int)splits;
   p.n_ctas = p.n_q_tiles * p.n_splits;

@@ -164,6 +164,7 @@ def lib() -> C.CDLL:
         "fps_mf_sgd_step": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, vp, i64, P(FpsMfParams), vp, vp]),
         "fps_mf_predict": (C.c_int, [P(FpsTableView), P(FpsTableView), vp, vp, i64, vp, vp]),
         "fps_mf_sample_negatives": (C.c_int, [P(FpsTableView), P(FpsNegSampler), vp, vp, vp, i64, u64, vp, vp, vp, vp]),
+        "fps_mf_sample_negatives_dtag": (C.c_int, [P(FpsTableView), P(FpsNegSampler), vp, vp, vp, i64, vp, vp, vp, vp, vp]),
         "fps_seen_ring_append": (C.c_int, [vp, vp, i32, i64, vp, vp, i64, vp]),
         "fps_mark_live_items": (C.c_int, [P(FpsTableView), i32, vp, vp, i64, vp, vp]),
         "fps_mf_tiles_scratch_bytes": (C.c_size_t, [i64]),
@@ -175,6 +176,7 @@ def lib() -> C.CDLL:
         "fps_pa_step_cost": (C.c_int, [P(FpsTableView), vp, vp, vp, vp, i64, P(FpsPaParams), vp, vp, vp, vp]),
         "fps_table_flush_delta": (C.c_int, [vp, vp]),
         "fps_topk_scratch_bytes": (C.c_size_t, [i64, i32, i64]),
+        "fps_topk_scratch_bytes_full": (C.c_size_t, [i64, i32, i64]),
         "fps_lemp_topk": (C.c_int, [vp, i32, i64, vp, i32, vp, vp, i64, i32, i32, i32, vp, C.c_size_t,
                                     vp, vp, vp, vp]),
         "fps_topk_packed_bytes": (C.c_size_t, [i64, i32]),

@@ -30,8 +30,12 @@ def _pad4(t):
     return torch.nn.functional.pad(t, (0, pad)).contiguous()
 
 
-def scratch_bytes(n_q: int, k: int, n_items: int) -> int:
-    return int(N.lib().fps_topk_scratch_bytes(n_q, k, n_items))
+def scratch_bytes(n_q: int, k: int, n_items: int, full: bool = False) -> int:
+    """Scratch of ``fps_lemp_topk`` / ``fps_topk_simt``: the minimum (<= 16 item splits per query tile), or
+    with ``full`` what lets a small query batch spread over all SMs (<= 64 splits; the kernel takes as many
+    splits as the buffer it is given allows)."""
+    L = N.lib()
+    return int((L.fps_topk_scratch_bytes_full if full else L.fps_topk_scratch_bytes)(n_q, k, n_items))
 
 
 def _run(fn_name: str, queries, items, k: int, item_len, item_ids, use_pruning: bool, scratch, stats):
@@ -43,7 +47,7 @@ def _run(fn_name: str, queries, items, k: int, item_len, item_ids, use_pruning: 
     n_q, n_items = q.shape[0], it.shape[0]
     need = scratch_bytes(n_q, k, n_items)
     if scratch is None:
-        scratch = torch.empty(need, device="cuda", dtype=torch.uint8)
+        scratch = torch.empty(scratch_bytes(n_q, k, n_items, full=True), device="cuda", dtype=torch.uint8)
     assert scratch.numel() >= need
     out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
     out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
@@ -210,7 +214,7 @@ def lemp_topk_table(queries, table_rows, dim: int, k: int, live_ids, *, scratch=
     import torch
     q = _pad4(queries.float())
     n_q, n_items = q.shape[0], table_rows.shape[0]
-    need = scratch_bytes(n_q, k, n_items)
+    need = scratch_bytes(n_q, k, n_items, full=True)
     if scratch is None or scratch.numel() < need:
         scratch = torch.empty(need, device="cuda", dtype=torch.uint8)
     out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)

@@ -260,6 +260,12 @@ int fps_mf_sample_negatives(const FpsTableView* users, const FpsNegSampler* samp
                             const int32_t* d_user_ids, const int32_t* d_item_ids, const float* d_ratings,
                             int64_t n, uint64_t step_tag, int32_t* d_out_users, int32_t* d_out_items,
                             float* d_out_ratings, void* stream);
+/* The same with the step tag read from device memory at launch time: for step sequences replayed from a
+ * CUDA graph, where a by-value tag would be frozen at capture (the caller bumps *d_step_tag on the stream). */
+int fps_mf_sample_negatives_dtag(const FpsTableView* users, const FpsNegSampler* sampler,
+                                 const int32_t* d_user_ids, const int32_t* d_item_ids, const float* d_ratings,
+                                 int64_t n, const uint64_t* d_step_tag, int32_t* d_out_users,
+                                 int32_t* d_out_items, float* d_out_ratings, void* stream);
 
 /* Replicated table with deferred pushes: add the locally accumulated deltas to every other replica
  * (red.add.v4 per peer, all-zero 16-byte chunks are skipped) and clear them.  Run it on the stream of
@@ -310,6 +316,10 @@ int fps_pa_step_cost(const FpsTableView* weights, const int64_t* d_indptr, const
  * use_pruning: bit 0 = the LENGTH bound; bit 1 = items whose d_item_ids entry is negative are skipped
  * (scoring a worker-resident table in place, where not every slot is a live item).                 */
 size_t fps_topk_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items);
+/* With a buffer of this size (>= the one above) fps_lemp_topk / fps_topk_simt cut the items into up to 64
+ * splits per query tile instead of 16, so that a small query batch still occupies the SMs; with anything in
+ * between they take as many splits as fit.                                                              */
+size_t fps_topk_scratch_bytes_full(int64_t n_q, int32_t k, int64_t n_items);
 int fps_lemp_topk(const float* d_queries, int32_t q_stride, int64_t n_q,
                   const float* d_items, int32_t item_stride, const float* d_item_len,
                   const int32_t* d_item_ids, int64_t n_items, int32_t dim, int32_t k,

@@ -211,3 +211,27 @@ def test_locked_read_modify_write_loses_no_update(lazy):
 
     with pytest.raises(ValueError):
         ShardedTable(8, 4, n_shards=1).locked_axpby(ids[:4] % 8, 1.0, ones[:4, :4])        # no aux column for the lock
+
+
+@pytest.mark.gpu
+def test_learner_generator_step_replayed_from_a_cuda_graph():
+    """cuda_graph=True: the step sequence is captured after two eager steps of a batch size and replayed; the
+    sampler's step tag lives on the device, so replays keep drawing fresh negatives and the job learns as the
+    eager one does."""
+    import random
+    import torch
+    from fps_b200.models.mf import Rating
+    from fps_b200.models.mf.device_topk import ps_online_learner_and_generator_device
+    rnd = random.Random(2)
+    stream = [Rating(u := rnd.randrange(40), (u % 4) * 10 + rnd.randrange(10), 1.0, t) for t in range(2000)]
+    kw = dict(n_users=40, n_items=40, batch_size=50, num_factors=8, range_min=-0.1, range_max=0.1, learning_rate=0.1,
+              negative_sample_rate=3, user_memory=4, K=10, worker_k=10, pull_limit=500)
+    out_g, lg_g = ps_online_learner_and_generator_device(stream, cuda_graph=True, **kw)
+    out_e, lg_e = ps_online_learner_and_generator_device(stream, cuda_graph=False, **kw)
+    assert 50 in lg_g._graphs and not lg_e._graphs                 # 40 batches of 50: 2 eager, 38 replayed
+    assert lg_g.batches == lg_e.batches == 40
+    assert lg_g.stats()["records"] == lg_e.stats()["records"]     # same number of SGD records (negatives included)
+    assert len(out_g) == len(out_e) == len(stream)
+    hg, he = out_g.hit_rate(1000), out_e.hit_rate(1000)
+    assert hg > 0.3 and abs(hg - he) < 0.12, (hg, he)
+    assert int(lg_g._tag_dev.item()) == 40                          # the tag advanced on every replay
