@@ -484,7 +484,7 @@ constexpr uint32_t W_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(W_
 
 __global__ void __launch_bounds__(256)
 k_pack_items_wide(const float* __restrict__ items, int stride, long long n_items, int dim, int kblks,
-                  float* __restrict__ packed) {
+                  float* __restrict__ packed, const int* __restrict__ live_ids) {
   const long long tile = blockIdx.x;
   const long long i0 = tile * W_N;
   float* out = packed + tile * 2 * (long long)kblks * W_SLAB;
@@ -502,6 +502,12 @@ k_pack_items_wide(const float* __restrict__ items, int stride, long long n_items
         if (col + 1 < dim) x.y = p[1];
         if (col + 2 < dim) x.z = p[2];
       }
+    }
+    // live mask as arithmetic: column `dim` of a dead slot is -1e30, of a live one 0; the caller gives every
+    // query a 1 in that column, so a dead slot scores about -1e30 and a live one exactly its inner product
+    if (live_ids != nullptr && i0 + r < n_items && dim >= col && dim < col + 4 && live_ids[i0 + r] < 0) {
+      const float dead = -1e30f;
+      if (dim == col) x.x = dead; else if (dim == col + 1) x.y = dead; else if (dim == col + 2) x.z = dead; else x.w = dead;
     }
     float4 h, l;
     h.x = to_tf32(x.x); h.y = to_tf32(x.y); h.z = to_tf32(x.z); h.w = to_tf32(x.w);
@@ -984,7 +990,19 @@ int fps_topk_pack_items_wide(const float* d_items, int32_t item_stride, int64_t 
               "fps_topk_pack_items_wide: bad arguments (rank must be <= 128, stride a multiple of 4)");
   const int kblks = (dim + TK_KB - 1) / TK_KB;
   const long long n_tiles = (n_items + W_N - 1) / W_N;
-  k_pack_items_wide<<<(unsigned)n_tiles, 256, 0, (cudaStream_t)stream>>>(d_items, item_stride, n_items, dim, kblks, (float*)d_packed);
+  k_pack_items_wide<<<(unsigned)n_tiles, 256, 0, (cudaStream_t)stream>>>(d_items, item_stride, n_items, dim, kblks, (float*)d_packed, nullptr);
+  FPS_LAUNCH_CHECK();
+  return 0;
+}
+
+int fps_topk_pack_items_wide_live(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim,
+                                  const int32_t* d_live_ids, void* d_packed, void* stream) {
+  FPS_REQUIRE(d_items && d_packed && d_live_ids && n_items > 0 && dim > 0 && dim < 128 && item_stride % 4 == 0, FPS_E_INVALID,
+              "fps_topk_pack_items_wide_live: bad arguments (rank must be < 128: one more column carries the mask)");
+  const int kblks = (dim + 1 + TK_KB - 1) / TK_KB;
+  const long long n_tiles = (n_items + W_N - 1) / W_N;
+  k_pack_items_wide<<<(unsigned)n_tiles, 256, 0, (cudaStream_t)stream>>>(d_items, item_stride, n_items, dim, kblks, (float*)d_packed,
+                                                                         d_live_ids);
   FPS_LAUNCH_CHECK();
   return 0;
 }

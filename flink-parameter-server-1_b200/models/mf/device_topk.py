@@ -18,6 +18,7 @@ Learning re-uses the fused MF kernel with the tables swapped: the pulled row is 
 from __future__ import annotations
 
 import ctypes as C
+import os
 from collections import deque
 from typing import Dict, Iterable, List, Optional, Tuple
 
@@ -26,7 +27,7 @@ import numpy as np
 from ...ops import _native as N
 from ...ops import philox
 from ...ops.table import ShardedTable, new_flow, read_flow
-from ...ops.topk import (PackedItems, lemp_topk, lemp_topk_filtered, lemp_topk_packed, lemp_topk_table, sort_items_by_length,
+from ...ops.topk import (InPlaceScorer, PackedItems, lemp_topk, lemp_topk_filtered, lemp_topk_packed, lemp_topk_table, sort_items_by_length,
                          topk_merge)
 from ...utils.observability import nvtx_range
 
@@ -300,6 +301,7 @@ class DeviceLearnerGenerator:
         self.local = _LocalItems()
         self._since_refresh = 1 << 30
         self._scratch = None
+        self._scorer = None
         self._skip = torch.tensor(N.SKIP_ID, device="cuda", dtype=torch.int32)
         self.batches = 0
 
@@ -309,6 +311,14 @@ class DeviceLearnerGenerator:
         n_q = q.shape[0]
         if self.dense:
             rows = self.items.rows[self._shard]
+            # the TMA + tcgen05 pipeline over a per-step packed image pays from ~1K queries on (measured, rank 10,
+            # 19K items, ms per step packed / in-kernel staging: 64 queries 0.64 / 0.35, 256: 0.68 / 0.50,
+            # 2048: 0.93 / 1.06, 8192: 1.88 / 3.08); FPS_TOPK_INPLACE_PACKED=0 / 1 forces one of them
+            force = os.environ.get("FPS_TOPK_INPLACE_PACKED")
+            if self.dim < 128 and (force == "1" or (force != "0" and n_q >= 1024)):
+                if self._scorer is None:
+                    self._scorer = InPlaceScorer(rows.shape[0], self.dim)
+                return self._scorer.topk(q, rows, self.worker_k, self.live_ids)
             ls, li, self._scratch = lemp_topk_table(q, rows, self.dim, self.worker_k, self.live_ids, scratch=self._scratch)
             return ls, li
         # large catalogue: length-sorted packed snapshot, refreshed every few batches

@@ -187,6 +187,7 @@ def lib() -> C.CDLL:
         "fps_topk_wide_packed_bytes": (C.c_size_t, [i64, i32]),
         "fps_topk_wide_scratch_bytes": (C.c_size_t, [i64, i32, i64]),
         "fps_topk_pack_items_wide": (C.c_int, [vp, i32, i64, i32, vp, vp]),
+        "fps_topk_pack_items_wide_live": (C.c_int, [vp, i32, i64, i32, vp, vp, vp]),
         "fps_lemp_topk_wide": (C.c_int, [vp, i32, i64, vp, vp, vp, i64, i32, i32, i32, vp, C.c_size_t,
                                          vp, vp, vp, vp]),
         "fps_lemp_topk_static": (C.c_int, [vp, i32, i64, vp, i32, vp, vp, i64, i32, i32, i32, vp, vp, vp, vp]),

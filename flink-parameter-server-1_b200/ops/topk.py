@@ -205,6 +205,47 @@ def topk_merge(part_scores, part_ids, k_out: int, seen=None):
     return out_s, out_i
 
 
+class InPlaceScorer:
+    """Top-``k`` against a worker-resident table scored in place through the TMA + tcgen05 pipeline
+    (``fps_lemp_topk_wide``): every call re-packs the table (one pass over it) into a persistent image whose
+    extra column carries the live mask (0 for a live slot, -1e30 for a dead one; the queries get a 1 there), so
+    the scoring kernel needs no mask logic and live slots score exactly their inner product.  Rank < 128.
+    Replaces the in-kernel-staging kernel on this path: 256 queries x 19K items, rank 10: 0.2 ms -> see
+    ``profiles/README.md`` R2.5."""
+
+    def __init__(self, n_items: int, dim: int):
+        import torch
+        if dim >= 128:
+            raise ValueError("InPlaceScorer needs rank < 128 (one more column carries the live mask)")
+        self.n_items, self.dim = int(n_items), int(dim)
+        L = N.lib()
+        self.packed = torch.empty(int(L.fps_topk_wide_packed_bytes(self.n_items, self.dim + 1)), device="cuda",
+                                  dtype=torch.uint8)
+        self.scratch = None
+
+    def topk(self, queries, table_rows, k: int, live_ids):
+        import torch
+        L = N.lib()
+        n_q = queries.shape[0]
+        q = torch.zeros((n_q, ((self.dim + 1 + 3) // 4) * 4), device="cuda", dtype=torch.float32)
+        q[:, : self.dim] = queries[:, : self.dim]
+        q[:, self.dim] = 1.0
+        N.check(L.fps_topk_pack_items_wide_live(N.ptr(table_rows), table_rows.shape[1], self.n_items, self.dim,
+                                                N.ptr(live_ids), N.ptr(self.packed), N.current_stream()),
+                "fps_topk_pack_items_wide_live")
+        need = int(L.fps_topk_wide_scratch_bytes(n_q, k, self.n_items))
+        if self.scratch is None or self.scratch.numel() < need:
+            self.scratch = torch.empty(need, device="cuda", dtype=torch.uint8)
+        out_s = torch.empty((n_q, k), device="cuda", dtype=torch.float32)
+        out_i = torch.empty((n_q, k), device="cuda", dtype=torch.int32)
+        with nvtx_range("fps.topk.in_place"):
+            N.check(L.fps_lemp_topk_wide(N.ptr(q), q.shape[1], n_q, N.ptr(self.packed), None, N.ptr(live_ids),
+                                         self.n_items, self.dim + 1, k, 0, N.ptr(self.scratch), self.scratch.numel(),
+                                         N.ptr(out_s), N.ptr(out_i), None, N.current_stream()), "fps_lemp_topk_wide (in place)")
+        dead = out_i < 0
+        return torch.where(dead, torch.full_like(out_s, -float("inf")), out_s), torch.where(dead, torch.full_like(out_i, -1), out_i)
+
+
 def lemp_topk_table(queries, table_rows, dim: int, k: int, live_ids, *, scratch=None):
     """Top-``k`` of every query against a worker-resident table scored *in place*: ``table_rows`` is the
     shard's ``[rows, stride]`` tensor, ``live_ids[slot]`` the id of the item living in that slot or a

@@ -348,6 +348,12 @@ size_t fps_topk_wide_packed_bytes(int64_t n_items, int32_t dim);
 size_t fps_topk_wide_scratch_bytes(int64_t n_q, int32_t k, int64_t n_items);
 int fps_topk_pack_items_wide(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim,
                              void* d_packed, void* stream);
+/* The same for a table scored in place: d_live_ids[slot] < 0 marks a slot that is not a candidate.  The packed
+ * image gets one more column (rank + 1 <= 128: size it with fps_topk_wide_packed_bytes(n_items, dim + 1)) that
+ * holds 0 for a live slot and -1e30 for a dead one; run fps_lemp_topk_wide with dim + 1 and queries whose column
+ * `dim` is 1: live slots score exactly their inner product, dead ones about -1e30 (ids from d_live_ids: < 0).  */
+int fps_topk_pack_items_wide_live(const float* d_items, int32_t item_stride, int64_t n_items, int32_t dim,
+                                  const int32_t* d_live_ids, void* d_packed, void* stream);
 int fps_lemp_topk_wide(const float* d_queries, int32_t q_stride, int64_t n_q, const void* d_packed,
                        const float* d_item_len, const int32_t* d_item_ids, int64_t n_items,
                        int32_t dim, int32_t k, int32_t use_pruning, void* d_scratch,

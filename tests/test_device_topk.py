@@ -256,3 +256,32 @@ def test_filtered_retrieval_is_exact_and_counts_like_the_host(strategy):
         lemp_top_k((float(np.linalg.norm(qa)), qa), desc, model, k, bucket, strat, stats=host)
     assert abs(host.get("scored", 0) - scored) <= 0.03 * host["scored"] + 64, (host, stats.tolist())
     assert abs(host.get("pruned", 0) - pruned) <= 0.03 * max(host.get("pruned", 0), 1) + 64, (host, stats.tolist())
+
+
+def test_in_place_scorer_through_the_packed_pipeline_matches_the_masked_kernel():
+    """InPlaceScorer (pack with the live mask as an extra column + fps_lemp_topk_wide) against brute force over
+    the live slots, including a query batch that spans query tiles, fewer live items than k, and rank 127."""
+    from fps_b200.ops.topk import InPlaceScorer, lemp_topk_table
+    g = torch.Generator(device="cuda").manual_seed(21)
+    for n_rows, dim, n_q, k, p_live in [(5000, 10, 300, 75, 0.6), (700, 127, 40, 20, 0.5), (300, 16, 10, 50, 0.1)]:
+        stride = ((dim + 3) // 4) * 4
+        rows = torch.randn(n_rows, stride, device="cuda", generator=g)
+        live = torch.rand(n_rows, device="cuda", generator=g) < p_live
+        live_ids = torch.where(live, torch.arange(n_rows, device="cuda", dtype=torch.int32) + 1000, torch.full((n_rows,), -1, device="cuda", dtype=torch.int32))
+        q = torch.randn(n_q, dim, device="cuda", generator=g)
+        sc = InPlaceScorer(n_rows, dim)
+        s, i = sc.topk(q, rows, k, live_ids)
+        full = q.double() @ rows[:, :dim].double().T
+        full[:, ~live] = -float("inf")
+        n_live = int(live.sum())
+        kk = min(k, n_live)
+        ref_v, ref_i = full.topk(kk, dim=1)
+        torch.testing.assert_close(s[:, :kk].double(), ref_v, rtol=2e-5, atol=2e-5)
+        assert torch.equal(i[:, :kk].sort(dim=1).values, (ref_i + 1000).int().sort(dim=1).values) or \
+            (i[:, :kk].sort(dim=1).values == (ref_i + 1000).int().sort(dim=1).values).float().mean() > 0.99
+        if kk < k:
+            assert torch.all(i[:, kk:] == -1) and torch.all(torch.isinf(s[:, kk:]))
+        # second call after the table changed: the image is re-packed
+        rows[:, :dim] *= 0.5
+        s2, _ = sc.topk(q, rows, k, live_ids)
+        torch.testing.assert_close(s2[:, :kk].double(), ref_v * 0.5, rtol=2e-5, atol=2e-5)
