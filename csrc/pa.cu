@@ -78,7 +78,10 @@ __device__ __forceinline__ void pa_flush(PaCounters c, FpsFlow* flow) {
 }
 
 // ---- N3 / N5 binary: one warp per example -----------------------------------------------------
-__global__ void __launch_bounds__(PA_THREADS)
+// measured on config 3 (limit 10 000 / no limit, ms): prefetch depth 4 at 106 registers 0.935 / 0.168, depth 3 at 80
+// 0.913 / 0.156, depth 3 at 64 0.920 / 0.153, depth 2 at 64 1.004 / 0.170; the plain loop it replaced 1.43 / 0.160
+constexpr int PB_PF = 3;
+__global__ void __launch_bounds__(PA_THREADS, 4)
 k_pa_binary(const __grid_constant__ FpsTableView t, const long long* __restrict__ indptr,
             const int* __restrict__ indices, const float* __restrict__ values,
             const int* __restrict__ labels, long long n, const FpsPaParams p, int* __restrict__ pred,
@@ -93,44 +96,107 @@ k_pa_binary(const __grid_constant__ FpsTableView t, const long long* __restrict_
   const int WPB = warps_active;
   const int credits = warps_active * lanes_active;
   if (p.pull_limit > 0) flow_acquire(flow, credits, p.pull_limit);
-  for (long long e0 = (long long)blockIdx.x * WPB; e0 < n; e0 += (long long)gridDim.x * WPB) {
-    const long long e = e0 + warp;
-    if (e < n && warp < WPB) {
-      const long long b = indptr[e], end = indptr[e + 1];
-      float m = 0.f, n2 = 0.f;
-      for (long long k = b + lane; k < end && lane < lanes_active; k += lanes_active) {
-        const long long id = indices[k];
-        const float x = values[k];
-        const RowRef r = locate(t, id);
-        if (!in_table(t, id, r)) { ++c.bad; continue; }
-        m = fmaf(x, pull_scalar(t, id, r), m);
-        n2 = fmaf(x, x, n2);
-        ++c.pulls;
-        if (r.owner != p.local_shard) ++c.remote;
-      }
+  // Software pipeline over the warp's examples.  What a credit pays for is the weight load; everything that is
+  // not a pull - row pointers, feature ids, values, the label - is fetched ahead: the row pointers two examples
+  // ahead, ids / values / label one example ahead, so that a warp waits for weights and for nothing else
+  // (the first version waited for indptr, then ids, then weights, three times per 75-feature example: a
+  // credit was held ~1.45 us per pull, now about the weight latency).  PB_PF chunks of one feature per active
+  // lane are prefetched into registers; a longer example takes its tail through a plain loop.
+  const bool puller = warp < WPB;
+  const long long estride = (long long)gridDim.x * WPB;
+  long long e = (long long)blockIdx.x * WPB + warp;
+  const bool limited = p.pull_limit > 0;
+  long long nb = 0, nend = 0;                              // bounds of the NEXT example (prefetched)
+  int nid[PB_PF];
+  float nx[PB_PF];
+  int nlabel = 1;
+  auto fetch_features = [&](long long ee, long long bb, long long eend) {
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        m += __shfl_xor_sync(0xffffffffu, m, o);
-        n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+    for (int q = 0; q < PB_PF; ++q) {
+      const long long k = bb + lane + (long long)q * lanes_active;
+      const bool have = lane < lanes_active && k < eend;
+      nid[q] = have ? indices[k] : -1;
+      nx[q] = have ? values[k] : 0.f;
+    }
+    nlabel = p.predict_only ? 1 : labels[ee];
+  };
+  if (puller && e < n) {
+    nb = indptr[e];
+    nend = indptr[e + 1];
+    fetch_features(e, nb, nend);
+  }
+  long long b2 = 0, end2 = 0;                              // bounds of the example after the next
+  if (puller && e + estride < n) { b2 = indptr[e + estride]; end2 = indptr[e + estride + 1]; }
+  for (; puller && e < n; e += estride) {
+    // ---- the current example moves out of the prefetch registers
+    const long long b = nb, end = nend;
+    int id[PB_PF];
+    float x[PB_PF];
+#pragma unroll
+    for (int q = 0; q < PB_PF; ++q) { id[q] = nid[q]; x[q] = nx[q]; }
+    const int label = nlabel;
+    // ---- prefetch: features of the next example, bounds of the one after it
+    nb = b2;
+    nend = end2;
+    if (e + estride < n) fetch_features(e + estride, nb, nend);
+    if (e + 2 * estride < n) { b2 = indptr[e + 2 * estride]; end2 = indptr[e + 2 * estride + 1]; }
+    // ---- pull + margin
+    float m = 0.f, n2 = 0.f;
+#pragma unroll
+    for (int q = 0; q < PB_PF; ++q) {
+      if (id[q] >= 0) {
+        const RowRef r = locate(t, id[q]);
+        if (!in_table(t, id[q], r)) { ++c.bad; id[q] = -1; }
+        else {
+          m = fmaf(x[q], pull_scalar(t, id[q], r), m);
+          n2 = fmaf(x[q], x[q], n2);
+          ++c.pulls;
+          if (r.owner != p.local_shard) ++c.remote;
+        }
       }
-      if (lane == 0) {
-        ++c.records;
-        if (pred != nullptr) pred[e] = m > 0.f ? 1 : -1;
-      }
-      if (!p.predict_only) {
-        const float y = labels[e] > 0 ? 1.f : -1.f;
-        const float loss = fmaxf(0.f, 1.f - y * m);
-        const float mult = tau_of(p.variant, p.C, loss, n2) * y;
-        if (lane == 0) c.loss += loss;
-        if (mult != 0.f) {
-          for (long long k = b + lane; k < end; k += 32) {
-            const long long id = indices[k];
-            const RowRef r = locate(t, id);
-            if (!in_table(t, id, r)) continue;
-            if (t.lazy) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
-            push_add1(t, r.owner, r.slot * t.stride, mult * values[k]);
-            ++c.pushes;
-          }
+      // under a limit a lane has ONE weight load outstanding: the next chunk's load may not issue before this one is used
+      if (limited) asm volatile("" ::"f"(m) : "memory");
+    }
+    for (long long k = b + lane + (long long)PB_PF * lanes_active; k < end && lane < lanes_active; k += lanes_active) {
+      const long long fid = indices[k];
+      const float fx = values[k];
+      const RowRef r = locate(t, fid);
+      if (!in_table(t, fid, r)) { ++c.bad; continue; }
+      m = fmaf(fx, pull_scalar(t, fid, r), m);
+      n2 = fmaf(fx, fx, n2);
+      ++c.pulls;
+      if (r.owner != p.local_shard) ++c.remote;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      m += __shfl_xor_sync(0xffffffffu, m, o);
+      n2 += __shfl_xor_sync(0xffffffffu, n2, o);
+    }
+    if (lane == 0) {
+      ++c.records;
+      if (pred != nullptr) pred[e] = m > 0.f ? 1 : -1;
+    }
+    if (!p.predict_only) {
+      const float y = label > 0 ? 1.f : -1.f;
+      const float loss = fmaxf(0.f, 1.f - y * m);
+      const float mult = tau_of(p.variant, p.C, loss, n2) * y;
+      if (lane == 0) c.loss += loss;
+      if (mult != 0.f) {
+#pragma unroll
+        for (int q = 0; q < PB_PF; ++q) {
+          if (id[q] < 0) continue;
+          const RowRef r = locate(t, id[q]);
+          if (t.lazy) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
+          push_add1(t, r.owner, r.slot * t.stride, mult * x[q]);
+          ++c.pushes;
+        }
+        for (long long k = b + lane + (long long)PB_PF * lanes_active; k < end && lane < lanes_active; k += lanes_active) {
+          const long long fid = indices[k];
+          const RowRef r = locate(t, fid);
+          if (!in_table(t, fid, r)) continue;
+          if (t.lazy) touch_state(t.state[r.owner], r.slot, FPS_ROW_PUSHED);
+          push_add1(t, r.owner, r.slot * t.stride, mult * values[k]);
+          ++c.pushes;
         }
       }
     }
