@@ -151,6 +151,19 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t leader, uint32_t d_tmem, u
       ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(TK_IDESC), "r"(ACC ? 1u : 0u), "r"(leader)
       : "memory");
 }
+// tcgen05.ld of 32 columns without the wait (the caller waits once for a batch of loads)
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, float (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]),
+        "=f"(v[8]), "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15]),
+        "=f"(v[16]), "=f"(v[17]), "=f"(v[18]), "=f"(v[19]), "=f"(v[20]), "=f"(v[21]), "=f"(v[22]), "=f"(v[23]),
+        "=f"(v[24]), "=f"(v[25]), "=f"(v[26]), "=f"(v[27]), "=f"(v[28]), "=f"(v[29]), "=f"(v[30]), "=f"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
 template <bool ACC>
 __device__ __forceinline__ void umma_tf32_ts_i(uint32_t leader, uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc) {
   asm volatile(
@@ -474,7 +487,7 @@ k_lemp_topk_packed(const float* __restrict__ queries, int q_stride, long long n_
 // MMA warp accumulates over the tile's K-block stages - the K loop of a GEMM - before it commits the
 // accumulator.  TMEM: two 128-column accumulators + the 2 x 128 query columns.
 // =================================================================================================
-constexpr int W_N = 128;              // items per tile
+constexpr int W_N = 128;              // items per tile = UMMA N (a multiple of 128)
 constexpr int W_STAGES = 6;           // shared-memory stages of one K block each (32 KB)
 constexpr int W_ACC = 2;              // TMEM accumulators of W_N columns
 constexpr int W_CAP = 512;            // candidate slots per (CTA, query): a tile may add W_N
@@ -728,24 +741,32 @@ k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
         tc_fence_after();
         const long long i0 = tile_of(j) * W_N;
         const int i_valid = (int)min((long long)W_N, n_items - i0);
-        float v[4][32];
         const uint32_t lane_addr = tmem_base + ((uint32_t)(sub * 32) << 16) + (uint32_t)b * W_N;
-#pragma unroll
-        for (int h = 0; h < 4; ++h) tmem_ld32(lane_addr + 32 * h, v[h]);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sh.acc_empty[b]);       // the MMAs of the tile after next may overwrite it now
         if (q_ok) theta = fmaxf(theta, key2f(theta_key));
-        if (i_valid < W_N) {                                 // ragged last tile
-#pragma unroll
-          for (int h = 0; h < 4; ++h)
-#pragma unroll
-            for (int jj = 0; jj < 32; ++jj)
-              if (32 * h + jj >= i_valid) v[h][jj] = -INFINITY;
-        }
         const int before = cnt;
+        // the tile's W_N columns in halves of 128 (register budget); the four loads of a half are issued
+        // back to back and waited for once; the accumulator is released after the last half's loads
+#pragma unroll 1
+        for (int half = 0; half < W_N / 128; ++half) {
+          float v[4][32];
 #pragma unroll
-        for (int h = 0; h < 4; ++h) select32(v[h], theta, (int)i0 + 32 * h, rs, ri, cnt);
+          for (int h = 0; h < 4; ++h) tmem_ld32_nowait(lane_addr + 128 * half + 32 * h, v[h]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          if (half == W_N / 128 - 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sh.acc_empty[b]);       // the next tile's MMAs may overwrite it now
+          }
+          if (i_valid < W_N) {                                 // ragged last tile
+#pragma unroll
+            for (int h = 0; h < 4; ++h)
+#pragma unroll
+              for (int jj = 0; jj < 32; ++jj)
+                if (128 * half + 32 * h + jj >= i_valid) v[h][jj] = -INFINITY;
+          }
+#pragma unroll
+          for (int h = 0; h < 4; ++h) select32(v[h], theta, (int)i0 + 128 * half + 32 * h, rs, ri, cnt);
+        }
         accepted += (unsigned)(cnt - before);
         if (__any_sync(0xffffffffu, cnt > W_CAP - W_N)) {
           __syncwarp();

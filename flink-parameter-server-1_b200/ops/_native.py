@@ -193,6 +193,7 @@ def lib() -> C.CDLL:
         "fps_lemp_topk_static": (C.c_int, [vp, i32, i64, vp, i32, vp, vp, i64, i32, i32, i32, vp, vp, vp, vp]),
         "fps_topk_simt": (C.c_int, [vp, i32, i64, vp, i32, vp, i64, i32, i32, vp, C.c_size_t, vp, vp, vp]),
         "fps_topk_merge": (C.c_int, [vp, vp, i32, i64, i32, i32, vp, i32, vp, vp, vp]),
+        "fps_umma_probe": (C.c_int, [i32, i32, i32, vp, vp]),
         "fps_lemp_keep_mask": (C.c_int, [vp, i32, i64, vp, i32, vp, i64, i32, vp, i32, i32, i32, C.c_float, vp, vp]),
         "fps_lemp_topk_filtered": (C.c_int, [vp, i32, i64, vp, i32, vp, vp, i64, i32, i32, i32, i32, i32, C.c_float,
                                              vp, vp, vp, vp, vp, vp]),

@@ -398,6 +398,11 @@ int fps_lemp_topk_filtered(const float* d_queries, int32_t q_stride, int64_t n_q
                            int32_t n_focus, float switch_threshold, float* d_part_scores,
                            int32_t* d_part_ids, float* d_out_scores, int32_t* d_out_ids, uint64_t* d_stats,
                            void* stream);
+/* Microbenchmark: cycles per tcgen05.mma kind::tf32 instruction (M128, K8) for a long chain issued by one
+ * thread per CTA on n_ctas CTAs.  mode 0 / 1: A from TMEM, one / two accumulators (N 128); 2 / 3: A from
+ * shared memory, one / two accumulators; 4: A from TMEM, N 256; 5: A from TMEM, four accumulators of N 64.
+ * d_cycles_per_mma: n_ctas floats.  (scripts/umma_probe.py, profiles/r2_topk/README.md)                 */
+int fps_umma_probe(int32_t mode, int32_t n_mma, int32_t n_ctas, float* d_cycles_per_mma, void* stream);
 /* Merge n_parts partial top-k lists per query (X8: CollectTopKFromEachWorker.scala:40-48) with an
  * optional per-query seen-set filter (d_seen: [n_q, seen_stride] item ids, -1 padded).            */
 int fps_topk_merge(const float* d_part_scores, const int32_t* d_part_ids, int32_t n_parts,
