@@ -491,7 +491,9 @@ constexpr int W_N = 128;              // items per tile = UMMA N (a multiple of 
 constexpr int W_STAGES = 6;           // shared-memory stages of one K block each (32 KB)
 constexpr int W_ACC = 2;              // TMEM accumulators of W_N columns
 constexpr int W_CAP = 512;            // candidate slots per (CTA, query): a tile may add W_N
-constexpr int W_THREADS = 6 * 32;     // 4 selection warps + producer + MMA issuer
+constexpr int W_ISSUERS = 2;           // MMA-issuing warps: ONE issuing thread cannot feed the tensor core (106 cycles per
+                                      // M128 x N128 x K8 tf32 instruction against 64 with two, scripts/umma_probe.py)
+constexpr int W_THREADS = (5 + W_ISSUERS) * 32;     // 4 selection warps + producer + MMA issuers
 constexpr int W_SLAB = W_N * TK_KB;   // floats of one [128 x 128 B] image
 constexpr uint32_t W_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(W_N >> 3) << 17) | ((uint32_t)(TK_M >> 4) << 24);
 
@@ -668,8 +670,11 @@ k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
         __threadfence_block();
         sh.issued_final = issued;
       }
-    } else if (warp == 5) {
-      // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+    } else if (warp >= 5) {
+      // ===================== MMA issuers (converged warps, one elected lane each issues) ===============
+      // Issuer w takes the tiles whose accumulator is w (tile ordinals alternate), so both have instructions
+      // in flight at the same time; each commits its own stages and its own accumulator.
+      const int issuer = warp - 5;
       const uint32_t leader = elect_one();
       const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
       const uint32_t a_hi = tb + TP_A_COL, a_lo = tb + TP_A_COL + 128;
@@ -677,6 +682,7 @@ k_lemp_topk_wide(const float* __restrict__ queries, int q_stride, long long n_q,
       for (int j = 0; j < my_tiles; ++j) {
         const long long a = a_base + j;
         const int b = (int)(a % W_ACC);
+        if ((int)(a % W_ISSUERS) != issuer) { g += kblks; continue; }
         bool have = true;
         for (int kb = 0; kb < kblks; ++kb, ++g) {
           const int s = (int)(g % W_STAGES);

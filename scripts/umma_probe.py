@@ -4,10 +4,10 @@ import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from fps_b200.ops import _native as N
 names = {0: "TS N128, 1 accumulator", 1: "TS N128, 2 accumulators", 2: "SS N128, 1 accumulator", 3: "SS N128, 2 accumulators",
-         4: "TS N256, 1 accumulator", 5: "TS N64, 4 accumulators"}
+         4: "TS N256, 1 accumulator", 5: "TS N64, 4 accumulators", 6: "TS N128, 2 issuing warps"}
 sms = torch.cuda.get_device_properties(0).multi_processor_count
 for ctas in (1, sms):
-    for mode in range(6):
+    for mode in range(7):
         out = torch.zeros(ctas, device="cuda")
         for _ in range(2):
             N.check(N.lib().fps_umma_probe(mode, 20000, ctas, N.ptr(out), N.current_stream()), "probe")
