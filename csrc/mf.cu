@@ -38,6 +38,37 @@ k_mf_sgd(const __grid_constant__ FpsTableView items, const __grid_constant__ Fps
   c.flush(flow);
 }
 
+// The same step for SMALL pull limits, where a credit is a scarce thing: the ids and the rating of a sub-warp's
+// next record are fetched while the current record's rows are in flight, so an allowance is held for about one
+// row latency per record instead of two dependent latencies (ids, then rows).  Not used without a limit or
+// with a generous one: there thousands of resident warps hide the id loads, and the extra registers cost
+// occupancy (the default build runs at 32 registers, 8 CTAs per SM).
+template <int LANES, int VPL, bool LAZY>
+__global__ void __launch_bounds__(MF_THREADS)
+k_mf_sgd_pf(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
+            const int* __restrict__ uid, const int* __restrict__ iid, const float* __restrict__ rating,
+            long long n, const FpsMfParams p, int chunk, int cta_credits, FpsFlow* flow) {
+  constexpr int GPB = MF_THREADS / LANES;
+  const int grp = threadIdx.x / LANES;
+  MfCounters c;
+  c.clear();
+  if (p.pull_limit > 0) flow_acquire(flow, cta_credits, p.pull_limit);
+  for (long long base = (long long)blockIdx.x * chunk; base < n; base += (long long)gridDim.x * chunk) {
+    const int cnt = (int)min((long long)chunk, n - base);
+    MfIds nxt = mf_fetch_ids(uid, iid, rating, grp < cnt ? base + grp : -1);
+    for (int k0 = 0; k0 < cnt; k0 += GPB) {              // warp-uniform trip count (shuffles inside)
+      const MfIds cur = nxt;
+      const int kn = k0 + GPB + grp;
+      nxt = mf_fetch_ids(uid, iid, rating, kn < cnt ? base + kn : -1);
+      MfRec<VPL> rec;
+      mf_load_ids<LANES, VPL, LAZY>(rec, items, users, cur, p.local_shard, c);
+      mf_update<LANES, VPL, LAZY, false>(rec, items, p, c);
+    }
+  }
+  if (p.pull_limit > 0) flow_release(flow, cta_credits);
+  c.flush(flow);
+}
+
 template <int LANES, int VPL, bool LAZY>
 __global__ void __launch_bounds__(MF_THREADS)
 k_mf_predict(const __grid_constant__ FpsTableView items, const __grid_constant__ FpsTableView users,
@@ -220,12 +251,16 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
   const long long cap = (long long)fps_num_sms() * bps;
   if (blocks > cap) blocks = cap;
   const int unroll = params->unroll;   // 0 = default
+  // small limits: the id-prefetching build (see k_mf_sgd_pf); FPS_MF_PREFETCH=0 / 1 forces the choice
+  static const int pf_env = []() { const char* e = getenv("FPS_MF_PREFETCH"); return e ? atoi(e) : -1; }();
+  const bool use_pf = !repl && (unroll == 0) && params->pull_limit > 0 &&
+                      (pf_env == 1 || (pf_env != 0 && params->pull_limit <= 4096));   // measured: 1600: 3.51 -> 3.15 ms, 16384: 1.374 -> 1.416 ms
   int cta_credits = 0;
   if (params->pull_limit > 0) {
     // one pass of a CTA has (sub-warps x ratings per sub-warp) pulls outstanding, or the whole chunk if
     // that is smaller; the grid holds as many CTAs as allowances fit the limit
     const Shape sh = shape_for(items->stride);
-    const int per_pass = (MF_THREADS / sh.lanes) * (unroll == 2 || unroll == 4 ? unroll : (sh.vpl == 2 ? 2 : 1));
+    const int per_pass = (MF_THREADS / sh.lanes) * (use_pf ? 1 : (unroll == 2 || unroll == 4 ? unroll : (sh.vpl == 2 ? 2 : 1)));
     cta_credits = per_pass < chunk ? per_pass : chunk;
     // at most SMs x 8 CTAs (the tightest launch bound) are resident and hold credits at a time; only if
     // even those do not fit is the grid cut down to a persistent one
@@ -239,7 +274,8 @@ int fps_mf_sgd_step(const FpsTableView* items, const FpsTableView* users, const 
   // 2-ratings-per-sub-warp build at 56 registers - thread-level parallelism hides the row-load
   // latency better than per-warp ILP here.  `unroll` = 2 / 4 select the ILP builds explicitly.
 #define FN(L, V, Z)                                                                                   \
-  if (repl) k_mf_sgd<L, V, false, 1, 1, true> MF_ARGS;                                                \
+  if (use_pf) { if (Z) k_mf_sgd_pf<L, V, true> MF_ARGS; else k_mf_sgd_pf<L, V, false> MF_ARGS; }      \
+  else if (repl) k_mf_sgd<L, V, false, 1, 1, true> MF_ARGS;                                           \
   else if (Z) k_mf_sgd<L, V, true, 1> MF_ARGS;                                                        \
   else if (unroll == 4 && V == 1) k_mf_sgd<L, V, false, (V == 1 ? 4 : 1)> MF_ARGS;                    \
   else if (unroll == 2 || V > 1) k_mf_sgd<L, V, false, (V <= 2 ? 2 : 1)> MF_ARGS;                     \
