@@ -218,7 +218,8 @@ k_pa_multi(const __grid_constant__ FpsTableView t, const long long* __restrict__
   constexpr int WPB = PM_THREADS / 32;
   extern __shared__ __align__(16) float smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nvec = t.stride >> 2, L = p.n_classes;
+  // float4 slices that hold classes; a table padded to line-aligned rows (stride > dim) has more that stay zero
+  const int L = p.n_classes, nvec = (L + 3) >> 2;
   float* s_part = smem;                       // [WPB][stride]
   float* s_d = smem + WPB * t.stride;         // [stride] decision, then multiplier vector
   __shared__ float s_n2[WPB];

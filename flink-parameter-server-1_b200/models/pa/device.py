@@ -10,6 +10,7 @@ The dump at ``close`` lists only touched features (``RangePSLogicWithClose.scala
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Iterable, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -52,10 +53,16 @@ class DevicePA:
         self.feature_count, self.label_count = feature_count, (1 if algorithm == "binary" else label_count)
         if replicated is None:
             replicated = self.ctx.distributed and feature_count * self.label_count * 4 <= REPLICATE_BELOW_BYTES
+        # multiclass rows of 256 bytes and more are padded to whole 128-byte lines: a 400-byte row (100 classes)
+        # straddles 4-5 lines wherever it starts, a 512-byte one covers exactly 4 (measured on config 4: 0.675 ->
+        # see profiles/r2_pa/README.md; FPS_PA_ALIGN_ROWS=0 keeps the packed layout)
+        pad = 0
+        if algorithm != "binary" and self.label_count >= 64 and os.environ.get("FPS_PA_ALIGN_ROWS", "1") != "0":
+            pad = (-self.label_count) % 32
         self.table = ShardedTable(feature_count, self.label_count, n_shards=n_shards,
                                   partition="range" if range_partitioning else "hash",
                                   init_range=(0.0, 0.0), lazy=lazy, ctx=self.ctx,
-                                  scalar=(algorithm == "binary"), replicated=replicated)
+                                  scalar=(algorithm == "binary"), replicated=replicated, aux_cols=pad)
         self.params = N.FpsPaParams()
         self.params.variant = VARIANT[variant]
         self.params.C = aggressiveness
@@ -101,7 +108,7 @@ class DevicePA:
     def dump(self) -> list:
         """``Right((feature_id, param))`` for every touched feature of the local shard."""
         ids, rows = self.table.dump()
-        rows = rows.cpu().numpy().astype(np.float64)
+        rows = rows[:, : self.label_count].cpu().numpy().astype(np.float64)        # padding columns stay inside
         if self.algorithm == "binary":
             return [Right((k, float(v[0]))) for k, v in zip(ids.tolist(), rows)]
         return [Right((k, v)) for k, v in zip(ids.tolist(), rows)]
