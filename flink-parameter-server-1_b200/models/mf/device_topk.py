@@ -435,15 +435,25 @@ def ps_top_k_generator_device(src, model, num_factors: int = 10, user_memory: in
 def ps_online_learner_and_generator_device(src, n_users: int, n_items: int, batch_size: int = 256, **kw):
     """Device twin of ``ps_online_learner_and_generator`` (mini-batched prequential loop).  Returns
     ``(PrequentialOutput, DeviceLearnerGenerator)``; the output behaves like the reference's list of
-    ``(user, item, timestamp, topK)`` records and also offers vectorised ``ndcg()`` / ``hit_rate()``."""
+    ``(user, item, timestamp, topK)`` records and also offers vectorised ``ndcg()`` / ``hit_rate()``.
+    ``src``: an iterable of ``Rating`` or, columnar, a tuple ``(users, items, ratings[, timestamps])`` of arrays."""
     import torch
     lg = DeviceLearnerGenerator(n_users, n_items, **kw)
-    ratings = src if isinstance(src, list) else list(src)
-    n = len(ratings)
-    u = np.fromiter((r.user for r in ratings), dtype=np.int32, count=n)
-    i = np.fromiter((r.item for r in ratings), dtype=np.int32, count=n)
-    v = np.fromiter((r.rating for r in ratings), dtype=np.float32, count=n)
-    ts = [r.timestamp for r in ratings]
+    if isinstance(src, tuple) and len(src) in (3, 4) and not hasattr(src[0], "user"):
+        # columnar input ``(users, items, ratings[, timestamps])``: no per-record Python objects (unpacking 69K
+        # ``Rating`` objects costs 13 ms - half of the whole config-7 job at 2.6 M events/s)
+        u = np.ascontiguousarray(np.asarray(src[0]), dtype=np.int32)
+        i = np.ascontiguousarray(np.asarray(src[1]), dtype=np.int32)
+        v = np.ascontiguousarray(np.asarray(src[2]), dtype=np.float32)
+        n = len(u)
+        ts = list(np.asarray(src[3]).tolist()) if len(src) == 4 else list(range(n))
+    else:
+        ratings = src if isinstance(src, list) else list(src)
+        n = len(ratings)
+        u = np.fromiter((r.user for r in ratings), dtype=np.int32, count=n)
+        i = np.fromiter((r.item for r in ratings), dtype=np.int32, count=n)
+        v = np.fromiter((r.rating for r in ratings), dtype=np.float32, count=n)
+        ts = [r.timestamp for r in ratings]
     du, di, dv = (torch.from_numpy(x).cuda() for x in (u, i, v))
     parts = []
     for s in range(0, n, batch_size):

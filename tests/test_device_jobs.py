@@ -235,3 +235,22 @@ def test_learner_generator_step_replayed_from_a_cuda_graph():
     hg, he = out_g.hit_rate(1000), out_e.hit_rate(1000)
     assert hg > 0.3 and abs(hg - he) < 0.12, (hg, he)
     assert int(lg_g._tag_dev.item()) == 40                          # the tag advanced on every replay
+
+
+@pytest.mark.gpu
+def test_learner_generator_accepts_columnar_input():
+    """(users, items, ratings, timestamps) arrays instead of Rating objects: same job, same records."""
+    import random
+    from fps_b200.models.mf import Rating
+    from fps_b200.models.mf.device_topk import ps_online_learner_and_generator_device
+    rnd = random.Random(5)
+    stream = [Rating(u := rnd.randrange(30), (u % 3) * 10 + rnd.randrange(10), 1.0, 100 + t) for t in range(600)]
+    kw = dict(n_users=30, n_items=30, batch_size=64, num_factors=8, range_min=-0.1, range_max=0.1, learning_rate=0.1,
+              negative_sample_rate=2, user_memory=4, K=5, worker_k=5, pull_limit=500, seed=3)
+    out_a, _ = ps_online_learner_and_generator_device(stream, **kw)
+    cols = (np.array([r.user for r in stream]), np.array([r.item for r in stream]), np.array([r.rating for r in stream]),
+            np.array([r.timestamp for r in stream]))
+    out_b, _ = ps_online_learner_and_generator_device(cols, **kw)
+    assert len(out_a) == len(out_b) == 600
+    assert out_b[7][:3] == (stream[7].user, stream[7].item, stream[7].timestamp)
+    assert abs(out_a.hit_rate(300) - out_b.hit_rate(300)) < 0.15
