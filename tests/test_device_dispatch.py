@@ -411,3 +411,29 @@ def test_conflict_free_rounds_schedule():
     assert conflict_free_rounds(torch.tensor([], dtype=torch.int64)) == []
     one = conflict_free_rounds(torch.tensor([5, 6, 7]))
     assert len(one) == 1 and one[0].tolist() == [0, 1, 2]
+
+
+def test_pruning_strategy_codes_of_the_c_abi():
+    """LEMPPruningStrategy (object or the reference's string form) -> (code, focus set size, switch threshold)."""
+    from fps_b200.models.mf import pruning as P
+    from fps_b200.ops.topk import _strategy_code
+    assert _strategy_code(P.LENGTH()) == (0, 0, 0.0)
+    assert _strategy_code("coord") == (1, 0, 0.0)
+    assert _strategy_code(P.INCR(7)) == (2, 7, 0.0)
+    assert _strategy_code("lc:1.5") == (3, 0, 1.5)
+    assert _strategy_code(P.LI(5, 2.5)) == (4, 5, 2.5)
+    with pytest.raises(TypeError):
+        _strategy_code(3)
+    with pytest.raises(ValueError):
+        _strategy_code("nearest")
+
+
+def test_device_pruning_announces_only_what_is_not_executed():
+    from fps_b200.models.mf.jobs import device_pruning
+    from fps_b200.models.mf.pruning import COORD, LENGTH
+    with warnings.catch_warnings():
+        warnings.simplefilter("error", DE.DeviceFallbackWarning)
+        assert device_pruning(LENGTH()) is True
+        assert device_pruning(COORD(), candidate_filters=True) is True
+    with pytest.warns(DE.DeviceFallbackWarning, match="candidate_filters=True"):
+        assert device_pruning(COORD()) is True
